@@ -1,0 +1,208 @@
+/* tmat_b200.h -- C ABI of libtmat_b200.so: the B200 (sm_100a) implementation of the
+ * microvessel-branching segmentation hot path of fogg-lab/tissue-model-analysis-tools.
+ *
+ * The reference has no FFI on this path (plain Python functions on numpy arrays); these
+ * entry points are what a ctypes binding inside the reference package would call.  Each
+ * one cites the reference function it replaces (paths relative to the reference repo,
+ * package dir fl_tissue_model_tools/ abbreviated to its file name).
+ *
+ * Conventions
+ *   - every function returns 0 (TMAT_OK) or a negative TMAT_ERR_* code; the message for the
+ *     calling thread is available from tmat_last_error().  No exception crosses the boundary.
+ *   - pointers named *_dev are device pointers on the context's device; pointers named
+ *     *_host are host pointers (pageable or pinned).  The caller owns every buffer.
+ *   - images are row-major (C order), stacks are (Z, H, W) row-major, like the numpy
+ *     arrays the reference passes around (helper.py:90).
+ *   - device-pointer entry points are asynchronous on `stream` (a cudaStream_t passed as
+ *     void*; NULL = the legacy default stream); *_host entry points copy in, run, copy out
+ *     and synchronise before returning.
+ *   - a context owns scratch device memory and may be used by one thread at a time; create
+ *     one context per thread (compute_cell_area.py:108-113 fans out over dask threads).
+ */
+#ifndef TMAT_B200_H
+#define TMAT_B200_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TMAT_OK                  0
+#define TMAT_ERR_INVALID        -1   /* bad argument */
+#define TMAT_ERR_CUDA           -2   /* a CUDA call failed; see tmat_last_error() */
+#define TMAT_ERR_UNSUPPORTED    -3   /* valid in the reference, not implemented here */
+#define TMAT_ERR_NOMEM          -4
+#define TMAT_ERR_NO_DEVICE      -5   /* no sm_100 device: there is no CPU fallback */
+
+/* element types of images / stacks */
+#define TMAT_U8   0
+#define TMAT_U16  1
+#define TMAT_F32  2
+#define TMAT_F64  3
+
+/* Z-projection methods (scripts/compute_zproj.py:26-32) */
+#define TMAT_ZPROJ_MIN 0   /* zstacks.py:237 proj_min  -> same dtype  */
+#define TMAT_ZPROJ_MAX 1   /* zstacks.py:221 proj_max  -> same dtype  */
+#define TMAT_ZPROJ_AVG 2   /* zstacks.py:192 proj_avg  -> float64     */
+#define TMAT_ZPROJ_MED 3   /* zstacks.py:206 proj_med  -> float64     */
+#define TMAT_ZPROJ_FS  4   /* zstacks.py:153 proj_focus_stacking -> same dtype */
+
+typedef struct tmat_ctx  tmat_ctx;
+typedef struct tmat_unet tmat_unet;
+
+/* ---- library / context ------------------------------------------------------------ */
+int         tmat_version(void);
+const char* tmat_last_error(void);
+int  tmat_ctx_create(int device, tmat_ctx** out);
+int  tmat_ctx_destroy(tmat_ctx* ctx);
+int  tmat_ctx_sync(tmat_ctx* ctx);
+/* number of kernels of this library launched through `ctx` since creation (bench.py's
+ * gpu_launches claim is read from here). */
+int  tmat_ctx_launch_count(tmat_ctx* ctx, int64_t* out);
+
+/* ---- stage 1: Z projection  (zstacks.py:134-249) ------------------------------------ */
+/* stack: (Z,H,W) of dtype TMAT_U8|TMAT_U16 (TMAT_F32 for min/max/avg/med).  out: (H,W) of the
+ * stack dtype for MIN/MAX/FS, float64 for AVG/MED.  ksize must be 5 for FS (the reference's
+ * default kernel_size, zstacks.py:153). */
+int tmat_zproj_dev(tmat_ctx* ctx, const void* stack_dev, int dtype, int Z, int H, int W,
+                   int method, int ksize, void* out_dev, void* stream);
+int tmat_zproj_host(tmat_ctx* ctx, const void* stack_host, int dtype, int Z, int H, int W,
+                    int method, int ksize, void* out_host);
+
+/* ---- stage 2: smooth tiled prediction  (smooth_tiled_predictions.py:220-267) --------- */
+/* Geometry helper: padded shape, tiles per orientation (rotated frame), aug.
+ * geom[0]=aug geom[1]=PM geom[2]=PN geom[3]=step geom[4..5]=tiles (rows,cols) of even
+ * orientations, geom[6..7]= of odd orientations. */
+int tmat_stp_geometry(int H, int W, int ws, int subdiv, int* geom8);
+
+/* Generic pred_func path, step 1: tiles of orientation g (0..7, the order of
+ * _rotate_mirror_do, smooth_tiled_predictions.py:103-112) of the image padded by
+ * aug with its global minimum (:68-79), in raster order of the rotated frame (:157-163).
+ * tiles_dev: (n_tiles, ws, ws) float32. */
+int tmat_stp_gather_dev(tmat_ctx* ctx, const float* img_dev, int H, int W, int ws, int subdiv,
+                        int orient, float* tiles_dev, void* stream);
+/* Generic path, step 2: window multiply (:185), overlap-add (:206-217), /subdiv^2, D4 undo
+ * (:125-132), mean of 8 (:133), unpad + crop (:263-265).  preds_dev: the predictions of all 8
+ * orientations concatenated in orientation order, (n_total, ws, ws) float32.  window1d_host:
+ * ws float64 values of _spline_window (:26-41); NULL = computed by the library.
+ * out_dev: (H,W) float64.  Bit-identical to the reference given identical predictions. */
+int tmat_stp_blend_dev(tmat_ctx* ctx, const float* preds_dev, int H, int W, int ws, int subdiv,
+                       const double* window1d_host, double* out_dev, void* stream);
+int tmat_stp_gather_host(tmat_ctx* ctx, const float* img_host, int H, int W, int ws, int subdiv,
+                         int orient, float* tiles_host);
+int tmat_stp_blend_host(tmat_ctx* ctx, const float* preds_host, int H, int W, int ws, int subdiv,
+                        const double* window1d_host, double* out_host);
+/* _spline_window(ws, power=2) (:26-41) */
+int tmat_spline_window(int ws, double* out_host);
+
+/* UNet-Xception (models.py:85-171), forward only.  Weights are passed in Keras array layouts,
+ * float32, as parallel arrays of names/pointers (names as in oracle/unet.py: "stem.kernel",
+ * "down0.sep1.dw", "up2.ct1.kernel", "head.bias", ...). */
+typedef struct {
+  int patch;            /* window size, multiple of 32                         */
+  int channels;         /* input channels: 1 (models.py:600 default)            */
+  int filter_counts[4]; /* ascending, e.g. 64,128,256,512 (unet_patch_segmentor_1.json) */
+  int impl;             /* 0 = auto (tcgen05 when filter counts are multiples of 64),
+                           1 = force CUDA-core kernels (cross-check path), 2 = force tcgen05 */
+} tmat_unet_desc;
+int tmat_unet_load(tmat_ctx* ctx, const tmat_unet_desc* desc, int n_arrays,
+                   const char* const* names, const float* const* arrays_host,
+                   const int64_t* sizes, tmat_unet** out);
+int tmat_unet_free(tmat_unet* net);
+/* model.predict on a batch of patches: (n, ws, ws) float32 -> (n, ws, ws) float32 sigmoid
+ * probabilities (models.py:166).  logits!=0 returns pre-sigmoid values. */
+int tmat_unet_forward_dev(tmat_ctx* ctx, tmat_unet* net, const float* patches_dev, int n,
+                          float* probs_dev, int logits, void* stream);
+int tmat_unet_forward_host(tmat_ctx* ctx, tmat_unet* net, const float* patches_host, int n,
+                           float* probs_host, int logits);
+/* Fused fast path of predict_img_with_smooth_windowing with pred_func = this UNet
+ * (models.py:640): D4 folded into the stem's tile read, all orientations in one canvas. */
+int tmat_stp_predict_dev(tmat_ctx* ctx, tmat_unet* net, const float* img_dev, int H, int W,
+                         int subdiv, double* out_dev, void* stream);
+int tmat_stp_predict_host(tmat_ctx* ctx, tmat_unet* net, const float* img_host, int H, int W,
+                          int subdiv, double* out_host);
+/* debug / test hook: copy a named intermediate activation of the last forward (float32 NHWC)
+ * to the host; returns TMAT_ERR_INVALID when the tap does not exist. */
+int tmat_unet_debug_tap(tmat_ctx* ctx, tmat_unet* net, const char* name, float* out_host,
+                        int64_t capacity, int64_t* n_written);
+/* FLOPs (2*MAC of every convolution as written in models.py:110-171) of one patch */
+int tmat_unet_flops_per_patch(const tmat_unet_desc* desc, double* flops);
+
+/* ---- stage 3: thresholds and the Gaussian pre-filter -------------------------------- */
+/* scripts/compute_branches.py:334  seg_mask = pred > 0.5   (mask: uint8 0/1) */
+int tmat_threshold_gt_f64_dev(tmat_ctx* ctx, const double* x_dev, int64_t n, double thr,
+                              uint8_t* mask_dev, void* stream);
+/* preprocessing.py:13-23 apply_mask (out = img where mask!=0 else 0), float32 */
+int tmat_apply_mask_f32_dev(tmat_ctx* ctx, const float* img_dev, const uint8_t* mask_dev,
+                            int64_t n, float* out_dev, void* stream);
+/* skimage.filters.gaussian(image, sigma) as called at well_mask_generation.py:245:
+ * separable, mode='nearest', truncate=4; integer input is scaled to [0,1] float64 first and
+ * the result is float64; float32 input gives float32.  out dtype: F64 for U8/U16, F32 for F32. */
+int tmat_gaussian_dev(tmat_ctx* ctx, const void* img_dev, int dtype, int H, int W, double sigma,
+                      void* out_dev, void* stream);
+int tmat_gaussian_host(tmat_ctx* ctx, const void* img_host, int dtype, int H, int W, double sigma,
+                       void* out_host);
+/* well_mask_generation.py:236-277 auto_threshold_well: gaussian(sigma=1) -> rescale to uint8
+ * -> corner medians -> optional invert -> Otsu -> '>=' -> binary_erosion(disk(5)).
+ * mask: uint8 0/1.  info (optional, 4 ints): [0]=inverted [1]=otsu threshold [2]=u8 min [3]=u8 max */
+int tmat_auto_threshold_well_dev(tmat_ctx* ctx, const void* img_dev, int dtype, int H, int W,
+                                 uint8_t* mask_dev, int* info, void* stream);
+int tmat_auto_threshold_well_host(tmat_ctx* ctx, const void* img_host, int dtype, int H, int W,
+                                  uint8_t* mask_host, int* info);
+
+/* ---- stage 4: binary morphology / component cleanup --------------------------------- */
+/* skimage.filters.median(bool mask, disk(2)) (transforms.py:323) */
+int tmat_median_disk2_dev(tmat_ctx* ctx, const uint8_t* mask_dev, int H, int W, uint8_t* out_dev,
+                          void* stream);
+/* skimage.morphology.binary_erosion(mask, disk(r)) (well_mask_generation.py:275,
+ * scripts/compute_branches.py:130); outside the image counts as `border_value`. */
+int tmat_erode_disk_dev(tmat_ctx* ctx, const uint8_t* mask_dev, int H, int W, int r,
+                        int border_value, uint8_t* out_dev, void* stream);
+/* skimage.measure.label(mask, connectivity) (transforms.py:188,196,301,325): connectivity 1
+ * (4-neighbour) or 2 (8-neighbour); labels 1..n numbered in raster order of each component's
+ * first pixel.  Synchronises (n is returned to the host). */
+int tmat_label_dev(tmat_ctx* ctx, const uint8_t* mask_dev, int H, int W, int connectivity,
+                   int32_t* labels_dev, int* n_labels, void* stream);
+/* regionprops area + the 50-bin border-code histogram behind skimage's perimeter
+ * (transforms.py:326-329).  area_host: n int64; perim_hist_host: n*50 int64. */
+int tmat_region_stats_dev(tmat_ctx* ctx, const int32_t* labels_dev, int H, int W, int n_labels,
+                          int64_t* area_host, int64_t* perim_hist_host, void* stream);
+/* skimage.morphology.skeletonize, 2-D (transforms.py:331).  iterations (optional) receives
+ * the number of {sub-pass 1, sub-pass 2} rounds executed. */
+int tmat_skeletonize_dev(tmat_ctx* ctx, const uint8_t* mask_dev, int H, int W, uint8_t* out_dev,
+                         int* iterations, void* stream);
+/* transforms.py:306-361 filter_branch_seg_mask(mask, footprint=disk(2)|None, remove_isolated) */
+int tmat_filter_branch_seg_mask_dev(tmat_ctx* ctx, const uint8_t* mask_dev, int H, int W,
+                                    int use_median, int remove_isolated, uint8_t* out_dev,
+                                    void* stream);
+int tmat_filter_branch_seg_mask_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W,
+                                     int use_median, int remove_isolated, uint8_t* out_host);
+/* transforms.py:170-206 remove_small_islands; returns TMAT_ERR_INVALID for non-{0,1} input
+ * (the reference raises ValueError, :183-184). */
+int tmat_remove_small_islands_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W,
+                                   int min_area0, int min_area1, int connectivity0,
+                                   int connectivity1, uint8_t* out_host);
+/* transforms.py:291-303 regionprops_image(mask, 'area'): float64 image of component areas */
+int tmat_area_image_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W, double* out_host);
+/* host variants of the primitives (used by the Python mirror of transforms.py) */
+int tmat_median_disk2_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W, uint8_t* out_host);
+int tmat_erode_disk_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W, int r,
+                         int border_value, uint8_t* out_host);
+int tmat_label_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W, int connectivity,
+                    int32_t* labels_host, int* n_labels);
+int tmat_skeletonize_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W, uint8_t* out_host,
+                          int* iterations);
+
+/* ---- whole path for one image (scripts/compute_branches.py:316-337) ------------------ */
+/* stack (Z,H,W) uint16 -> max projection (:228) -> rescale_intensity to [0,1] float32 (:316)
+ * -> predict_img_with_smooth_windowing (models.py:640) -> pred > 0.5 (:334)
+ * -> filter_branch_seg_mask (:337).  pred_dev (optional) receives the float64 probabilities. */
+int tmat_branch_mask_dev(tmat_ctx* ctx, tmat_unet* net, const uint16_t* stack_dev, int Z, int H,
+                         int W, int subdiv, double* pred_dev, uint8_t* mask_dev, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TMAT_B200_H */

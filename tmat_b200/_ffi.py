@@ -1,0 +1,168 @@
+"""ctypes binding of libtmat_b200.so (include/tmat_b200.h).
+
+The library is the product; there is no Python or CPU fallback.  If the shared object is
+missing it is built in-tree (nvcc); if no sm_100 device is present every compute call raises
+``TmatError``.
+"""
+import ctypes as C
+import os
+import threading
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libtmat_b200.so")
+
+OK, ERR_INVALID, ERR_CUDA, ERR_UNSUPPORTED, ERR_NOMEM, ERR_NO_DEVICE = 0, -1, -2, -3, -4, -5
+U8, U16, F32, F64 = 0, 1, 2, 3
+DTYPES = {np.dtype(np.uint8): U8, np.dtype(np.uint16): U16, np.dtype(np.float32): F32,
+          np.dtype(np.float64): F64}
+ZPROJ = {"min": 0, "max": 1, "avg": 2, "med": 3, "fs": 4}
+
+
+class TmatError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"libtmat_b200 error {code}: {msg}")
+        self.code = code
+
+
+class UnetDesc(C.Structure):
+    _fields_ = [("patch", C.c_int), ("channels", C.c_int), ("filter_counts", C.c_int * 4),
+                ("impl", C.c_int)]
+
+
+_lib = None
+_lib_lock = threading.Lock()
+
+_vp, _i, _i64 = C.c_void_p, C.c_int, C.c_int64
+_pi = C.POINTER(C.c_int)
+
+# name -> argtypes (restype is always int unless listed in _SPECIAL)
+SIGNATURES = {
+    "tmat_ctx_create": [_i, C.POINTER(_vp)],
+    "tmat_ctx_destroy": [_vp],
+    "tmat_ctx_sync": [_vp],
+    "tmat_ctx_launch_count": [_vp, C.POINTER(_i64)],
+    "tmat_zproj_dev": [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp],
+    "tmat_zproj_host": [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp],
+    "tmat_stp_geometry": [_i, _i, _i, _i, _pi],
+    "tmat_stp_gather_dev": [_vp, _vp, _i, _i, _i, _i, _i, _vp, _vp],
+    "tmat_stp_blend_dev": [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp],
+    "tmat_stp_gather_host": [_vp, _vp, _i, _i, _i, _i, _i, _vp],
+    "tmat_stp_blend_host": [_vp, _vp, _i, _i, _i, _i, _vp, _vp],
+    "tmat_spline_window": [_i, _vp],
+    "tmat_unet_load": [_vp, C.POINTER(UnetDesc), _i, C.POINTER(C.c_char_p), C.POINTER(_vp),
+                       C.POINTER(_i64), C.POINTER(_vp)],
+    "tmat_unet_free": [_vp],
+    "tmat_unet_forward_dev": [_vp, _vp, _vp, _i, _vp, _i, _vp],
+    "tmat_unet_forward_host": [_vp, _vp, _vp, _i, _vp, _i],
+    "tmat_stp_predict_dev": [_vp, _vp, _vp, _i, _i, _i, _vp, _vp],
+    "tmat_stp_predict_host": [_vp, _vp, _vp, _i, _i, _i, _vp],
+    "tmat_unet_debug_tap": [_vp, _vp, C.c_char_p, _vp, _i64, C.POINTER(_i64)],
+    "tmat_unet_flops_per_patch": [C.POINTER(UnetDesc), C.POINTER(C.c_double)],
+    "tmat_threshold_gt_f64_dev": [_vp, _vp, _i64, C.c_double, _vp, _vp],
+    "tmat_apply_mask_f32_dev": [_vp, _vp, _vp, _i64, _vp, _vp],
+    "tmat_gaussian_dev": [_vp, _vp, _i, _i, _i, C.c_double, _vp, _vp],
+    "tmat_gaussian_host": [_vp, _vp, _i, _i, _i, C.c_double, _vp],
+    "tmat_auto_threshold_well_dev": [_vp, _vp, _i, _i, _i, _vp, _pi, _vp],
+    "tmat_auto_threshold_well_host": [_vp, _vp, _i, _i, _i, _vp, _pi],
+    "tmat_median_disk2_dev": [_vp, _vp, _i, _i, _vp, _vp],
+    "tmat_erode_disk_dev": [_vp, _vp, _i, _i, _i, _i, _vp, _vp],
+    "tmat_label_dev": [_vp, _vp, _i, _i, _i, _vp, _pi, _vp],
+    "tmat_region_stats_dev": [_vp, _vp, _i, _i, _i, _vp, _vp, _vp],
+    "tmat_skeletonize_dev": [_vp, _vp, _i, _i, _vp, _pi, _vp],
+    "tmat_filter_branch_seg_mask_dev": [_vp, _vp, _i, _i, _i, _i, _vp, _vp],
+    "tmat_filter_branch_seg_mask_host": [_vp, _vp, _i, _i, _i, _i, _vp],
+    "tmat_remove_small_islands_host": [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp],
+    "tmat_area_image_host": [_vp, _vp, _i, _i, _vp],
+    "tmat_median_disk2_host": [_vp, _vp, _i, _i, _vp],
+    "tmat_erode_disk_host": [_vp, _vp, _i, _i, _i, _i, _vp],
+    "tmat_label_host": [_vp, _vp, _i, _i, _i, _vp, _pi],
+    "tmat_skeletonize_host": [_vp, _vp, _i, _i, _vp, _pi],
+    "tmat_branch_mask_dev": [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp],
+}
+_SPECIAL = {"tmat_version": ([], _i), "tmat_last_error": ([], C.c_char_p)}
+
+
+def lib():
+    """Load (building if necessary) the shared library and declare every prototype."""
+    global _lib
+    with _lib_lock:
+        if _lib is None:
+            if not os.path.exists(LIB_PATH):
+                from . import build as _build
+                _build.build()
+            L = C.CDLL(LIB_PATH)
+            for name, args in SIGNATURES.items():
+                f = getattr(L, name)
+                f.argtypes = args
+                f.restype = _i
+            for name, (args, res) in _SPECIAL.items():
+                f = getattr(L, name)
+                f.argtypes = args
+                f.restype = res
+            _lib = L
+    return _lib
+
+
+def check(code):
+    if code != OK:
+        raise TmatError(code, lib().tmat_last_error().decode("utf-8", "replace"))
+
+
+class Context:
+    """One libtmat_b200 context (device scratch + launch counter).  Not thread-safe: use
+    ``default_context()`` for a per-thread instance."""
+
+    def __init__(self, device=0):
+        self.handle = _vp()
+        check(lib().tmat_ctx_create(device, C.byref(self.handle)))
+        self.device = device
+
+    def close(self):
+        if self.handle:
+            lib().tmat_ctx_destroy(self.handle)
+            self.handle = _vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def sync(self):
+        check(lib().tmat_ctx_sync(self.handle))
+
+    def launch_count(self):
+        n = _i64()
+        check(lib().tmat_ctx_launch_count(self.handle, C.byref(n)))
+        return n.value
+
+
+_tls = threading.local()
+
+
+def default_context():
+    ctx = getattr(_tls, "ctx", None)
+    if ctx is None:
+        dev = int(os.environ.get("TMAT_DEVICE", os.environ.get("LOCAL_RANK", "0")))
+        ctx = Context(dev)
+        _tls.ctx = ctx
+    return ctx
+
+
+def ptr(a):
+    """void* of a C-contiguous numpy array, or of anything exposing data_ptr() (torch)."""
+    if a is None:
+        return None
+    if hasattr(a, "data_ptr"):
+        return _vp(a.data_ptr())
+    assert a.flags["C_CONTIGUOUS"]
+    return _vp(a.ctypes.data)
+
+
+def as_c(a, dtype=None):
+    a = np.asarray(a)
+    if dtype is not None and a.dtype != dtype:
+        a = a.astype(dtype)
+    return np.ascontiguousarray(a)

@@ -1,0 +1,116 @@
+// Context, scratch arena and error plumbing of libtmat_b200 (no reference counterpart: the
+// reference is a Python library; this is the state a ctypes binding holds per thread).
+#include "common.cuh"
+
+static thread_local char g_err[1024] = "";
+
+void tmat_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+extern "C" const char* tmat_last_error(void) { return g_err; }
+extern "C" int tmat_version(void) { return 100; }
+
+extern "C" int tmat_ctx_create(int device, tmat_ctx** out) {
+  if (!out) {
+    tmat_set_error("tmat_ctx_create: out is NULL");
+    return TMAT_ERR_INVALID;
+  }
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0) {
+    tmat_set_error("tmat_ctx_create: no CUDA device (%s); libtmat_b200 has no CPU fallback",
+                   e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
+    cudaGetLastError();
+    return TMAT_ERR_NO_DEVICE;
+  }
+  TMAT_REQUIRE(device >= 0 && device < n, "tmat_ctx_create: device %d out of range [0,%d)", device, n);
+  CUDA_TRY(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) {
+    tmat_set_error("tmat_ctx_create: device %d is sm_%d%d; this library is built for sm_100a only",
+                   device, prop.major, prop.minor);
+    return TMAT_ERR_NO_DEVICE;
+  }
+  tmat_ctx* ctx = new tmat_ctx();
+  ctx->device = device;
+  ctx->sm_count = prop.multiProcessorCount;
+  ctx->cc_major = prop.major;
+  ctx->cc_minor = prop.minor;
+  ctx->pinned_cap = 1 << 16;
+  CUDA_TRY(cudaMallocHost(&ctx->pinned, ctx->pinned_cap));
+  *out = ctx;
+  return TMAT_OK;
+}
+
+static void free_overflow(tmat_ctx* ctx) {
+  for (void* p : ctx->overflow) cudaFree(p);
+  ctx->overflow.clear();
+  ctx->overflow_bytes = 0;
+}
+
+extern "C" int tmat_ctx_destroy(tmat_ctx* ctx) {
+  if (!ctx) return TMAT_OK;
+  cudaSetDevice(ctx->device);
+  cudaDeviceSynchronize();
+  free_overflow(ctx);
+  if (ctx->arena) cudaFree(ctx->arena);
+  if (ctx->pinned) cudaFreeHost(ctx->pinned);
+  delete ctx;
+  return TMAT_OK;
+}
+
+extern "C" int tmat_ctx_sync(tmat_ctx* ctx) {
+  TMAT_REQUIRE(ctx, "tmat_ctx_sync: ctx is NULL");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  CUDA_TRY(cudaDeviceSynchronize());
+  return TMAT_OK;
+}
+
+extern "C" int tmat_ctx_launch_count(tmat_ctx* ctx, int64_t* out) {
+  TMAT_REQUIRE(ctx && out, "tmat_ctx_launch_count: NULL argument");
+  *out = ctx->launches;
+  return TMAT_OK;
+}
+
+int arena_reset(tmat_ctx* ctx) {
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  if (!ctx->overflow.empty()) {
+    // the previous call did not fit: wait for it, then grow so the steady state is malloc-free
+    CUDA_TRY(cudaDeviceSynchronize());
+    size_t want = align_up(ctx->arena_off + ctx->overflow_bytes + (ctx->overflow.size() + 1) * 512, 1 << 20);
+    want += want / 4;
+    free_overflow(ctx);
+    if (ctx->arena) CUDA_TRY(cudaFree(ctx->arena));
+    ctx->arena = nullptr;
+    ctx->arena_cap = 0;
+    CUDA_TRY(cudaMalloc((void**)&ctx->arena, want));
+    ctx->arena_cap = want;
+  }
+  ctx->arena_off = 0;
+  return TMAT_OK;
+}
+
+int arena_alloc(tmat_ctx* ctx, size_t bytes, void** out) {
+  bytes = align_up(bytes ? bytes : 1, 512);
+  if (ctx->arena && ctx->arena_off + bytes <= ctx->arena_cap) {
+    *out = ctx->arena + ctx->arena_off;
+    ctx->arena_off += bytes;
+    return TMAT_OK;
+  }
+  void* p = nullptr;
+  cudaError_t e = cudaMalloc(&p, bytes);
+  if (e != cudaSuccess) {
+    tmat_set_error("arena_alloc: cudaMalloc(%zu) failed: %s", bytes, cudaGetErrorString(e));
+    cudaGetLastError();
+    return TMAT_ERR_NOMEM;
+  }
+  ctx->overflow.push_back(p);
+  ctx->overflow_bytes += bytes;
+  *out = p;
+  return TMAT_OK;
+}
