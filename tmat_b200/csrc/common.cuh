@@ -68,6 +68,9 @@ static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; 
 int arena_reset(tmat_ctx* ctx);
 // Allocate scratch device memory valid until the next arena_reset.
 int arena_alloc(tmat_ctx* ctx, size_t bytes, void** out);
+int arena_reserve(tmat_ctx* ctx, size_t bytes);
+static inline size_t arena_mark(tmat_ctx* ctx) { return ctx->arena_off; }
+static inline void arena_release(tmat_ctx* ctx, size_t mark) { if (mark <= ctx->arena_off) ctx->arena_off = mark; }
 template <typename T>
 static inline int arena_get(tmat_ctx* ctx, size_t count, T** out) {
   void* p = nullptr;

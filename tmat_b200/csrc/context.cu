@@ -114,3 +114,22 @@ int arena_alloc(tmat_ctx* ctx, size_t bytes, void** out) {
   *out = p;
   return TMAT_OK;
 }
+
+// Make sure the arena can hold `bytes` (plus what is already allocated) without overflowing.
+int arena_reserve(tmat_ctx* ctx, size_t bytes) {
+  size_t want = align_up(ctx->arena_off + bytes + (1 << 20), 1 << 20);
+  if (ctx->arena && want <= ctx->arena_cap) return TMAT_OK;
+  if (ctx->arena_off != 0) return TMAT_OK;   // live allocations: fall back to overflow blocks
+  CUDA_TRY(cudaDeviceSynchronize());
+  if (ctx->arena) CUDA_TRY(cudaFree(ctx->arena));
+  ctx->arena = nullptr;
+  ctx->arena_cap = 0;
+  cudaError_t e = cudaMalloc((void**)&ctx->arena, want);
+  if (e != cudaSuccess) {
+    tmat_set_error("arena_reserve: cudaMalloc(%zu) failed: %s", want, cudaGetErrorString(e));
+    cudaGetLastError();
+    return TMAT_ERR_NOMEM;
+  }
+  ctx->arena_cap = want;
+  return TMAT_OK;
+}

@@ -2,14 +2,6 @@
 // TMAT_ERR_UNSUPPORTED loudly; the file shrinks as stages land and is deleted when empty.
 #include "common.cuh"
 #define STUB(name, ...) extern "C" int name(__VA_ARGS__) { tmat_set_error(#name ": not implemented yet"); return TMAT_ERR_UNSUPPORTED; }
-STUB(tmat_unet_load, tmat_ctx*, const tmat_unet_desc*, int, const char* const*, const float* const*, const int64_t*, tmat_unet**)
-STUB(tmat_unet_free, tmat_unet*)
-STUB(tmat_unet_forward_dev, tmat_ctx*, tmat_unet*, const float*, int, float*, int, void*)
-STUB(tmat_unet_forward_host, tmat_ctx*, tmat_unet*, const float*, int, float*, int)
-STUB(tmat_stp_predict_dev, tmat_ctx*, tmat_unet*, const float*, int, int, int, double*, void*)
-STUB(tmat_stp_predict_host, tmat_ctx*, tmat_unet*, const float*, int, int, int, double*)
-STUB(tmat_unet_debug_tap, tmat_ctx*, tmat_unet*, const char*, float*, int64_t, int64_t*)
-STUB(tmat_unet_flops_per_patch, const tmat_unet_desc*, double*)
 STUB(tmat_threshold_gt_f64_dev, tmat_ctx*, const double*, int64_t, double, uint8_t*, void*)
 STUB(tmat_apply_mask_f32_dev, tmat_ctx*, const float*, const uint8_t*, int64_t, float*, void*)
 STUB(tmat_gaussian_dev, tmat_ctx*, const void*, int, int, int, double, void*, void*)

@@ -1,0 +1,190 @@
+"""UNet-Xception patch segmentor on the B200: drop-in for the inference side of the reference's
+``fl_tissue_model_tools/models.py`` (``build_UNetXception:85``, ``UNetXceptionPatchSegmentor:597``,
+``get_unet_patch_segmentor_from_cfg:656``).  Forward pass only; training utilities are out of scope.
+
+``CudaUNet`` plays the role of the Keras model: ``CudaUNet.predict(batch, verbose=0)`` has the
+``model.predict`` contract that ``predict_img_with_smooth_windowing`` expects, and is recognised
+there as the fused fast path.
+"""
+import ctypes as C
+import json
+import os
+
+import numpy as np
+
+from . import _ffi
+from .smooth_tiled_predictions import predict_img_with_smooth_windowing
+
+
+def weight_names(filter_counts=(64, 128, 256, 512)):
+    """Names and Keras-layout shapes of every array of build_UNetXception (models.py:110-171)."""
+    fc = sorted(filter_counts)
+    out = []
+
+    def bn(prefix, c):
+        for k in ("gamma", "beta", "mean", "var"):
+            out.append((f"{prefix}.{k}", (c,)))
+
+    out.append(("stem.kernel", (3, 3, 1, fc[0])))
+    out.append(("stem.bias", (fc[0],)))
+    bn("stem.bn", fc[0])
+    cin = fc[0]
+    for i, f in enumerate(fc[1:]):
+        p = f"down{i}"
+        for s, ci in (("sep1", cin), ("sep2", f)):
+            out.append((f"{p}.{s}.dw", (3, 3, ci, 1)))
+            out.append((f"{p}.{s}.pw", (1, 1, ci, f)))
+            out.append((f"{p}.{s}.bias", (f,)))
+            bn(f"{p}.bn{s[-1]}", f)
+        out.append((f"{p}.res.kernel", (1, 1, cin, f)))
+        out.append((f"{p}.res.bias", (f,)))
+        cin = f
+    for i, f in enumerate(reversed(fc)):
+        p = f"up{i}"
+        for s, ci in (("ct1", cin), ("ct2", f)):
+            out.append((f"{p}.{s}.kernel", (3, 3, f, ci)))     # Conv2DTranspose: (kh, kw, out, in)
+            out.append((f"{p}.{s}.bias", (f,)))
+            bn(f"{p}.bn{s[-1]}", f)
+        out.append((f"{p}.res.kernel", (1, 1, cin, f)))
+        out.append((f"{p}.res.bias", (f,)))
+        cin = f
+    out.append(("head.kernel", (3, 3, cin, 1)))
+    out.append(("head.bias", (1,)))
+    return out
+
+
+def random_init_weights(filter_counts=(64, 128, 256, 512), seed=0):
+    """Keras default initialisation of a freshly built model: glorot-uniform kernels, zero biases,
+    identity BatchNorm statistics (what the reference has before ``load_weights``, models.py:615)."""
+    rng = np.random.default_rng(seed)
+    w = {}
+    for name, shape in weight_names(filter_counts):
+        leaf = name.rsplit(".", 1)[1]
+        if leaf in ("kernel", "dw", "pw"):
+            kh, kw, a, b = shape
+            if leaf == "dw":
+                fan_in, fan_out = kh * kw * a, kh * kw * b
+            elif ".ct" in name:
+                fan_in, fan_out = kh * kw * b, kh * kw * a
+            else:
+                fan_in, fan_out = kh * kw * a, kh * kw * b
+            lim = np.sqrt(6.0 / (fan_in + fan_out))
+            w[name] = rng.uniform(-lim, lim, size=shape).astype(np.float32)
+        elif leaf in ("gamma", "var"):
+            w[name] = np.ones(shape, np.float32)
+        else:
+            w[name] = np.zeros(shape, np.float32)
+    return w
+
+
+class CudaUNet:
+    """The compiled UNet living on the GPU.  ``impl``: 'auto' | 'simt' | 'tc'."""
+
+    def __init__(self, weights, patch, filter_counts=(64, 128, 256, 512), channels=1, impl="auto", ctx=None):
+        self.ctx = ctx or _ffi.default_context()
+        self.patch = int(patch)
+        self.filter_counts = tuple(sorted(int(f) for f in filter_counts))
+        desc = _ffi.UnetDesc()
+        desc.patch = self.patch
+        desc.channels = int(channels)
+        for i, f in enumerate(self.filter_counts):
+            desc.filter_counts[i] = f
+        desc.impl = {"auto": 0, "simt": 1, "tc": 2}[impl]
+        self.desc = desc
+        names = sorted(weights)
+        arrays = [np.ascontiguousarray(weights[k], dtype=np.float32) for k in names]
+        n = len(names)
+        c_names = (C.c_char_p * n)(*[k.encode() for k in names])
+        c_ptrs = (C.c_void_p * n)(*[a.ctypes.data for a in arrays])
+        c_sizes = (C.c_int64 * n)(*[a.size for a in arrays])
+        h = C.c_void_p()
+        _ffi.check(_ffi.lib().tmat_unet_load(self.ctx.handle, C.byref(desc), n, c_names, c_ptrs, c_sizes,
+                                             C.byref(h)))
+        self._tmat_handle = h
+
+    def close(self):
+        if getattr(self, "_tmat_handle", None):
+            _ffi.lib().tmat_unet_free(self._tmat_handle)
+            self._tmat_handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def flops_per_patch(self):
+        f = C.c_double()
+        _ffi.check(_ffi.lib().tmat_unet_flops_per_patch(C.byref(self.desc), C.byref(f)))
+        return f.value
+
+    def predict(self, batch, verbose=0, logits=False):
+        """Keras ``model.predict`` contract: (n, ws, ws[, 1]) float32 -> (n, ws, ws, 1) float32."""
+        x = _ffi.as_c(batch, np.float32)
+        if x.ndim == 4 and x.shape[-1] == 1:
+            x = x[..., 0]
+        if x.ndim != 3 or x.shape[1] != self.patch or x.shape[2] != self.patch:
+            raise ValueError(f"expected (n, {self.patch}, {self.patch}) patches, got {x.shape}")
+        x = np.ascontiguousarray(x)
+        out = np.empty(x.shape, dtype=np.float32)
+        _ffi.check(_ffi.lib().tmat_unet_forward_host(self.ctx.handle, self._tmat_handle, _ffi.ptr(x), x.shape[0],
+                                                     _ffi.ptr(out), int(bool(logits))))
+        return out[..., None]
+
+    def debug_tap(self, name):
+        n = C.c_int64()
+        L = _ffi.lib()
+        _ffi.check(L.tmat_unet_debug_tap(self.ctx.handle, self._tmat_handle, name.encode(), None, 0, C.byref(n)))
+        out = np.empty(n.value, np.float32)
+        _ffi.check(L.tmat_unet_debug_tap(self.ctx.handle, self._tmat_handle, name.encode(), _ffi.ptr(out), n.value,
+                                         C.byref(n)))
+        return out
+
+
+def load_checkpoint(checkpoint_file, filter_counts):
+    """Weights as a name -> array dict.  ``.npz`` files use the names of :func:`weight_names`;
+    ``None`` gives a random initialisation (the reference's trained ``checkpoint_1.h5`` is not
+    distributed with its repository)."""
+    if checkpoint_file is None:
+        return random_init_weights(filter_counts)
+    if isinstance(checkpoint_file, dict):
+        return checkpoint_file
+    if str(checkpoint_file).endswith(".npz"):
+        with np.load(checkpoint_file) as z:
+            return {k: z[k] for k in z.files}
+    raise ValueError("checkpoint must be a .npz with tmat_b200.models.weight_names() keys "
+                     "(convert a Keras .h5 with model.get_weights() in layer order)")
+
+
+class UNetXceptionPatchSegmentor:
+    """models.py:597-653, same constructor and ``predict`` signature."""
+
+    def __init__(self, patch_size, checkpoint_file, filter_counts, ds_ratio=0.5, norm_mean=None,
+                 norm_std=None, channels=1):
+        self.ds_ratio = ds_ratio
+        self.norm_mean = norm_mean
+        self.norm_std = norm_std
+        self.patch_size = patch_size
+        self.channels = channels
+        self.model = CudaUNet(load_checkpoint(checkpoint_file, filter_counts), patch_size, filter_counts, channels)
+
+    def predict(self, x, auto_resample=True):
+        x = np.asarray(x).astype(np.float32)
+        if auto_resample:
+            raise NotImplementedError("auto_resample (PIL Lanczos pre/post resize, models.py:630-651) is outside "
+                                      "the hot path; compute_branches.py calls predict(auto_resample=False)")
+        if self.norm_mean is not None and self.norm_std is not None:
+            x = (x - self.norm_mean) / self.norm_std
+        return predict_img_with_smooth_windowing(x, self.patch_size, 2, self.model.predict)
+
+
+def get_unet_patch_segmentor_from_cfg(cfg_json, checkpoint_file=None):
+    """models.py:656-684: build the segmentor from the reference's JSON config."""
+    with open(cfg_json, "r") as f:
+        cfg = json.load(f)
+    ckpt = checkpoint_file
+    if ckpt is None and cfg.get("checkpoint_file"):
+        cand = os.path.join(os.path.dirname(cfg_json), "..", "checkpoints", cfg["checkpoint_file"])
+        ckpt = cand if os.path.exists(cand) and cand.endswith(".npz") else None
+    return UNetXceptionPatchSegmentor(cfg["patch_size"], ckpt, cfg["filter_counts"], cfg.get("ds_ratio", 0.5),
+                                      cfg.get("norm_mean"), cfg.get("norm_std"), cfg.get("channels", 1))
