@@ -1,0 +1,85 @@
+"""GPU: UNet-Xception forward (tcgen05 and CUDA-core executors) and the fused tiled prediction
+vs the torch-CPU fp32 oracle.  Tolerance: north_star's 1e-2 max-abs on probabilities (bf16
+operands, fp32 accumulate); masks agree on >= 99.9 % of pixels."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import helpers
+from oracle import unet as ou, stp as ostp
+
+pytestmark = pytest.mark.gpu
+PROB_TOL = 1e-2   # BASELINE.json north_star: blended probabilities within 1e-2 max-abs
+
+CONV_CASES = [
+    # B, H, W, C0, C1, Cout, taps, epi, relu, dual
+    (1, 8, 16, 64, 0, 64, 1, 0, 0, 0), (1, 8, 16, 64, 0, 64, 9, 0, 0, 0),
+    (2, 16, 16, 128, 0, 128, 9, 0, 1, 0), (2, 20, 20, 512, 0, 512, 9, 0, 1, 0),
+    (3, 20, 20, 512, 512, 512, 9, 1, 0, 1), (2, 40, 40, 256, 512, 256, 9, 1, 0, 1),
+    (2, 80, 80, 64, 0, 128, 1, 0, 1, 0), (2, 40, 40, 64, 0, 128, 1, 2, 0, 1),
+    (1, 24, 24, 64, 0, 4, 9, 3, 0, 0), (5, 13, 27, 64, 64, 64, 9, 0, 0, 0),
+    (9, 7, 5, 128, 0, 256, 9, 0, 1, 0), (1, 160, 160, 128, 0, 64, 9, 0, 1, 0),
+]
+
+
+@pytest.mark.parametrize("case", CONV_CASES)
+def test_tcgen05_conv_matches_cuda_core_conv(case):
+    from tmat_b200 import _ffi
+    ctx = _ffi.default_context()
+    d, m = C.c_double(), C.c_double()
+    _ffi.check(_ffi.lib().tmat_debug_conv_selftest(ctx.handle, *case, 7, C.byref(d), C.byref(m)))
+    assert m.value > 0.1
+    # both executors round the same fp32 sums to bf16: at most one bf16 ulp apart
+    assert d.value <= m.value * 2 ** -7, (d.value, m.value)
+
+
+@pytest.mark.parametrize("fc,ws,n,impl", [((8, 16, 32, 64), 64, 2, "simt"), ((64, 128, 256, 512), 64, 3, "tc"),
+                                          ((64, 128, 256, 512), 96, 5, "tc"), ((64, 64, 128, 128), 64, 2, "tc")])
+def test_unet_forward_vs_oracle(fc, ws, n, impl):
+    from tmat_b200 import models
+    w = ou.make_weights(fc, seed=3, randomize_affine=True)
+    x = np.random.default_rng(0).random((n, ws, ws), dtype=np.float32)
+    taps = {}
+    ref = ou.forward(w, x, taps=taps)
+    net = models.CudaUNet(w, ws, fc, impl=impl)
+    out = net.predict(x)
+    assert out.shape == ref.shape and out.dtype == np.float32
+    assert np.abs(out - ref).max() < PROB_TOL
+    for name in ("stem", "down0", "down2", "up0", "up2"):
+        got = net.debug_tap(name).reshape(taps[name].shape)
+        assert np.abs(got - taps[name]).max() < 0.02 * max(1.0, np.abs(taps[name]).max()), name
+    assert abs(net.flops_per_patch() - ou.flops_per_patch(ws, fc)) < 1
+
+
+def test_unet_full_patch_keras_default_init():
+    """The reference configuration (patch 320, filters 64..512) with Keras-default weights."""
+    from tmat_b200 import models
+    w = ou.make_weights(seed=0)
+    x = np.stack([helpers.synth_projection(320, 320, 5), helpers.synth_projection(320, 320, 6)])
+    ref = ou.forward(w, x)
+    net = models.CudaUNet(w, 320, impl="tc")
+    out = net.predict(x)
+    assert np.abs(out - ref).max() < PROB_TOL
+    assert abs(net.flops_per_patch() / 1e9 - 31.026) < 0.01
+
+
+def test_fused_tiled_prediction_vs_oracle():
+    """predict_img_with_smooth_windowing with the CUDA UNet (fused path) vs the oracle driver with
+    the oracle UNet: probabilities within 1e-2, masks >= 99.9 % equal."""
+    from tmat_b200 import models
+    from tmat_b200.smooth_tiled_predictions import predict_img_with_smooth_windowing
+    fc, ws = (64, 128, 256, 512), 64
+    w = ou.make_weights(fc, seed=5, randomize_affine=True, head_gain=4.0)
+    img = helpers.synth_projection(150, 131, 9)
+    net = models.CudaUNet(w, ws, fc, impl="tc")
+    out = predict_img_with_smooth_windowing(img, ws, 2, net.predict)
+    ref = ostp.predict_img_with_smooth_windowing(img, ws, 2, ou.make_pred_func(w))
+    assert out.shape == ref.shape and out.dtype == np.float64
+    assert np.abs(out - ref).max() < PROB_TOL
+    clear = np.abs(ref - 0.5) > PROB_TOL
+    assert ((out > 0.5) == (ref > 0.5))[clear].all()
+    assert ((out > 0.5) == (ref > 0.5)).mean() >= 0.999
+    # the generic route (tiles -> net.predict on host batches -> GPU blend) agrees with the fused one
+    gen = predict_img_with_smooth_windowing(img, ws, 2, lambda b, verbose=0: net.predict(b))
+    assert np.abs(gen - out).max() < 1e-6
