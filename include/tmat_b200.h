@@ -62,6 +62,12 @@ int  tmat_ctx_sync(tmat_ctx* ctx);
  * gpu_launches claim is read from here). */
 int  tmat_ctx_launch_count(tmat_ctx* ctx, int64_t* out);
 
+/* Per-launch CUDA-event timing of the tensor-core convolution kernel (bench.py's roofline leg).
+ * collect: out3[0] = summed kernel time in ms since the last collect, out3[1] = launches,
+ * out3[2] = FLOPs executed by them; synchronises the device. */
+int  tmat_ctx_profile_enable(tmat_ctx* ctx, int on);
+int  tmat_ctx_profile_collect(tmat_ctx* ctx, double* out3);
+
 /* ---- stage 1: Z projection  (zstacks.py:134-249) ------------------------------------ */
 /* stack: (Z,H,W) of dtype TMAT_U8|TMAT_U16 (TMAT_F32 for min/max/avg/med).  out: (H,W) of the
  * stack dtype for MIN/MAX/FS, float64 for AVG/MED.  ksize must be 5 for FS (the reference's

@@ -43,6 +43,8 @@ SIGNATURES = {
     "tmat_ctx_destroy": [_vp],
     "tmat_ctx_sync": [_vp],
     "tmat_ctx_launch_count": [_vp, C.POINTER(_i64)],
+    "tmat_ctx_profile_enable": [_vp, _i],
+    "tmat_ctx_profile_collect": [_vp, C.POINTER(C.c_double)],
     "tmat_zproj_dev": [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp],
     "tmat_zproj_host": [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp],
     "tmat_stp_geometry": [_i, _i, _i, _i, _pi],
@@ -134,6 +136,15 @@ class Context:
 
     def sync(self):
         check(lib().tmat_ctx_sync(self.handle))
+
+    def profile(self, on):
+        check(lib().tmat_ctx_profile_enable(self.handle, int(on)))
+
+    def profile_collect(self):
+        """(kernel ms, launches, executed FLOPs) of the tcgen05 conv launches since the last call."""
+        out = (C.c_double * 3)()
+        check(lib().tmat_ctx_profile_collect(self.handle, out))
+        return out[0], int(out[1]), out[2]
 
     def launch_count(self):
         n = _i64()

@@ -60,6 +60,11 @@ struct tmat_ctx {
   // small pinned staging area for scalars coming back from the device
   void* pinned = nullptr;
   size_t pinned_cap = 0;
+  // optional per-launch timing of the tensor-core convolution kernel (bench.py's roofline leg)
+  bool profiling = false;
+  struct ProfRec { cudaEvent_t a, b; double flops; };
+  std::vector<ProfRec> prof;
+  std::vector<cudaEvent_t> event_pool;
 };
 
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }

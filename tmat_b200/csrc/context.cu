@@ -60,6 +60,8 @@ extern "C" int tmat_ctx_destroy(tmat_ctx* ctx) {
   free_overflow(ctx);
   if (ctx->arena) cudaFree(ctx->arena);
   if (ctx->pinned) cudaFreeHost(ctx->pinned);
+  for (auto& r : ctx->prof) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+  for (auto e : ctx->event_pool) cudaEventDestroy(e);
   delete ctx;
   return TMAT_OK;
 }
@@ -131,5 +133,33 @@ int arena_reserve(tmat_ctx* ctx, size_t bytes) {
     return TMAT_ERR_NOMEM;
   }
   ctx->arena_cap = want;
+  return TMAT_OK;
+}
+
+extern "C" int tmat_ctx_profile_enable(tmat_ctx* ctx, int on) {
+  TMAT_REQUIRE(ctx, "tmat_ctx_profile_enable: ctx is NULL");
+  ctx->profiling = on != 0;
+  return TMAT_OK;
+}
+
+// out[0] = summed duration (ms) of the profiled tcgen05 convolution launches since the last collect,
+// out[1] = their count, out[2] = the FLOPs (2*M*N*K) they executed.  Synchronises the device.
+extern "C" int tmat_ctx_profile_collect(tmat_ctx* ctx, double* out3) {
+  TMAT_REQUIRE(ctx && out3, "tmat_ctx_profile_collect: NULL argument");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  CUDA_TRY(cudaDeviceSynchronize());
+  double ms = 0, fl = 0;
+  for (auto& r : ctx->prof) {
+    float t = 0;
+    CUDA_TRY(cudaEventElapsedTime(&t, r.a, r.b));
+    ms += t;
+    fl += r.flops;
+    ctx->event_pool.push_back(r.a);
+    ctx->event_pool.push_back(r.b);
+  }
+  out3[0] = ms;
+  out3[1] = (double)ctx->prof.size();
+  out3[2] = fl;
+  ctx->prof.clear();
   return TMAT_OK;
 }

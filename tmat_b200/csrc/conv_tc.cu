@@ -461,8 +461,21 @@ static int launch_tc(tmat_ctx* ctx, const CUtensorMap& a0, const CUtensorMap& a1
     configured = true;
   }
   int grid = std::min(p.total_tiles, ctx->sm_count);
+  tmat_ctx::ProfRec rec{nullptr, nullptr, 0.0};
+  if (ctx->profiling) {
+    for (cudaEvent_t* e : {&rec.a, &rec.b}) {
+      if (!ctx->event_pool.empty()) { *e = ctx->event_pool.back(); ctx->event_pool.pop_back(); }
+      else CUDA_TRY(cudaEventCreate(e));
+    }
+    rec.flops = 2.0 * p.e.B * p.e.H * p.e.W * (double)(p.tiles_n * BN) * (double)(p.nk * KSLAB);
+    CUDA_TRY(cudaEventRecord(rec.a, st));
+  }
   conv_tc_kernel<BN, STAGES><<<grid, TC_THREADS, L::BYTES, st>>>(a0, a1, b, p);
   KERNEL_CHECK(ctx);
+  if (ctx->profiling) {
+    CUDA_TRY(cudaEventRecord(rec.b, st));
+    ctx->prof.push_back(rec);
+  }
   return TMAT_OK;
 }
 
