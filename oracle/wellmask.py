@@ -30,7 +30,8 @@ def gaussian_kernel1d(sigma=1.0, truncate=4.0):
 def gaussian(image, sigma=1.0):
     image = np.asarray(image)
     if image.dtype in _INT_SCALE:
-        image = image.astype(np.float64) / _INT_SCALE[image.dtype]
+        # skimage.util.dtype._convert (0.22): unsigned ints -> np.multiply(image, 1. / imax, dtype=float64)
+        image = np.multiply(image, 1.0 / _INT_SCALE[image.dtype], dtype=np.float64)
     elif image.dtype == np.float16:
         image = image.astype(np.float32)
     elif image.dtype == bool:

@@ -1,0 +1,128 @@
+"""GPU: thresholds, Gaussian pre-filter, auto_threshold_well and the mask-cleanup stage through the
+C ABI vs the oracle and the golden fixtures.  Integer / mask results are bit-exact."""
+import numpy as np
+import pytest
+
+import helpers
+from oracle import morphology as om, wellmask as ow
+
+pytestmark = pytest.mark.gpu
+
+
+def _unpack(g, name):
+    shape = tuple(g[f"{name}_shape"])
+    return lambda a: np.unpackbits(a)[: shape[0] * shape[1]].reshape(shape).astype(bool)
+
+
+def test_filter_branch_seg_mask_golden(golden):
+    from tmat_b200 import transforms as T
+    g = golden("morphology")
+    for name in ("real", "synth"):
+        un = _unpack(g, name)
+        m = un(g[f"{name}_in"])
+        assert np.array_equal(T.filter_branch_seg_mask(m), un(g[f"{name}_filter_composition"])), name
+        assert np.array_equal(T.filter_branch_seg_mask(m, None, False),
+                              un(g[f"{name}_filter_nomedian_keepisolated_composition"])), name
+        assert np.array_equal(T.remove_small_islands(m.astype(np.uint8), 30, 40, 1, 2).astype(bool),
+                              un(g[f"{name}_islands_composition"])), name
+        assert np.array_equal(T.regionprops_image(m, "area").astype(np.float32), g[f"{name}_area_image_composition"])
+
+
+@pytest.mark.parametrize("h,w,seed", [(64, 64, 1), (97, 131, 2), (300, 340, 3), (33, 500, 4), (1, 40, 5), (40, 1, 6)])
+def test_morphology_primitives_vs_oracle(h, w, seed):
+    from tmat_b200 import transforms as T
+    m = helpers.synth_mask(h, w, seed, density=0.15)
+    assert np.array_equal(T.median_filter(m, T.disk(2)), om.median_bool(m, om.disk(2)))
+    for r in (1, 3, 5):
+        assert np.array_equal(T.binary_erosion(m, T.disk(r)), om.binary_erosion(m, om.disk(r))), r
+    for conn in (1, 2):
+        lab, n = T.measure_label(m, conn, return_num=True)
+        ref, nr = om.label(m, conn)
+        assert n == nr and np.array_equal(lab, ref), conn
+    sk, it = T.skeletonize(m, return_iterations=True)
+    assert np.array_equal(sk, om.skeletonize(m)) and it == om.skeletonize.last_iterations
+    for rem in (True, False):
+        for fp in ("disk2", None):
+            got = T.filter_branch_seg_mask(m, T.disk(2) if fp else None, rem)
+            assert np.array_equal(got, om.filter_branch_seg_mask(m, fp, rem)), (rem, fp)
+    u = m.astype(np.uint8)
+    if u.min() == 0 and u.max() == 1:
+        assert np.array_equal(T.remove_small_islands(u, 20, 25, 2, 1), om.remove_small_islands(u, 20, 25, 2, 1))
+    assert np.array_equal(T.regionprops_image(m, "area"), om.regionprops_image_area(m))
+
+
+def test_region_stats_vs_oracle():
+    import ctypes as C
+    import torch
+    from tmat_b200 import _ffi
+    m = helpers.synth_mask(200, 260, 8, density=0.2)
+    lab, n = om.label(m, 2)
+    ctx = _ffi.default_context()
+    d_lab = torch.from_numpy(lab).cuda()
+    area = np.zeros(n, np.int64)
+    hist = np.zeros((n, 50), np.int64)
+    _ffi.check(_ffi.lib().tmat_region_stats_dev(ctx.handle, _ffi.ptr(d_lab), 200, 260, n, _ffi.ptr(area), _ffi.ptr(hist), None))
+    assert np.array_equal(area, om.region_areas(lab, n))
+    assert np.array_equal(hist, om.perimeter_code_hist(lab, n))
+
+
+def test_edge_cases_empty_full_and_errors():
+    from tmat_b200 import transforms as T
+    z = np.zeros((50, 60), bool)
+    o = np.ones((50, 60), bool)
+    assert not T.filter_branch_seg_mask(z).any()
+    assert np.array_equal(T.filter_branch_seg_mask(o), om.filter_branch_seg_mask(o))
+    lab, n = T.measure_label(z, 2, return_num=True)
+    assert n == 0 and not lab.any()
+    assert T.measure_label(o, 1, return_num=True)[1] == 1
+    assert not T.skeletonize(z).any()
+    with pytest.raises(ValueError):
+        T.remove_small_islands(np.full((8, 8), 2, np.uint8))
+    with pytest.raises(ValueError):
+        T.remove_small_islands(np.ones((8, 8), np.uint8))     # the reference rejects an all-ones mask too
+
+
+@pytest.mark.parametrize("dtype,invert", [(np.uint16, False), (np.uint16, True), (np.uint8, False), (np.float32, True),
+                                          (np.float32, False)])
+def test_auto_threshold_well_vs_oracle(dtype, invert):
+    from tmat_b200 import well_mask_generation as W
+    img = helpers.synth_well(240, 310, 11, dtype, invert)
+    blur = W.gaussian(img, 1.0)
+    ref_blur = ow.gaussian(img, 1.0)
+    assert blur.dtype == ref_blur.dtype and np.array_equal(blur, ref_blur)
+    mask, info = W.auto_threshold_well(img, return_info=True)
+    ref, st = ow.auto_threshold_well(img, return_stages=True)
+    assert info["invert"] == st["invert"] and info["otsu"] == st["otsu"]
+    assert np.array_equal(mask, ref)
+
+
+def test_full_size_mask_path_properties():
+    """C3/C4 size (2048x2048): idempotence and agreement with the oracle on a crop-independent statistic."""
+    from tmat_b200 import transforms as T
+    m = helpers.synth_mask(2048, 2048, 21, density=0.05)
+    out = T.filter_branch_seg_mask(m)
+    assert out.shape == m.shape and not (out & ~om.median_bool(m, om.disk(2))).any()
+    again = T.filter_branch_seg_mask(out, None, True)
+    assert np.array_equal(again, out)            # surviving components all have forks and low circularity
+    lab, n = T.measure_label(out, 2, return_num=True)
+    ref, nr = om.label(out, 2)
+    assert n == nr and np.array_equal(lab, ref)
+
+
+def test_threshold_and_apply_mask():
+    import torch
+    from tmat_b200 import _ffi, preprocessing as P
+    ctx = _ffi.default_context()
+    x = np.random.default_rng(0).random(10007)
+    x[:3] = 0.5
+    d = torch.from_numpy(x).cuda()
+    m = torch.empty(x.size, dtype=torch.uint8, device="cuda")
+    _ffi.check(_ffi.lib().tmat_threshold_gt_f64_dev(ctx.handle, _ffi.ptr(d), x.size, 0.5, _ffi.ptr(m), None))
+    torch.cuda.synchronize()
+    assert np.array_equal(m.cpu().numpy().astype(bool), x > 0.5)
+    img = np.random.default_rng(1).random((33, 47)).astype(np.float32)
+    mk = (np.random.default_rng(2).random((33, 47)) > 0.4).astype(np.uint8)
+    ref = img.copy()
+    ref[mk == 0] = 0
+    assert np.array_equal(P.apply_mask(img, mk), ref)
+    assert np.array_equal(P.bin_thresh(img, 255, 0.5), np.where(img > 0.5, 255, 0))

@@ -84,6 +84,9 @@ static inline int arena_get(tmat_ctx* ctx, size_t count, T** out) {
   return r;
 }
 
+// numpy's pairwise summation of a contiguous float64 vector (np.add.reduce), defined in stp.cu
+double np_pairwise_sum(const double* a, int64_t n);
+
 static inline cudaStream_t as_stream(void* s) { return (cudaStream_t)s; }
 
 static inline size_t dtype_size(int dtype) {

@@ -1,0 +1,367 @@
+// Stage 3: thresholds and the Gaussian pre-filter.
+// Reference: scripts/compute_branches.py:334 (pred > 0.5), fl_tissue_model_tools/preprocessing.py:13-23
+// (apply_mask), fl_tissue_model_tools/well_mask_generation.py:236-277 (auto_threshold_well) and the
+// scikit-image 0.22 calls it makes: filters.gaussian (= scipy.ndimage.gaussian_filter, mode 'nearest',
+// truncate 4), exposure.rescale_intensity, filters.threshold_otsu, morphology.binary_erosion(disk(5)).
+// Floating-point steps that feed an integer decision are evaluated in the reference's precision
+// with the reference's operation order and no FMA contraction, so the uint8 image is bit-identical.
+#include "common.cuh"
+#include <math.h>
+#include <algorithm>
+
+int erode_disk(tmat_ctx* ctx, const uint8_t* in, int H, int W, int r, int border_value, uint8_t* out, cudaStream_t st);
+
+namespace {
+
+__global__ void __launch_bounds__(256) threshold_gt_f64(const double* __restrict__ x, int64_t n, double thr,
+                                                        uint8_t* __restrict__ mask) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) mask[i] = x[i] > thr ? 1 : 0;
+}
+
+__global__ void __launch_bounds__(256) apply_mask_f32(const float* __restrict__ img, const uint8_t* __restrict__ m,
+                                                      int64_t n, float* __restrict__ out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = m[i] ? img[i] : 0.f;
+}
+
+// ---- separable Gaussian, scipy.ndimage.correlate1d semantics -----------------------------------
+// symmetric kernel:  tmp = x[l]*w[0];  for j = -R..-1: tmp += (x[l+j] + x[l-j]) * w[j]   (double, no FMA)
+// mode 'nearest' = index clamp.  Pass 1 filters along axis 0 (rows), pass 2 along axis 1, as
+// gaussian_filter does; a float32 image is rounded to float32 between the passes (scipy writes
+// the intermediate into the float32 output array).
+constexpr int GAUSS_MAX_R = 32;
+struct GaussW { double w[GAUSS_MAX_R + 1]; int R; };   // w[k] = weight at distance k
+
+template <typename TIn>
+__device__ __forceinline__ double load_as_f64(const TIn* p, int64_t i, double int_scale);
+template <> __device__ __forceinline__ double load_as_f64<uint8_t>(const uint8_t* p, int64_t i, double s) { return __dmul_rn((double)p[i], s); }
+template <> __device__ __forceinline__ double load_as_f64<uint16_t>(const uint16_t* p, int64_t i, double s) { return __dmul_rn((double)p[i], s); }
+template <> __device__ __forceinline__ double load_as_f64<float>(const float* p, int64_t i, double) { return (double)p[i]; }
+template <> __device__ __forceinline__ double load_as_f64<double>(const double* p, int64_t i, double) { return p[i]; }
+
+// vertical pass (axis 0): thread per pixel, coalesced along x
+template <typename TIn, typename TOut>
+__global__ void __launch_bounds__(256) gauss_axis0(const TIn* __restrict__ in, int H, int W, GaussW g, double int_scale,
+                                                   TOut* __restrict__ out) {
+  int x = blockIdx.x * blockDim.x + threadIdx.x;
+  int y = blockIdx.y;
+  if (x >= W) return;
+  double tmp = __dmul_rn(load_as_f64<TIn>(in, (int64_t)y * W + x, int_scale), g.w[0]);
+  for (int j = g.R; j >= 1; --j) {
+    int ya = max(y - j, 0), yb = min(y + j, H - 1);
+    double a = load_as_f64<TIn>(in, (int64_t)ya * W + x, int_scale);
+    double b = load_as_f64<TIn>(in, (int64_t)yb * W + x, int_scale);
+    tmp = __dadd_rn(tmp, __dmul_rn(__dadd_rn(a, b), g.w[j]));
+  }
+  out[(int64_t)y * W + x] = (TOut)tmp;
+}
+
+// horizontal pass (axis 1): one CTA per row segment, row staged in shared memory with its halo
+template <typename T>
+__global__ void __launch_bounds__(256) gauss_axis1(const T* __restrict__ in, int H, int W, GaussW g, T* __restrict__ out) {
+  __shared__ double s[256 + 2 * GAUSS_MAX_R];
+  int y = blockIdx.y;
+  int x0 = blockIdx.x * 256;
+  const T* row = in + (int64_t)y * W;
+  for (int i = threadIdx.x; i < 256 + 2 * g.R; i += 256) {
+    int xx = min(max(x0 - g.R + i, 0), W - 1);
+    s[i] = (double)row[xx];
+  }
+  __syncthreads();
+  int x = x0 + threadIdx.x;
+  if (x >= W) return;
+  int c = threadIdx.x + g.R;
+  double tmp = __dmul_rn(s[c], g.w[0]);
+  for (int j = g.R; j >= 1; --j) tmp = __dadd_rn(tmp, __dmul_rn(__dadd_rn(s[c - j], s[c + j]), g.w[j]));
+  out[(int64_t)y * W + x] = (T)tmp;
+}
+
+// ---- min / max of a float image (exact), via order-preserving integer keys -------------------------
+__device__ __forceinline__ unsigned long long f64_key(double d) {
+  unsigned long long b = (unsigned long long)__double_as_longlong(d);
+  return (b >> 63) ? ~b : (b | 0x8000000000000000ull);
+}
+__device__ __forceinline__ double f64_unkey(unsigned long long k) {
+  return __longlong_as_double((long long)((k >> 63) ? (k & 0x7fffffffffffffffull) : ~k));
+}
+__global__ void minmax64_init(unsigned long long* k) { k[0] = ~0ull; k[1] = 0ull; }
+template <typename T>
+__global__ void __launch_bounds__(256) minmax64(const T* __restrict__ x, int64_t n, unsigned long long* k) {
+  unsigned long long lo = ~0ull, hi = 0ull;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    unsigned long long e = f64_key((double)x[i]);
+    lo = min(lo, e);
+    hi = max(hi, e);
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+    hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+  }
+  if ((threadIdx.x & 31) == 0) { atomicMin(k, lo); atomicMax(k + 1, hi); }
+}
+
+// rescale_intensity(x, out_range=(0,255)).astype(uint8)  +  the 4 corner histograms + global histogram
+//   y = (x - lo) / (hi - lo);  y = y * 255 + 0;  uint8(trunc(y))      in T's precision (float64 / float32)
+template <typename T>
+__global__ void __launch_bounds__(256) rescale_u8_hist(const T* __restrict__ x, int H, int W,
+                                                       const unsigned long long* __restrict__ keys, int xs, int xe,
+                                                       int ys, int ye, uint8_t* __restrict__ u8,
+                                                       unsigned int* __restrict__ hist /*[5][256]*/) {
+  __shared__ unsigned int sh[5 * 256];
+  for (int i = threadIdx.x; i < 5 * 256; i += blockDim.x) sh[i] = 0;
+  __syncthreads();
+  const T lo = (T)f64_unkey(keys[0]), hi = (T)f64_unkey(keys[1]);
+  const bool flat = (lo == hi);
+  int64_t n = (int64_t)H * W;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    T v = x[i];
+    T y;
+    if (sizeof(T) == 8) {
+      double d = (double)v;
+      if (!flat) d = __ddiv_rn(__dsub_rn(d, (double)lo), __dsub_rn((double)hi, (double)lo));
+      y = (T)__dadd_rn(__dmul_rn(d, 255.0), 0.0);
+    } else {
+      float f = (float)v;
+      if (!flat) f = __fdiv_rn(__fsub_rn(f, (float)lo), __fsub_rn((float)hi, (float)lo));
+      y = (T)__fadd_rn(__fmul_rn(f, 255.0f), 0.0f);
+    }
+    uint8_t q = (uint8_t)(long long)y;
+    u8[i] = q;
+    int r = (int)(i / W), c = (int)(i - (int64_t)r * W);
+    atomicAdd(&sh[4 * 256 + q], 1u);
+    if (r < xs && c < ys) atomicAdd(&sh[0 * 256 + q], 1u);
+    if (r < xs && c >= ye) atomicAdd(&sh[1 * 256 + q], 1u);
+    if (r >= xe && c < ys) atomicAdd(&sh[2 * 256 + q], 1u);
+    if (r >= xe && c >= ye) atomicAdd(&sh[3 * 256 + q], 1u);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 5 * 256; i += blockDim.x)
+    if (sh[i]) atomicAdd(&hist[i], sh[i]);
+}
+
+__global__ void __launch_bounds__(256) threshold_ge_u8(const uint8_t* __restrict__ u8, int64_t n, int invert, int thr,
+                                                       uint8_t* __restrict__ mask) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int v = u8[i];
+  if (invert) v = 255 - v;
+  mask[i] = v >= thr ? 1 : 0;
+}
+
+}  // namespace
+
+// ---- host side --------------------------------------------------------------------------------
+static int make_gauss(double sigma, GaussW* g) {
+  TMAT_REQUIRE(sigma > 0, "gaussian: sigma must be positive");
+  int R = (int)(4.0 * sigma + 0.5);   // truncate = 4.0
+  TMAT_REQUIRE(R >= 1 && R <= GAUSS_MAX_R, "gaussian: radius %d outside [1,%d]", R, GAUSS_MAX_R);
+  // scipy.ndimage._filters._gaussian_kernel1d: exp(-0.5 / sigma^2 * x^2) / sum  (numpy pairwise sum)
+  std::vector<double> phi(2 * R + 1);
+  double s2 = sigma * sigma;
+  for (int x = -R; x <= R; ++x) phi[x + R] = exp(-0.5 / s2 * (double)(x * x));
+  double sum = np_pairwise_sum(phi.data(), 2 * R + 1);
+  g->R = R;
+  for (int k = 0; k <= R; ++k) g->w[k] = phi[R + k] / sum;
+  return TMAT_OK;
+}
+
+// blur: float64 (H,W) for integer input, float32 for float32 input
+static int gaussian_impl(tmat_ctx* ctx, const void* img, int dtype, int H, int W, double sigma, void* out,
+                         cudaStream_t st) {
+  GaussW g;
+  TMAT_TRY(make_gauss(sigma, &g));
+  dim3 grid0(cdiv(W, 256), H), grid1(cdiv(W, 256), H);
+  size_t n = (size_t)H * W;
+  if (dtype == TMAT_U8 || dtype == TMAT_U16) {
+    double* tmp;
+    TMAT_TRY(arena_get(ctx, n, &tmp));
+    // skimage img_as_float: np.multiply(image, 1. / imax, dtype=float64)
+    if (dtype == TMAT_U8) gauss_axis0<uint8_t, double><<<grid0, 256, 0, st>>>((const uint8_t*)img, H, W, g, 1.0 / 255.0, tmp);
+    else gauss_axis0<uint16_t, double><<<grid0, 256, 0, st>>>((const uint16_t*)img, H, W, g, 1.0 / 65535.0, tmp);
+    KERNEL_CHECK(ctx);
+    gauss_axis1<double><<<grid1, 256, 0, st>>>(tmp, H, W, g, (double*)out);
+    KERNEL_CHECK(ctx);
+  } else if (dtype == TMAT_F32) {
+    float* tmp;
+    TMAT_TRY(arena_get(ctx, n, &tmp));
+    gauss_axis0<float, float><<<grid0, 256, 0, st>>>((const float*)img, H, W, g, 1.0, tmp);
+    KERNEL_CHECK(ctx);
+    gauss_axis1<float><<<grid1, 256, 0, st>>>(tmp, H, W, g, (float*)out);
+    KERNEL_CHECK(ctx);
+  } else if (dtype == TMAT_F64) {
+    double* tmp;
+    TMAT_TRY(arena_get(ctx, n, &tmp));
+    gauss_axis0<double, double><<<grid0, 256, 0, st>>>((const double*)img, H, W, g, 1.0, tmp);
+    KERNEL_CHECK(ctx);
+    gauss_axis1<double><<<grid1, 256, 0, st>>>(tmp, H, W, g, (double*)out);
+    KERNEL_CHECK(ctx);
+  } else {
+    tmat_set_error("gaussian: unsupported dtype %d", dtype);
+    return TMAT_ERR_UNSUPPORTED;
+  }
+  return TMAT_OK;
+}
+
+extern "C" int tmat_threshold_gt_f64_dev(tmat_ctx* ctx, const double* x_dev, int64_t n, double thr, uint8_t* mask_dev,
+                                         void* stream) {
+  TMAT_REQUIRE(ctx && x_dev && mask_dev && n >= 0, "tmat_threshold_gt_f64: bad argument");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  if (n == 0) return TMAT_OK;
+  threshold_gt_f64<<<(unsigned)cdiv64(n, 256), 256, 0, as_stream(stream)>>>(x_dev, n, thr, mask_dev);
+  KERNEL_CHECK(ctx);
+  return TMAT_OK;
+}
+
+extern "C" int tmat_apply_mask_f32_dev(tmat_ctx* ctx, const float* img_dev, const uint8_t* mask_dev, int64_t n,
+                                       float* out_dev, void* stream) {
+  TMAT_REQUIRE(ctx && img_dev && mask_dev && out_dev && n >= 0, "tmat_apply_mask_f32: bad argument");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  if (n == 0) return TMAT_OK;
+  apply_mask_f32<<<(unsigned)cdiv64(n, 256), 256, 0, as_stream(stream)>>>(img_dev, mask_dev, n, out_dev);
+  KERNEL_CHECK(ctx);
+  return TMAT_OK;
+}
+
+extern "C" int tmat_gaussian_dev(tmat_ctx* ctx, const void* img_dev, int dtype, int H, int W, double sigma,
+                                 void* out_dev, void* stream) {
+  TMAT_REQUIRE(ctx && img_dev && out_dev && H >= 1 && W >= 1, "tmat_gaussian: bad argument");
+  TMAT_TRY(arena_reset(ctx));
+  return gaussian_impl(ctx, img_dev, dtype, H, W, sigma, out_dev, as_stream(stream));
+}
+
+extern "C" int tmat_gaussian_host(tmat_ctx* ctx, const void* img_host, int dtype, int H, int W, double sigma,
+                                  void* out_host) {
+  TMAT_REQUIRE(ctx && img_host && out_host && H >= 1 && W >= 1, "tmat_gaussian_host: bad argument");
+  TMAT_REQUIRE(dtype_size(dtype) > 0, "tmat_gaussian_host: bad dtype %d", dtype);
+  TMAT_TRY(arena_reset(ctx));
+  size_t n = (size_t)H * W, es = dtype_size(dtype), os = (dtype == TMAT_F32) ? 4 : 8;
+  void *d_in, *d_out;
+  TMAT_TRY(arena_alloc(ctx, n * es, &d_in));
+  TMAT_TRY(arena_alloc(ctx, n * os, &d_out));
+  CUDA_TRY(cudaMemcpyAsync(d_in, img_host, n * es, cudaMemcpyHostToDevice, 0));
+  TMAT_TRY(gaussian_impl(ctx, d_in, dtype, H, W, sigma, d_out, 0));
+  CUDA_TRY(cudaMemcpyAsync(out_host, d_out, n * os, cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaStreamSynchronize(0));
+  return TMAT_OK;
+}
+
+// ---- auto_threshold_well (well_mask_generation.py:236-277) ------------------------------------------
+// np.median of a uint8 block from its histogram
+static double hist_median(const unsigned int* h) {
+  uint64_t n = 0;
+  for (int i = 0; i < 256; ++i) n += h[i];
+  if (n == 0) return NAN;
+  uint64_t k0 = (n - 1) / 2, k1 = n / 2, acc = 0;
+  int v0 = -1, v1 = -1;
+  for (int i = 0; i < 256; ++i) {
+    acc += h[i];
+    if (v0 < 0 && acc > k0) v0 = i;
+    if (v1 < 0 && acc > k1) { v1 = i; break; }
+  }
+  return ((double)v0 + (double)v1) / 2.0;
+}
+
+// skimage.filters.threshold_otsu on a uint8 image given its 256-bin histogram (numpy dtype semantics:
+// float32 counts and class weights, float64 class means)
+static int otsu_from_hist(const uint64_t* h) {
+  int lo = 0, hi = 255;
+  while (lo < 256 && h[lo] == 0) ++lo;
+  while (hi >= 0 && h[hi] == 0) --hi;
+  if (lo >= hi) return lo > 255 ? 0 : lo;
+  int n = hi - lo + 1;
+  std::vector<float> counts(n), w1(n), w2(n);
+  std::vector<double> cc(n), m1(n), m2(n);
+  for (int i = 0; i < n; ++i) { counts[i] = (float)h[lo + i]; cc[i] = (double)counts[i] * (double)(lo + i); }
+  float a = 0.f;
+  for (int i = 0; i < n; ++i) { a += counts[i]; w1[i] = a; }
+  a = 0.f;
+  for (int i = n - 1; i >= 0; --i) { a += counts[i]; w2[i] = a; }
+  double s = 0.0;
+  for (int i = 0; i < n; ++i) { s += cc[i]; m1[i] = s / (double)w1[i]; }
+  s = 0.0;
+  for (int i = n - 1; i >= 0; --i) { s += cc[i]; m2[i] = s / (double)w2[i]; }
+  int best = 0;
+  double bestv = -1.0;
+  for (int i = 0; i + 1 < n; ++i) {
+    float ww = w1[i] * w2[i + 1];
+    double d = m1[i] - m2[i + 1];
+    double v = (double)ww * (d * d);
+    if (v > bestv) { bestv = v; best = i; }
+  }
+  return lo + best;
+}
+
+static int auto_threshold_impl(tmat_ctx* ctx, const void* img, int dtype, int H, int W, uint8_t* mask, int* info,
+                               cudaStream_t st) {
+  TMAT_REQUIRE(dtype == TMAT_U8 || dtype == TMAT_U16 || dtype == TMAT_F32 || dtype == TMAT_F64,
+               "auto_threshold_well: unsupported dtype %d", dtype);
+  TMAT_REQUIRE(H >= 20 && W >= 20, "auto_threshold_well: image %dx%d too small for the 5%% corner blocks", H, W);
+  size_t n = (size_t)H * W;
+  const bool f32 = (dtype == TMAT_F32);
+  void* blur;
+  TMAT_TRY(arena_alloc(ctx, n * (f32 ? 4 : 8), &blur));
+  TMAT_TRY(gaussian_impl(ctx, img, dtype, H, W, 1.0, blur, st));
+  unsigned long long* keys;
+  unsigned int* hist;
+  uint8_t *u8, *thr_mask;
+  TMAT_TRY(arena_get(ctx, 2, &keys));
+  TMAT_TRY(arena_get(ctx, 5 * 256, &hist));
+  TMAT_TRY(arena_get(ctx, n, &u8));
+  TMAT_TRY(arena_get(ctx, n, &thr_mask));
+  minmax64_init<<<1, 1, 0, st>>>(keys);
+  KERNEL_CHECK(ctx);
+  int blocks = (int)std::min<int64_t>(cdiv64((int64_t)n, 256), (int64_t)ctx->sm_count * 8);
+  if (f32) minmax64<float><<<blocks, 256, 0, st>>>((const float*)blur, (int64_t)n, keys);
+  else minmax64<double><<<blocks, 256, 0, st>>>((const double*)blur, (int64_t)n, keys);
+  KERNEL_CHECK(ctx);
+  CUDA_TRY(cudaMemsetAsync(hist, 0, 5 * 256 * sizeof(unsigned int), st));
+  int xs = (int)(H * 0.05), xe = (int)(H * 0.95), ys = (int)(W * 0.05), ye = (int)(W * 0.95);
+  if (f32) rescale_u8_hist<float><<<blocks, 256, 0, st>>>((const float*)blur, H, W, keys, xs, xe, ys, ye, u8, hist);
+  else rescale_u8_hist<double><<<blocks, 256, 0, st>>>((const double*)blur, H, W, keys, xs, xe, ys, ye, u8, hist);
+  KERNEL_CHECK(ctx);
+  unsigned int* hh = (unsigned int*)ctx->pinned;
+  CUDA_TRY(cudaMemcpyAsync(hh, hist, 5 * 256 * sizeof(unsigned int), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  // corner medians and the invert decision (:248-270)
+  double meds[4];
+  for (int c = 0; c < 4; ++c) meds[c] = hist_median(hh + c * 256);
+  int vmin = 0, vmax = 255;
+  while (vmin < 255 && hh[4 * 256 + vmin] == 0) ++vmin;
+  while (vmax > 0 && hh[4 * 256 + vmax] == 0) --vmax;
+  double mmin = std::min(std::min(meds[0], meds[1]), std::min(meds[2], meds[3]));
+  double mmax = std::max(std::max(meds[0], meds[1]), std::max(meds[2], meds[3]));
+  int invert = fabs((double)vmin - mmin) > fabs((double)vmax - mmax) ? 1 : 0;
+  uint64_t h64[256];
+  for (int i = 0; i < 256; ++i) h64[i] = hh[4 * 256 + (invert ? 255 - i : i)];
+  int thr = otsu_from_hist(h64);
+  threshold_ge_u8<<<(unsigned)cdiv64((int64_t)n, 256), 256, 0, st>>>(u8, (int64_t)n, invert, thr, thr_mask);
+  KERNEL_CHECK(ctx);
+  TMAT_TRY(erode_disk(ctx, thr_mask, H, W, 5, 1, mask, st));
+  if (info) { info[0] = invert; info[1] = thr; info[2] = invert ? 255 - vmax : vmin; info[3] = invert ? 255 - vmin : vmax; }
+  return TMAT_OK;
+}
+
+extern "C" int tmat_auto_threshold_well_dev(tmat_ctx* ctx, const void* img_dev, int dtype, int H, int W,
+                                            uint8_t* mask_dev, int* info, void* stream) {
+  TMAT_REQUIRE(ctx && img_dev && mask_dev, "tmat_auto_threshold_well: NULL argument");
+  TMAT_TRY(arena_reset(ctx));
+  return auto_threshold_impl(ctx, img_dev, dtype, H, W, mask_dev, info, as_stream(stream));
+}
+
+extern "C" int tmat_auto_threshold_well_host(tmat_ctx* ctx, const void* img_host, int dtype, int H, int W,
+                                             uint8_t* mask_host, int* info) {
+  TMAT_REQUIRE(ctx && img_host && mask_host, "tmat_auto_threshold_well_host: NULL argument");
+  TMAT_REQUIRE(dtype_size(dtype) > 0, "tmat_auto_threshold_well_host: bad dtype");
+  TMAT_TRY(arena_reset(ctx));
+  size_t n = (size_t)H * W, es = dtype_size(dtype);
+  void* d_in;
+  uint8_t* d_mask;
+  TMAT_TRY(arena_alloc(ctx, n * es, &d_in));
+  TMAT_TRY(arena_get(ctx, n, &d_mask));
+  CUDA_TRY(cudaMemcpyAsync(d_in, img_host, n * es, cudaMemcpyHostToDevice, 0));
+  TMAT_TRY(auto_threshold_impl(ctx, d_in, dtype, H, W, d_mask, info, 0));
+  CUDA_TRY(cudaMemcpyAsync(mask_host, d_mask, n, cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaStreamSynchronize(0));
+  return TMAT_OK;
+}

@@ -1,0 +1,640 @@
+// Stage 4: binary morphology and connected-component cleanup.
+// Reference: fl_tissue_model_tools/transforms.py:170-206 (remove_small_islands), :291-303
+// (regionprops_image), :306-361 (filter_branch_seg_mask), well_mask_generation.py:275 (binary_erosion) and
+// the scikit-image 0.22 primitives they call (filters.median on a bool image, measure.label,
+// regionprops area / perimeter, morphology.skeletonize, remove_small_objects, disk).
+// All integer work: bit-exact.  Masks are uint8 images; any non-zero value is foreground.
+#include "common.cuh"
+#include <math.h>
+#include <algorithm>
+
+namespace {
+
+// ---- median with the disk(2) footprint on a boolean image: >= 7 of the 13 pixels set -----------------
+// (skimage.filters.median -> scipy.ndimage.median_filter, mode 'nearest' = index clamp)
+__global__ void __launch_bounds__(256) median_disk2_kernel(const uint8_t* __restrict__ in, int H, int W,
+                                                           uint8_t* __restrict__ out) {
+  int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  if (x >= W) return;
+  int cnt = 0;
+#pragma unroll
+  for (int dy = -2; dy <= 2; ++dy) {
+    int hw = (dy == 0) ? 2 : ((dy == -1 || dy == 1) ? 1 : 0);
+    int yy = min(max(y + dy, 0), H - 1);
+    for (int dx = -hw; dx <= hw; ++dx) {
+      int xx = min(max(x + dx, 0), W - 1);
+      cnt += in[(int64_t)yy * W + xx] != 0;
+    }
+  }
+  out[(int64_t)y * W + x] = cnt >= 7;
+}
+
+// ---- erosion with disk(r): all footprint pixels set; outside the image counts as border_value --------
+constexpr int ER_T = 32, ER_MAX_R = 8;
+__global__ void __launch_bounds__(ER_T * 8) erode_disk_kernel(const uint8_t* __restrict__ in, int H, int W, int r,
+                                                             int border_value, uint8_t* __restrict__ out) {
+  __shared__ uint8_t s[ER_T + 2 * ER_MAX_R][ER_T + 2 * ER_MAX_R + 4];
+  const int x0 = blockIdx.x * ER_T, y0 = blockIdx.y * ER_T;
+  const int span = ER_T + 2 * r;
+  for (int i = threadIdx.y * ER_T + threadIdx.x; i < span * span; i += ER_T * 8) {
+    int ry = i / span, rx = i - ry * span;
+    int yy = y0 - r + ry, xx = x0 - r + rx;
+    s[ry][rx] = (yy < 0 || yy >= H || xx < 0 || xx >= W) ? (uint8_t)(border_value != 0) : (uint8_t)(in[(int64_t)yy * W + xx] != 0);
+  }
+  __syncthreads();
+  for (int ty = threadIdx.y; ty < ER_T; ty += 8) {
+    int x = x0 + threadIdx.x, y = y0 + ty;
+    if (x >= W || y >= H) continue;
+    int ok = 1;
+    for (int dy = -r; dy <= r && ok; ++dy) {
+      int hw = (int)floorf(sqrtf((float)(r * r - dy * dy)) + 1e-4f);
+      for (int dx = -hw; dx <= hw; ++dx) ok &= s[ty + r + dy][threadIdx.x + r + dx];
+    }
+    out[(int64_t)y * W + x] = (uint8_t)ok;
+  }
+}
+
+// ---- connected components: union-find on pixel indices; the root of a component is its first
+// pixel in raster order (links always point from the larger root to the smaller) ------------------------
+__device__ __forceinline__ int uf_find(int* parent, int i) {
+  int p = parent[i];
+  while (p != i) { i = p; p = parent[i]; }
+  return i;
+}
+__device__ __forceinline__ void uf_union(int* parent, int a, int b) {
+  while (true) {
+    a = uf_find(parent, a);
+    b = uf_find(parent, b);
+    if (a == b) return;
+    if (a < b) { int t = a; a = b; b = t; }
+    int old = atomicMin(&parent[a], b);
+    if (old == a) return;
+    a = old;
+  }
+}
+
+__global__ void __launch_bounds__(256) ccl_init(const uint8_t* __restrict__ m, int64_t n, int fg_is_zero,
+                                                int* __restrict__ parent) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  bool fg = fg_is_zero ? (m[i] == 0) : (m[i] != 0);
+  parent[i] = fg ? (int)i : -1;
+}
+
+__global__ void __launch_bounds__(256) ccl_merge(int* __restrict__ parent, int H, int W, int conn8) {
+  int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  if (x >= W) return;
+  int i = y * W + x;
+  if (parent[i] < 0) return;
+  if (x > 0 && parent[i - 1] >= 0) uf_union(parent, i, i - 1);
+  if (y > 0) {
+    if (parent[i - W] >= 0) uf_union(parent, i, i - W);
+    if (conn8) {
+      if (x > 0 && parent[i - W - 1] >= 0) uf_union(parent, i, i - W - 1);
+      if (x + 1 < W && parent[i - W + 1] >= 0) uf_union(parent, i, i - W + 1);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) ccl_flatten(int* __restrict__ parent, int64_t n) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n || parent[i] < 0) return;
+  parent[i] = uf_find(parent, (int)i);
+}
+
+// raster-order renumbering: rank of each root among the roots (3-kernel scan over 1024-pixel blocks)
+constexpr int SCAN_BLOCK = 1024;
+__global__ void __launch_bounds__(256) roots_count(const int* __restrict__ parent, int64_t n, int* __restrict__ bsum) {
+  __shared__ int ws[8];
+  int64_t base = (int64_t)blockIdx.x * SCAN_BLOCK;
+  int c = 0;
+  for (int k = threadIdx.x; k < SCAN_BLOCK; k += 256) {
+    int64_t i = base + k;
+    c += (i < n && parent[i] == (int)i);
+  }
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = c;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int t = 0;
+    for (int w = 0; w < 8; ++w) t += ws[w];
+    bsum[blockIdx.x] = t;
+  }
+}
+// single block: exclusive scan of bsum[nb] in place; total -> total_out
+__global__ void __launch_bounds__(1024) scan_block_sums(int* __restrict__ bsum, int nb, int* __restrict__ total_out) {
+  __shared__ int s[1024];
+  __shared__ int carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (int base = 0; base < nb; base += 1024) {
+    int i = base + threadIdx.x;
+    int v = (i < nb) ? bsum[i] : 0;
+    s[threadIdx.x] = v;
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1) {
+      int t = (threadIdx.x >= o) ? s[threadIdx.x - o] : 0;
+      __syncthreads();
+      s[threadIdx.x] += t;
+      __syncthreads();
+    }
+    if (i < nb) bsum[i] = carry + s[threadIdx.x] - v;
+    __syncthreads();
+    if (threadIdx.x == 0) carry += s[1023];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *total_out = carry;
+}
+// rank[root] = 1-based raster-order label, written at the root's own position
+__global__ void __launch_bounds__(256) roots_rank(const int* __restrict__ parent, int64_t n, const int* __restrict__ boff,
+                                                  int* __restrict__ rank) {
+  // one warp-serial pass per 1024 block: 256 threads x 4 consecutive pixels, block-level exclusive scan
+  __shared__ int ws[8];
+  int64_t base = (int64_t)blockIdx.x * SCAN_BLOCK + threadIdx.x * 4;
+  int f[4], c = 0;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) { int64_t i = base + k; f[k] = (i < n && parent[i] == (int)i); c += f[k]; }
+  int incl = c;
+  for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(0xffffffffu, incl, o); if ((threadIdx.x & 31) >= o) incl += t; }
+  if ((threadIdx.x & 31) == 31) ws[threadIdx.x >> 5] = incl;
+  __syncthreads();
+  int woff = 0;
+  for (int w = 0; w < (threadIdx.x >> 5); ++w) woff += ws[w];
+  int run = boff[blockIdx.x] + woff + incl - c;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) { int64_t i = base + k; if (f[k]) rank[i] = ++run; }
+}
+__global__ void __launch_bounds__(256) labels_from_rank(const int* __restrict__ parent, const int* __restrict__ rank,
+                                                        int64_t n, int32_t* __restrict__ labels) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int p = parent[i];
+  labels[i] = p < 0 ? 0 : rank[p];
+}
+
+// ---- region statistics: area and skimage's perimeter border-code histogram ---------------------------
+// border = fg with a 4-neighbour that is bg (outside = bg); code = sum over the 3x3 neighbourhood of
+// border * [[10,2,10],[2,1,2],[10,2,10]]  (skimage.measure.perimeter, neighbourhood 4)
+__global__ void __launch_bounds__(256) border_kernel(const int32_t* __restrict__ lab, int H, int W,
+                                                     uint8_t* __restrict__ border) {
+  int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  if (x >= W) return;
+  int64_t i = (int64_t)y * W + x;
+  bool fg = lab[i] > 0;
+  bool interior = fg && y > 0 && y + 1 < H && x > 0 && x + 1 < W && lab[i - W] > 0 && lab[i + W] > 0 &&
+                  lab[i - 1] > 0 && lab[i + 1] > 0;
+  border[i] = fg && !interior;
+}
+__global__ void __launch_bounds__(256) region_stats_kernel(const int32_t* __restrict__ lab, const uint8_t* __restrict__ border,
+                                                           int H, int W, unsigned int* __restrict__ area,
+                                                           unsigned int* __restrict__ hist /*[n][50]*/) {
+  int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  if (x >= W) return;
+  int64_t i = (int64_t)y * W + x;
+  int l = lab[i];
+  if (l <= 0) return;
+  atomicAdd(&area[l - 1], 1u);
+  if (!border[i]) return;
+  int code = 0;
+#pragma unroll
+  for (int dy = -1; dy <= 1; ++dy)
+#pragma unroll
+    for (int dx = -1; dx <= 1; ++dx) {
+      int yy = y + dy, xx = x + dx;
+      if (yy < 0 || yy >= H || xx < 0 || xx >= W) continue;
+      int wgt = (dy == 0 && dx == 0) ? 1 : ((dy == 0 || dx == 0) ? 2 : 10);
+      code += border[(int64_t)yy * W + xx] ? wgt : 0;
+    }
+  atomicAdd(&hist[(int64_t)(l - 1) * 50 + code], 1u);
+}
+// circularity 4*pi*area / (perimeter^2 + 1e-7) > 0.8  (transforms.py:326-329, :346), per label
+__global__ void __launch_bounds__(256) circ_flag_kernel(const unsigned int* __restrict__ area,
+                                                        const unsigned int* __restrict__ hist, int n,
+                                                        uint8_t* __restrict__ round_flag /*[n+1]*/) {
+  int l = blockIdx.x * blockDim.x + threadIdx.x;
+  if (l >= n) return;
+  const double w1 = 1.0, w2 = 1.4142135623730951, w3 = (1.0 + 1.4142135623730951) / 2.0;
+  const unsigned int* h = hist + (int64_t)l * 50;
+  double perim = 0.0;
+  for (int c = 0; c < 50; ++c) {
+    double w = (c == 5 || c == 7 || c == 15 || c == 17 || c == 25 || c == 27) ? w1
+             : ((c == 21 || c == 33) ? w2 : ((c == 13 || c == 23) ? w3 : 0.0));
+    perim = __dadd_rn(perim, __dmul_rn((double)h[c], w));
+  }
+  double circ = __ddiv_rn(__dmul_rn(__dmul_rn(4.0, 3.141592653589793), (double)area[l]),
+                          __dadd_rn(__dmul_rn(perim, perim), 1e-7));
+  round_flag[l + 1] = circ > 0.8;
+}
+
+// ---- Zhang-Suen thinning (skimage.morphology.skeletonize, 2-D) -----------------------------------------
+__constant__ uint8_t c_zs_lut[256];
+__device__ __forceinline__ int nb_code(const uint8_t* __restrict__ m, int H, int W, int y, int x) {
+  auto at = [&](int yy, int xx) -> int { return (yy >= 0 && yy < H && xx >= 0 && xx < W) ? (m[(int64_t)yy * W + xx] != 0) : 0; };
+  return at(y - 1, x - 1) | (at(y - 1, x) << 1) | (at(y - 1, x + 1) << 2) | (at(y, x + 1) << 3) | (at(y + 1, x + 1) << 4) |
+         (at(y + 1, x) << 5) | (at(y + 1, x - 1) << 6) | (at(y, x - 1) << 7);
+}
+__global__ void __launch_bounds__(256) thin_subpass(const uint8_t* __restrict__ in, int H, int W, int bit,
+                                                    uint8_t* __restrict__ out, unsigned int* __restrict__ removed) {
+  int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  if (x >= W) return;
+  int64_t i = (int64_t)y * W + x;
+  uint8_t v = in[i] != 0;
+  if (v && (c_zs_lut[nb_code(in, H, W, y, x)] & bit)) {
+    v = 0;
+    atomicAdd(removed, 1u);
+  }
+  out[i] = v;
+}
+// degree > 2 in the 8-neighbour pixel graph (transforms.py:248, :334)
+__global__ void __launch_bounds__(256) fork_kernel(const uint8_t* __restrict__ sk, int H, int W, const int* __restrict__ sk_root,
+                                                   uint8_t* __restrict__ has_fork /*indexed by root pixel*/) {
+  int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  if (x >= W) return;
+  int64_t i = (int64_t)y * W + x;
+  if (!sk[i]) return;
+  if (__popc(nb_code(sk, H, W, y, x)) > 2) has_fork[sk_root[i]] = 1;
+}
+// one thread per skeleton component (its root pixel): decide whether its mask component dies
+__global__ void __launch_bounds__(256) kill_kernel(const int* __restrict__ sk_root, const uint8_t* __restrict__ has_fork,
+                                                   const int32_t* __restrict__ labels, const uint8_t* __restrict__ round_flag,
+                                                   int64_t n, int remove_isolated, uint8_t* __restrict__ kill /*[nlab+1]*/) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n || sk_root[i] != (int)i) return;
+  int l = labels[i];
+  if ((remove_isolated && !has_fork[i]) || round_flag[l]) kill[l] = 1;
+}
+__global__ void __launch_bounds__(256) apply_kill(const uint8_t* __restrict__ m, const int32_t* __restrict__ labels,
+                                                  const uint8_t* __restrict__ kill, int64_t n, uint8_t* __restrict__ out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  out[i] = (m[i] != 0) && !kill[labels[i]];
+}
+__global__ void __launch_bounds__(256) binarize(const uint8_t* __restrict__ m, int64_t n, uint8_t* __restrict__ out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = m[i] != 0;
+}
+
+// ---- per-root areas (no renumbering needed) ------------------------------------------------------------
+__global__ void __launch_bounds__(256) root_area(const int* __restrict__ parent, int64_t n, unsigned int* __restrict__ area) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && parent[i] >= 0) atomicAdd(&area[parent[i]], 1u);
+}
+// remove_small_islands step: pixels whose component (of the tested polarity) is smaller than min_size flip
+__global__ void __launch_bounds__(256) flip_small(const int* __restrict__ parent, const unsigned int* __restrict__ area,
+                                                  int64_t n, unsigned int min_size, uint8_t set_to, uint8_t* __restrict__ mask) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && parent[i] >= 0 && area[parent[i]] < min_size) mask[i] = set_to;
+}
+__global__ void __launch_bounds__(256) area_image_kernel(const int* __restrict__ parent, const unsigned int* __restrict__ area,
+                                                         int64_t n, double* __restrict__ out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = parent[i] >= 0 ? (double)area[parent[i]] : 0.0;
+}
+
+}  // namespace
+
+// ---- host side --------------------------------------------------------------------------------------
+static const uint8_t* zs_lut_host() {
+  // Zhang-Suen deletability per 8-neighbour code (bit0 NW, 1 N, 2 NE, 3 E, 4 SE, 5 S, 6 SW, 7 W):
+  // bit 1 = deletable in sub-pass 1, bit 2 = deletable in sub-pass 2.
+  static uint8_t lut[256];
+  static bool init = false;
+  if (!init) {
+    for (int v = 0; v < 256; ++v) {
+      int nw = v & 1, n = (v >> 1) & 1, ne = (v >> 2) & 1, e = (v >> 3) & 1, se = (v >> 4) & 1, s = (v >> 5) & 1,
+          sw = (v >> 6) & 1, w = (v >> 7) & 1;
+      int ring[8] = {n, ne, e, se, s, sw, w, nw};   // P2..P9
+      int b = 0, a = 0;
+      for (int i = 0; i < 8; ++i) { b += ring[i]; a += (ring[i] == 0 && ring[(i + 1) & 7] == 1); }
+      uint8_t r = 0;
+      if (b >= 2 && b <= 6 && a == 1) {
+        if (n * e * s == 0 && e * s * w == 0) r |= 1;
+        if (n * e * w == 0 && n * s * w == 0) r |= 2;
+      }
+      lut[v] = r;
+    }
+    init = true;
+  }
+  return lut;
+}
+
+static inline dim3 grid2d(int H, int W) { return dim3(cdiv(W, 256), H); }
+static inline unsigned grid1d(int64_t n) { return (unsigned)cdiv64(n, 256); }
+
+int erode_disk(tmat_ctx* ctx, const uint8_t* in, int H, int W, int r, int border_value, uint8_t* out, cudaStream_t st) {
+  TMAT_REQUIRE(r >= 0 && r <= ER_MAX_R, "erode_disk: radius %d outside [0,%d]", r, ER_MAX_R);
+  dim3 grid(cdiv(W, ER_T), cdiv(H, ER_T)), block(ER_T, 8);
+  erode_disk_kernel<<<grid, block, 0, st>>>(in, H, W, r, border_value, out);
+  KERNEL_CHECK(ctx);
+  return TMAT_OK;
+}
+
+int median_disk2(tmat_ctx* ctx, const uint8_t* in, int H, int W, uint8_t* out, cudaStream_t st) {
+  median_disk2_kernel<<<grid2d(H, W), 256, 0, st>>>(in, H, W, out);
+  KERNEL_CHECK(ctx);
+  return TMAT_OK;
+}
+
+// parent[i] = index of the first pixel (raster order) of i's component, -1 for background
+static int ccl_roots(tmat_ctx* ctx, const uint8_t* mask, int H, int W, int connectivity, int fg_is_zero, int* parent,
+                     cudaStream_t st) {
+  TMAT_REQUIRE(connectivity == 1 || connectivity == 2, "label: connectivity must be 1 or 2, got %d", connectivity);
+  TMAT_REQUIRE((int64_t)H * W < (1ll << 31), "label: image too large");
+  int64_t n = (int64_t)H * W;
+  ccl_init<<<grid1d(n), 256, 0, st>>>(mask, n, fg_is_zero, parent);
+  KERNEL_CHECK(ctx);
+  ccl_merge<<<grid2d(H, W), 256, 0, st>>>(parent, H, W, connectivity == 2);
+  KERNEL_CHECK(ctx);
+  ccl_flatten<<<grid1d(n), 256, 0, st>>>(parent, n);
+  KERNEL_CHECK(ctx);
+  return TMAT_OK;
+}
+
+// labels 1..n in raster order of each component's first pixel; synchronises to return n
+static int label_impl(tmat_ctx* ctx, const uint8_t* mask, int H, int W, int connectivity, int32_t* labels, int* n_labels,
+                      int** parent_out, cudaStream_t st) {
+  int64_t n = (int64_t)H * W;
+  int nb = (int)cdiv64(n, SCAN_BLOCK);
+  int *parent, *rank, *bsum, *total;
+  TMAT_TRY(arena_get(ctx, (size_t)n, &parent));
+  TMAT_TRY(arena_get(ctx, (size_t)n, &rank));
+  TMAT_TRY(arena_get(ctx, (size_t)nb + 1, &bsum));
+  TMAT_TRY(arena_get(ctx, 1, &total));
+  TMAT_TRY(ccl_roots(ctx, mask, H, W, connectivity, 0, parent, st));
+  roots_count<<<nb, 256, 0, st>>>(parent, n, bsum);
+  KERNEL_CHECK(ctx);
+  scan_block_sums<<<1, 1024, 0, st>>>(bsum, nb, total);
+  KERNEL_CHECK(ctx);
+  roots_rank<<<nb, 256, 0, st>>>(parent, n, bsum, rank);
+  KERNEL_CHECK(ctx);
+  labels_from_rank<<<grid1d(n), 256, 0, st>>>(parent, rank, n, labels);
+  KERNEL_CHECK(ctx);
+  int* h = (int*)ctx->pinned;
+  CUDA_TRY(cudaMemcpyAsync(h, total, sizeof(int), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  *n_labels = *h;
+  if (parent_out) *parent_out = parent;
+  return TMAT_OK;
+}
+
+static int skeletonize_impl(tmat_ctx* ctx, const uint8_t* mask, int H, int W, uint8_t* out, int* iterations,
+                            cudaStream_t st) {
+  int64_t n = (int64_t)H * W;
+  CUDA_TRY(cudaMemcpyToSymbolAsync(c_zs_lut, zs_lut_host(), 256, 0, cudaMemcpyHostToDevice, st));
+  uint8_t* tmp;
+  unsigned int* counters;
+  constexpr int BATCH = 8;
+  TMAT_TRY(arena_get(ctx, (size_t)n, &tmp));
+  TMAT_TRY(arena_get(ctx, BATCH, &counters));
+  binarize<<<grid1d(n), 256, 0, st>>>(mask, n, out);
+  KERNEL_CHECK(ctx);
+  unsigned int* h = (unsigned int*)ctx->pinned;
+  int iters = 0;
+  for (;;) {
+    CUDA_TRY(cudaMemsetAsync(counters, 0, BATCH * sizeof(unsigned int), st));
+    for (int k = 0; k < BATCH; ++k) {
+      thin_subpass<<<grid2d(H, W), 256, 0, st>>>(out, H, W, 1, tmp, counters + k);
+      KERNEL_CHECK(ctx);
+      thin_subpass<<<grid2d(H, W), 256, 0, st>>>(tmp, H, W, 2, out, counters + k);
+      KERNEL_CHECK(ctx);
+    }
+    CUDA_TRY(cudaMemcpyAsync(h, counters, BATCH * sizeof(unsigned int), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    int k = 0;
+    while (k < BATCH && h[k] != 0) ++k;
+    if (k < BATCH) { iters += k + 1; break; }   // round k removed nothing: the reference stops there
+    iters += BATCH;
+  }
+  if (iterations) *iterations = iters;
+  return TMAT_OK;
+}
+
+// transforms.py:306-361.  `mask` and `out` may alias.
+int filter_branch_impl(tmat_ctx* ctx, const uint8_t* mask, int H, int W, int use_median, int remove_isolated,
+                       uint8_t* out, cudaStream_t st) {
+  int64_t n = (int64_t)H * W;
+  uint8_t *m, *sk, *border;
+  int32_t* labels;
+  TMAT_TRY(arena_get(ctx, (size_t)n, &m));
+  TMAT_TRY(arena_get(ctx, (size_t)n, &sk));
+  TMAT_TRY(arena_get(ctx, (size_t)n, &border));
+  TMAT_TRY(arena_get(ctx, (size_t)n, &labels));
+  if (use_median) TMAT_TRY(median_disk2(ctx, mask, H, W, m, st));
+  else { binarize<<<grid1d(n), 256, 0, st>>>(mask, n, m); KERNEL_CHECK(ctx); }
+  int nlab = 0;
+  TMAT_TRY(label_impl(ctx, m, H, W, 2, labels, &nlab, nullptr, st));
+  unsigned int *area, *hist;
+  uint8_t *round_flag, *kill, *has_fork;
+  int* sk_root;
+  TMAT_TRY(arena_get(ctx, (size_t)nlab + 1, &area));
+  TMAT_TRY(arena_get(ctx, ((size_t)nlab + 1) * 50, &hist));
+  TMAT_TRY(arena_get(ctx, (size_t)nlab + 2, &round_flag));
+  TMAT_TRY(arena_get(ctx, (size_t)nlab + 2, &kill));
+  TMAT_TRY(arena_get(ctx, (size_t)n, &has_fork));
+  TMAT_TRY(arena_get(ctx, (size_t)n, &sk_root));
+  CUDA_TRY(cudaMemsetAsync(area, 0, ((size_t)nlab + 1) * 4, st));
+  CUDA_TRY(cudaMemsetAsync(hist, 0, ((size_t)nlab + 1) * 200, st));
+  CUDA_TRY(cudaMemsetAsync(round_flag, 0, (size_t)nlab + 2, st));
+  CUDA_TRY(cudaMemsetAsync(kill, 0, (size_t)nlab + 2, st));
+  CUDA_TRY(cudaMemsetAsync(has_fork, 0, (size_t)n, st));
+  if (nlab > 0) {
+    border_kernel<<<grid2d(H, W), 256, 0, st>>>(labels, H, W, border);
+    KERNEL_CHECK(ctx);
+    region_stats_kernel<<<grid2d(H, W), 256, 0, st>>>(labels, border, H, W, area, hist);
+    KERNEL_CHECK(ctx);
+    circ_flag_kernel<<<cdiv(nlab, 256), 256, 0, st>>>(area, hist, nlab, round_flag);
+    KERNEL_CHECK(ctx);
+    TMAT_TRY(skeletonize_impl(ctx, m, H, W, sk, nullptr, st));
+    TMAT_TRY(ccl_roots(ctx, sk, H, W, 2, 0, sk_root, st));
+    fork_kernel<<<grid2d(H, W), 256, 0, st>>>(sk, H, W, sk_root, has_fork);
+    KERNEL_CHECK(ctx);
+    kill_kernel<<<grid1d(n), 256, 0, st>>>(sk_root, has_fork, labels, round_flag, n, remove_isolated, kill);
+    KERNEL_CHECK(ctx);
+  }
+  apply_kill<<<grid1d(n), 256, 0, st>>>(m, labels, kill, n, out);
+  KERNEL_CHECK(ctx);
+  return TMAT_OK;
+}
+
+// ---- C ABI: device-pointer entry points ----------------------------------------------------------------
+#define MORPH_ARGS_OK(name) TMAT_REQUIRE(ctx && mask_dev && H >= 1 && W >= 1, name ": bad argument")
+
+extern "C" int tmat_median_disk2_dev(tmat_ctx* ctx, const uint8_t* mask_dev, int H, int W, uint8_t* out_dev, void* stream) {
+  MORPH_ARGS_OK("tmat_median_disk2");
+  TMAT_REQUIRE(out_dev && out_dev != mask_dev, "tmat_median_disk2: out must be a distinct buffer");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  return median_disk2(ctx, mask_dev, H, W, out_dev, as_stream(stream));
+}
+
+extern "C" int tmat_erode_disk_dev(tmat_ctx* ctx, const uint8_t* mask_dev, int H, int W, int r, int border_value,
+                                   uint8_t* out_dev, void* stream) {
+  MORPH_ARGS_OK("tmat_erode_disk");
+  TMAT_REQUIRE(out_dev && out_dev != mask_dev, "tmat_erode_disk: out must be a distinct buffer");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  return erode_disk(ctx, mask_dev, H, W, r, border_value, out_dev, as_stream(stream));
+}
+
+extern "C" int tmat_label_dev(tmat_ctx* ctx, const uint8_t* mask_dev, int H, int W, int connectivity,
+                              int32_t* labels_dev, int* n_labels, void* stream) {
+  MORPH_ARGS_OK("tmat_label");
+  TMAT_REQUIRE(labels_dev && n_labels, "tmat_label: NULL output");
+  TMAT_TRY(arena_reset(ctx));
+  return label_impl(ctx, mask_dev, H, W, connectivity, labels_dev, n_labels, nullptr, as_stream(stream));
+}
+
+extern "C" int tmat_region_stats_dev(tmat_ctx* ctx, const int32_t* labels_dev, int H, int W, int n_labels,
+                                     int64_t* area_host, int64_t* perim_hist_host, void* stream) {
+  TMAT_REQUIRE(ctx && labels_dev && area_host && perim_hist_host && H >= 1 && W >= 1 && n_labels >= 0,
+               "tmat_region_stats: bad argument");
+  if (n_labels == 0) return TMAT_OK;
+  TMAT_TRY(arena_reset(ctx));
+  cudaStream_t st = as_stream(stream);
+  int64_t n = (int64_t)H * W;
+  uint8_t* border;
+  unsigned int *area, *hist;
+  TMAT_TRY(arena_get(ctx, (size_t)n, &border));
+  TMAT_TRY(arena_get(ctx, (size_t)n_labels, &area));
+  TMAT_TRY(arena_get(ctx, (size_t)n_labels * 50, &hist));
+  CUDA_TRY(cudaMemsetAsync(area, 0, (size_t)n_labels * 4, st));
+  CUDA_TRY(cudaMemsetAsync(hist, 0, (size_t)n_labels * 200, st));
+  border_kernel<<<grid2d(H, W), 256, 0, st>>>(labels_dev, H, W, border);
+  KERNEL_CHECK(ctx);
+  region_stats_kernel<<<grid2d(H, W), 256, 0, st>>>(labels_dev, border, H, W, area, hist);
+  KERNEL_CHECK(ctx);
+  std::vector<unsigned int> ha(n_labels), hh((size_t)n_labels * 50);
+  CUDA_TRY(cudaMemcpyAsync(ha.data(), area, (size_t)n_labels * 4, cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaMemcpyAsync(hh.data(), hist, (size_t)n_labels * 200, cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  for (int i = 0; i < n_labels; ++i) area_host[i] = ha[i];
+  for (size_t i = 0; i < hh.size(); ++i) perim_hist_host[i] = hh[i];
+  return TMAT_OK;
+}
+
+extern "C" int tmat_skeletonize_dev(tmat_ctx* ctx, const uint8_t* mask_dev, int H, int W, uint8_t* out_dev,
+                                    int* iterations, void* stream) {
+  MORPH_ARGS_OK("tmat_skeletonize");
+  TMAT_REQUIRE(out_dev && out_dev != mask_dev, "tmat_skeletonize: out must be a distinct buffer");
+  TMAT_TRY(arena_reset(ctx));
+  return skeletonize_impl(ctx, mask_dev, H, W, out_dev, iterations, as_stream(stream));
+}
+
+extern "C" int tmat_filter_branch_seg_mask_dev(tmat_ctx* ctx, const uint8_t* mask_dev, int H, int W, int use_median,
+                                               int remove_isolated, uint8_t* out_dev, void* stream) {
+  MORPH_ARGS_OK("tmat_filter_branch_seg_mask");
+  TMAT_REQUIRE(out_dev, "tmat_filter_branch_seg_mask: NULL output");
+  TMAT_TRY(arena_reset(ctx));
+  return filter_branch_impl(ctx, mask_dev, H, W, use_median, remove_isolated, out_dev, as_stream(stream));
+}
+
+// ---- C ABI: host-pointer entry points --------------------------------------------------------------------
+// copy a host mask in, run `body(d_in, d_out)`, copy the uint8 result out
+template <typename F>
+static int with_host_mask(tmat_ctx* ctx, const uint8_t* in_host, int H, int W, uint8_t* out_host, F body) {
+  TMAT_REQUIRE(ctx && in_host && out_host && H >= 1 && W >= 1, "morphology(host): bad argument");
+  TMAT_TRY(arena_reset(ctx));
+  size_t n = (size_t)H * W;
+  uint8_t *d_in, *d_out;
+  TMAT_TRY(arena_get(ctx, n, &d_in));
+  TMAT_TRY(arena_get(ctx, n, &d_out));
+  CUDA_TRY(cudaMemcpyAsync(d_in, in_host, n, cudaMemcpyHostToDevice, 0));
+  TMAT_TRY(body(d_in, d_out));
+  CUDA_TRY(cudaMemcpyAsync(out_host, d_out, n, cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaStreamSynchronize(0));
+  return TMAT_OK;
+}
+
+extern "C" int tmat_median_disk2_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W, uint8_t* out_host) {
+  return with_host_mask(ctx, mask_host, H, W, out_host,
+                        [&](uint8_t* a, uint8_t* b) { return median_disk2(ctx, a, H, W, b, 0); });
+}
+extern "C" int tmat_erode_disk_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W, int r, int border_value,
+                                    uint8_t* out_host) {
+  return with_host_mask(ctx, mask_host, H, W, out_host,
+                        [&](uint8_t* a, uint8_t* b) { return erode_disk(ctx, a, H, W, r, border_value, b, 0); });
+}
+extern "C" int tmat_skeletonize_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W, uint8_t* out_host,
+                                     int* iterations) {
+  return with_host_mask(ctx, mask_host, H, W, out_host,
+                        [&](uint8_t* a, uint8_t* b) { return skeletonize_impl(ctx, a, H, W, b, iterations, 0); });
+}
+extern "C" int tmat_filter_branch_seg_mask_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W, int use_median,
+                                                int remove_isolated, uint8_t* out_host) {
+  return with_host_mask(ctx, mask_host, H, W, out_host, [&](uint8_t* a, uint8_t* b) {
+    return filter_branch_impl(ctx, a, H, W, use_median, remove_isolated, b, 0);
+  });
+}
+
+extern "C" int tmat_label_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W, int connectivity,
+                               int32_t* labels_host, int* n_labels) {
+  TMAT_REQUIRE(ctx && mask_host && labels_host && n_labels && H >= 1 && W >= 1, "tmat_label_host: bad argument");
+  TMAT_TRY(arena_reset(ctx));
+  size_t n = (size_t)H * W;
+  uint8_t* d_in;
+  int32_t* d_lab;
+  TMAT_TRY(arena_get(ctx, n, &d_in));
+  TMAT_TRY(arena_get(ctx, n, &d_lab));
+  CUDA_TRY(cudaMemcpyAsync(d_in, mask_host, n, cudaMemcpyHostToDevice, 0));
+  TMAT_TRY(label_impl(ctx, d_in, H, W, connectivity, d_lab, n_labels, nullptr, 0));
+  CUDA_TRY(cudaMemcpyAsync(labels_host, d_lab, n * 4, cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaStreamSynchronize(0));
+  return TMAT_OK;
+}
+
+// transforms.py:170-206: fill holes smaller than min_area0 (background components, connectivity0), then
+// drop objects smaller than min_area1 (foreground components, connectivity1).
+extern "C" int tmat_remove_small_islands_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W, int min_area0,
+                                              int min_area1, int connectivity0, int connectivity1, uint8_t* out_host) {
+  TMAT_REQUIRE(ctx && mask_host && out_host && H >= 1 && W >= 1, "tmat_remove_small_islands: bad argument");
+  size_t n = (size_t)H * W;
+  uint8_t lo = 255, hi = 0;
+  for (size_t i = 0; i < n; ++i) { lo = std::min(lo, mask_host[i]); hi = std::max(hi, mask_host[i]); }
+  // the reference raises ValueError (transforms.py:183-184)
+  TMAT_REQUIRE(lo == 0 && hi <= 1, "this function expects a binary mask of values 0 and 1");
+  return with_host_mask(ctx, mask_host, H, W, out_host, [&](uint8_t* a, uint8_t* b) {
+    int* parent;
+    unsigned int* area;
+    TMAT_TRY(arena_get(ctx, n, &parent));
+    TMAT_TRY(arena_get(ctx, n, &area));
+    CUDA_TRY(cudaMemcpyAsync(b, a, n, cudaMemcpyDeviceToDevice, 0));
+    // background components of the input
+    TMAT_TRY(ccl_roots(ctx, b, H, W, connectivity0, 1, parent, 0));
+    CUDA_TRY(cudaMemsetAsync(area, 0, n * 4, 0));
+    root_area<<<grid1d((int64_t)n), 256>>>(parent, (int64_t)n, area);
+    KERNEL_CHECK(ctx);
+    flip_small<<<grid1d((int64_t)n), 256>>>(parent, area, (int64_t)n, (unsigned)std::max(min_area0, 0), 1, b);
+    KERNEL_CHECK(ctx);
+    // foreground components of the hole-filled mask
+    TMAT_TRY(ccl_roots(ctx, b, H, W, connectivity1, 0, parent, 0));
+    CUDA_TRY(cudaMemsetAsync(area, 0, n * 4, 0));
+    root_area<<<grid1d((int64_t)n), 256>>>(parent, (int64_t)n, area);
+    KERNEL_CHECK(ctx);
+    flip_small<<<grid1d((int64_t)n), 256>>>(parent, area, (int64_t)n, (unsigned)std::max(min_area1, 0), 0, b);
+    KERNEL_CHECK(ctx);
+    return TMAT_OK;
+  });
+}
+
+// transforms.py:291-303 with prop = 'area': label (full connectivity) and paint each component's area
+extern "C" int tmat_area_image_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W, double* out_host) {
+  TMAT_REQUIRE(ctx && mask_host && out_host && H >= 1 && W >= 1, "tmat_area_image: bad argument");
+  TMAT_TRY(arena_reset(ctx));
+  size_t n = (size_t)H * W;
+  uint8_t* d_in;
+  int* parent;
+  unsigned int* area;
+  double* d_out;
+  TMAT_TRY(arena_get(ctx, n, &d_in));
+  TMAT_TRY(arena_get(ctx, n, &parent));
+  TMAT_TRY(arena_get(ctx, n, &area));
+  TMAT_TRY(arena_get(ctx, n, &d_out));
+  CUDA_TRY(cudaMemcpyAsync(d_in, mask_host, n, cudaMemcpyHostToDevice, 0));
+  TMAT_TRY(ccl_roots(ctx, d_in, H, W, 2, 0, parent, 0));
+  CUDA_TRY(cudaMemsetAsync(area, 0, n * 4, 0));
+  root_area<<<grid1d((int64_t)n), 256>>>(parent, (int64_t)n, area);
+  KERNEL_CHECK(ctx);
+  area_image_kernel<<<grid1d((int64_t)n), 256>>>(parent, area, (int64_t)n, d_out);
+  KERNEL_CHECK(ctx);
+  CUDA_TRY(cudaMemcpyAsync(out_host, d_out, n * 8, cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaStreamSynchronize(0));
+  return TMAT_OK;
+}

@@ -37,7 +37,7 @@ extern "C" int tmat_stp_geometry(int H, int W, int ws, int subdiv, int* geom8) {
 // ---- spline window on the host, numpy-compatible ------------------------------------------
 // numpy's pairwise summation (np.add.reduce on a contiguous float64 vector), needed because
 // the window is normalised by np.average (:40).
-static double np_pairwise_sum(const double* a, int64_t n) {
+double np_pairwise_sum(const double* a, int64_t n) {
   if (n < 8) {
     double res = 0.;
     for (int64_t i = 0; i < n; i++) res += a[i];

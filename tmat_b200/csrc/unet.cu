@@ -473,6 +473,15 @@ extern "C" int tmat_unet_forward_host(tmat_ctx* ctx, tmat_unet* net, const float
   return r;
 }
 
+// scratch bytes stp_predict_impl takes from the arena (patch probabilities + one chunk of activations)
+size_t stp_predict_scratch_bytes(const tmat_unet* net, int H, int W, int subdiv) {
+  StpGeom G;
+  if (stp_make_geom(H, W, net->desc.patch, subdiv, &G) != TMAT_OK) return 0;
+  const int n_total = 8 * G.tiles_per_orient();
+  const int ws = net->desc.patch;
+  return (size_t)n_total * ws * ws * 4 + forward_scratch_bytes(net, std::min(n_total, chunk_size(net))) + (4 << 20);
+}
+
 // predict_img_with_smooth_windowing with pred_func = this UNet; arena must have been reset by the caller
 int stp_predict_impl(tmat_ctx* ctx, tmat_unet* net, const float* img_dev, int H, int W, int subdiv,
                      double* out_dev, cudaStream_t st) {
