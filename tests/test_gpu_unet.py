@@ -83,3 +83,29 @@ def test_fused_tiled_prediction_vs_oracle():
     # the generic route (tiles -> net.predict on host batches -> GPU blend) agrees with the fused one
     gen = predict_img_with_smooth_windowing(img, ws, 2, lambda b, verbose=0: net.predict(b))
     assert np.abs(gen - out).max() < 1e-6
+
+
+def test_whole_branch_mask_path_vs_oracle():
+    """tmat_branch_mask_dev (Z max -> rescale -> tiled UNet -> >0.5 -> cleanup) vs the same chain of oracles."""
+    import torch
+    from oracle import zstacks as oz, thresholds as ot, morphology as om
+    from tmat_b200 import _ffi, models
+    fc, ws = (64, 128, 256, 512), 64
+    w = ou.make_weights(fc, seed=5, randomize_affine=True, head_gain=4.0)
+    stack = helpers.synth_stack(5, 150, 131, 3)
+    net = models.CudaUNet(w, ws, fc, impl="tc")
+    ctx = net.ctx
+    d_stack = torch.from_numpy(stack).cuda()
+    d_pred = torch.empty((150, 131), dtype=torch.float64, device="cuda")
+    d_mask = torch.empty((150, 131), dtype=torch.uint8, device="cuda")
+    _ffi.check(_ffi.lib().tmat_branch_mask_dev(ctx.handle, net._tmat_handle, _ffi.ptr(d_stack), 5, 150, 131, 2,
+                                               _ffi.ptr(d_pred), _ffi.ptr(d_mask), None))
+    torch.cuda.synchronize()
+    pred, mask = d_pred.cpu().numpy(), d_mask.cpu().numpy().astype(bool)
+    img = ot.rescale_unit_f32(oz.proj_max(stack))
+    ref_pred = ostp.predict_img_with_smooth_windowing(img, ws, 2, ou.make_pred_func(w))
+    assert np.abs(pred - ref_pred).max() < PROB_TOL
+    # downstream of the threshold the stage is bit-exact: same cleanup of OUR thresholded prediction
+    assert np.array_equal(mask, om.filter_branch_seg_mask(pred > 0.5))
+    ref_mask = om.filter_branch_seg_mask(ref_pred > 0.5)
+    assert (mask == ref_mask).mean() >= 0.999 or np.abs(ref_pred - 0.5).min() < PROB_TOL
