@@ -136,10 +136,12 @@ int tmat_unet_debug_tap(tmat_ctx* ctx, tmat_unet* net, const char* name, float* 
 /* debug / test hook: one implicit-GEMM convolution (the unit the UNet is built from) on seeded
  * random data through the CUDA-core executor and through the tcgen05 executor; returns the
  * max-abs difference of the outputs and the max-abs of the CUDA-core output.
- * epi: 0 store, 1 upsample-store, 2 maxpool-add, 3 head (sigmoid unless relu!=0). */
+ * epi: 0 store, 1 parity store (3x3 conv on the 2x nearest-upsampled input, evaluated at low
+ * resolution), 3 head (sigmoid unless relu!=0).  dual: also write the ReLU'd copy (epi 0).
+ * addend: 0 none, 1 same-resolution addend, 2 half-resolution addend (epi 0). */
 int tmat_debug_conv_selftest(tmat_ctx* ctx, int B, int H, int W, int C0, int C1, int Cout, int ntaps,
-                             int epi, int relu, int dual, uint64_t seed, double* max_abs_diff,
-                             double* max_abs_ref);
+                             int epi, int relu, int dual, int addend, uint64_t seed,
+                             double* max_abs_diff, double* max_abs_ref);
 /* FLOPs (2*MAC of every convolution as written in models.py:110-171) of one patch */
 int tmat_unet_flops_per_patch(const tmat_unet_desc* desc, double* flops);
 

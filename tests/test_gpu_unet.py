@@ -13,13 +13,20 @@ pytestmark = pytest.mark.gpu
 PROB_TOL = 1e-2   # BASELINE.json north_star: blended probabilities within 1e-2 max-abs
 
 CONV_CASES = [
-    # B, H, W, C0, C1, Cout, taps, epi, relu, dual
-    (1, 8, 16, 64, 0, 64, 1, 0, 0, 0), (1, 8, 16, 64, 0, 64, 9, 0, 0, 0),
-    (2, 16, 16, 128, 0, 128, 9, 0, 1, 0), (2, 20, 20, 512, 0, 512, 9, 0, 1, 0),
-    (3, 20, 20, 512, 512, 512, 9, 1, 0, 1), (2, 40, 40, 256, 512, 256, 9, 1, 0, 1),
-    (2, 80, 80, 64, 0, 128, 1, 0, 1, 0), (2, 40, 40, 64, 0, 128, 1, 2, 0, 1),
-    (1, 24, 24, 64, 0, 4, 9, 3, 0, 0), (5, 13, 27, 64, 64, 64, 9, 0, 0, 0),
-    (9, 7, 5, 128, 0, 256, 9, 0, 1, 0), (1, 160, 160, 128, 0, 64, 9, 0, 1, 0),
+    # B, H, W, C0, C1, Cout, taps, epi (0 store, 1 parity, 3 head), relu, dual, addend (1 same-res, 2 half-res)
+    (1, 8, 16, 64, 0, 64, 1, 0, 0, 0, 0), (1, 8, 16, 64, 0, 64, 9, 0, 0, 0, 0),
+    (2, 16, 16, 128, 0, 128, 9, 0, 1, 0, 0), (2, 20, 20, 512, 0, 512, 9, 0, 1, 0, 0),
+    (3, 20, 20, 512, 512, 512, 9, 0, 0, 1, 0),          # up0.ct2: residual as extra k-steps, P and R stores
+    (2, 40, 40, 256, 0, 256, 9, 0, 0, 1, 2),            # up1.ct2: + Z[y/2, x/2], P and R stores
+    (2, 80, 80, 64, 0, 128, 1, 0, 1, 0, 0),
+    (2, 40, 40, 64, 0, 128, 1, 0, 0, 1, 1),             # down.res: + pooled tensor, P and R stores
+    (1, 24, 24, 64, 0, 4, 9, 3, 0, 0, 0), (5, 13, 27, 64, 64, 64, 9, 0, 0, 0, 0),
+    (9, 7, 5, 128, 0, 256, 9, 0, 1, 0, 0), (1, 160, 160, 128, 0, 64, 9, 0, 1, 0, 0),
+    (2, 13, 27, 64, 0, 64, 9, 0, 0, 0, 2),              # half-resolution addend on odd sizes
+    (2, 20, 20, 512, 0, 256, 9, 1, 1, 0, 0),            # parity store, 4 groups of 4 taps (up1.ct1)
+    (2, 40, 40, 256, 0, 128, 9, 1, 1, 0, 0),            # parity store, 2 groups of 6 taps (up2.ct1)
+    (1, 80, 80, 128, 0, 64, 9, 1, 1, 0, 0),             # parity store, 1 group of 9 taps (up3.ct1)
+    (3, 13, 11, 64, 0, 64, 9, 1, 0, 0, 0), (2, 7, 9, 128, 0, 128, 9, 1, 1, 0, 0),
 ]
 
 
@@ -46,7 +53,7 @@ def test_unet_forward_vs_oracle(fc, ws, n, impl):
     out = net.predict(x)
     assert out.shape == ref.shape and out.dtype == np.float32
     assert np.abs(out - ref).max() < PROB_TOL
-    for name in ("stem", "down0", "down2", "up0", "up2"):
+    for name in ("stem", "down0.r1", "down0.b2", "down0", "down2", "up0.r1", "up0", "up1.r1", "up2", "up3"):
         got = net.debug_tap(name).reshape(taps[name].shape)
         assert np.abs(got - taps[name]).max() < 0.02 * max(1.0, np.abs(taps[name]).max()), name
     assert abs(net.flops_per_patch() - ou.flops_per_patch(ws, fc)) < 1

@@ -9,12 +9,19 @@
 // The B tile is a 2-D TMA box of the packed weight matrix [Npad][K].  Both land in shared memory in
 // the 128-byte-swizzled K-major layout that the UMMA shared-memory descriptors describe.
 //
+// A ConvOp may carry up to 4 column groups (EPI_PAR: the output-pixel parities of a 3x3 convolution
+// on a 2x nearest-upsampled tensor, evaluated on the low-resolution tensor): every group has its own
+// tap list and its own rows of the weight matrix, and shares the A tensor.
+//
 // Warp roles (192 threads, persistent over output tiles):
 //   warp 0      TMA producer       (ring of STAGES stages, full/empty mbarriers)
 //   warp 1      MMA issuer         (one lane issues tcgen05.mma, tcgen05.commit frees stages);
 //               also owns the TMEM allocation (2 accumulator buffers of BN columns)
-//   warps 2..5  epilogue           (tcgen05.ld -> +shift / ReLU / pool-add / upsample / sigmoid ->
-//                                   global), overlapped with the next tile's MMAs
+//   warps 2..5  epilogue           (tcgen05.ld -> +shift / +addend / ReLU -> bf16 -> 128B-swizzled smem
+//                                   staging tile -> one TMA tensor store per 64 channels), overlapped
+//                                   with the next tile's MMAs.  The TMA store clips partial tiles and
+//                                   writes full 128-byte lines, so the epilogue issues no per-thread
+//                                   global stores (the head, 4 floats per pixel, stores directly).
 #include "unet.cuh"
 #include <cuda.h>
 #include <algorithm>
@@ -24,15 +31,24 @@ namespace {
 constexpr int TILE_M = 128;
 constexpr int KSLAB = 64;                          // bf16 elements per k-step = 128 bytes = swizzle span
 constexpr int A_STAGE_BYTES = TILE_M * KSLAB * 2;  // 16 KiB
-constexpr int MAX_KSTEPS = 96;
+constexpr int MAX_KSTEPS = 160;                    // over all groups
 constexpr int TC_THREADS = 192;
+constexpr int STG_BYTES = TILE_M * 128;            // one staging tile: 128 pixels x 64 bf16 channels
+constexpr int N_STG = 2;
 
 struct TcParams {
   int tw_log, th_log, tn_log;   // tile = 2^tw x 2^th pixels x 2^tn images (product 128)
-  int tiles_x, tiles_y, tiles_b, tiles_n, total_tiles;
-  int nk;
-  uint16_t kstep[MAX_KSTEPS];   // bit0 src | bits1-2 dy+1 | bits3-4 dx+1 | bits5.. c0/64
+  int tiles_x, tiles_y, tiles_b, tiles_n, ngroups, total_tiles;
+  int nk;                       // k-steps per group
+  int npad;                     // GEMM columns per group
+  uint16_t kstep[MAX_KSTEPS];   // [group][nk]: bit0 src | bits1-2 dy+1 | bits3-4 dx+1 | bits5.. c0/64
   EpiParams e;
+};
+
+// tensor maps of the output: m[q] = view of parity q (EPI_STORE: m[0] = the tensor), m2 = ReLU'd copy
+struct TcOutMaps {
+  CUtensorMap m[4];
+  CUtensorMap m2;
 };
 
 // ---- PTX wrappers ----------------------------------------------------------------------------
@@ -78,6 +94,23 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
   asm volatile(
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
       ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+// smem tile -> global tensor (bulk async group of the issuing thread)
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* map, uint32_t src, int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+      ::"l"(map), "r"(src), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void tma_store_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+// named barrier among the 128 epilogue threads (barrier 0 is __syncthreads)
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint4 v) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
@@ -151,83 +184,22 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
 }
 __device__ __forceinline__ float sigmoid_f(float v) { return 1.f / (1.f + __expf(-v)); }
 
-// ---- epilogue: 32 consecutive channels of one pixel -------------------------------------------
-__device__ __forceinline__ void store32(bf16* dst, const float (&v)[32], bool relu) {
-  uint4* d = reinterpret_cast<uint4*>(dst);
-#pragma unroll
-  for (int q = 0; q < 4; ++q) {
-    float f[8];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) f[i] = relu ? fmaxf(v[8 * q + i], 0.f) : v[8 * q + i];
-    uint4 o;
-    o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]);
-    o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
-    d[q] = o;
-  }
-}
-
-__device__ __forceinline__ void epilogue32(const EpiParams& e, int b, int y, int x, int col, float (&v)[32]) {
-#pragma unroll
-  for (int i = 0; i < 32; i += 4) {
-    float4 s = __ldg(reinterpret_cast<const float4*>(e.shift + col + i));
-    v[i] += s.x; v[i + 1] += s.y; v[i + 2] += s.z; v[i + 3] += s.w;
-  }
-  if (e.mode == EPI_POOLADD) {
-    const int H2 = 2 * e.H, W2 = 2 * e.W;
-    float m[32];
-#pragma unroll
-    for (int i = 0; i < 32; ++i) m[i] = -INFINITY;
-    for (int ky = 0; ky < 3; ++ky) {
-      int yy = 2 * y + ky;
-      if (yy >= H2) continue;
-      for (int kx = 0; kx < 3; ++kx) {
-        int xx = 2 * x + kx;
-        if (xx >= W2) continue;
-        const uint4* src = reinterpret_cast<const uint4*>(e.pool_src + (((int64_t)b * H2 + yy) * W2 + xx) * e.Cout + col);
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          uint4 u = __ldg(src + q);
-          const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            float2 t = __bfloat1622float2(h[i]);
-            m[8 * q + 2 * i] = fmaxf(m[8 * q + 2 * i], t.x);
-            m[8 * q + 2 * i + 1] = fmaxf(m[8 * q + 2 * i + 1], t.y);
-          }
-        }
-      }
-    }
-#pragma unroll
-    for (int i = 0; i < 32; ++i) v[i] += m[i];
-  }
-  if (e.mode == EPI_UP2) {
-    const int H2 = 2 * e.H, W2 = 2 * e.W;
-#pragma unroll
-    for (int d = 0; d < 4; ++d) {
-      int64_t o = (((int64_t)b * H2 + 2 * y + (d >> 1)) * W2 + 2 * x + (d & 1)) * e.Cout + col;
-      store32(e.out + o, v, e.relu != 0);
-      if (e.out2) store32(e.out2 + o, v, true);
-    }
-  } else {
-    int64_t o = (((int64_t)b * e.H + y) * e.W + x) * e.Cout + col;
-    store32(e.out + o, v, e.relu != 0);
-    if (e.out2) store32(e.out2 + o, v, true);
-  }
-}
-
 // ---- the kernel -------------------------------------------------------------------------------
 template <int BN, int STAGES>
 struct TcSmem {
   static constexpr int B_STAGE_BYTES = BN * KSLAB * 2;
   static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
-  static constexpr int BAR_OFFSET = STAGES * STAGE_BYTES;
+  static constexpr int STG_OFFSET = STAGES * STAGE_BYTES;
+  static constexpr int BAR_OFFSET = STG_OFFSET + N_STG * STG_BYTES;
   static constexpr int BYTES = BAR_OFFSET + 256 + 1024;   // barriers + alignment slack
+  static_assert(BYTES <= 227 * 1024, "shared memory budget");
 };
 
 template <int BN, int STAGES>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
-               const __grid_constant__ CUtensorMap tmB, const __grid_constant__ TcParams p) {
+               const __grid_constant__ CUtensorMap tmB, const __grid_constant__ TcOutMaps om,
+               const __grid_constant__ TcParams p) {
   using L = TcSmem<BN, STAGES>;
   constexpr int TMEM_COLS = (2 * BN <= 32) ? 32 : 2 * BN;   // power of two >= 32
   extern __shared__ uint8_t smem_raw[];
@@ -262,25 +234,34 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
 
   const int TW = 1 << p.tw_log, TH = 1 << p.th_log;
   const int tiles_xy = p.tiles_x * p.tiles_y;
+  const int tiles_gn = p.ngroups * p.tiles_n;
+  // tile index -> (pixel tile mt, group g, column tile nt); nt fastest so neighbouring CTAs share A in L2
+  auto decode = [&](int tile, int& g, int& nt, int& x0, int& y0, int& b0) {
+    int mt = tile / tiles_gn, r = tile - mt * tiles_gn;
+    g = r / p.tiles_n; nt = r - g * p.tiles_n;
+    int tb = mt / tiles_xy, rr = mt - tb * tiles_xy;
+    int ty = rr / p.tiles_x, tx = rr - ty * p.tiles_x;
+    x0 = tx << p.tw_log; y0 = ty << p.th_log; b0 = tb << p.tn_log;
+  };
 
   if (warp == 0) {
     // ================= TMA producer =================
     int stage = 0; uint32_t phase = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
-      int nt = tile % p.tiles_n, mt = tile / p.tiles_n;
-      int tb = mt / tiles_xy, r = mt - tb * tiles_xy;
-      int ty = r / p.tiles_x, tx = r - ty * p.tiles_x;
-      int x0 = tx << p.tw_log, y0 = ty << p.th_log, b0 = tb << p.tn_log;
+      int g, nt, x0, y0, b0;
+      decode(tile, g, nt, x0, y0, b0);
+      const uint16_t* ktab = p.kstep + g * p.nk;
+      const int brow = g * p.npad + nt * BN;
       for (int ks = 0; ks < p.nk; ++ks) {
         mbar_wait(empty_bar(stage), phase ^ 1);
         if (lane == 0) {
-          uint32_t kd = p.kstep[ks];
+          uint32_t kd = ktab[ks];
           int src = kd & 1, dy = (int)((kd >> 1) & 3) - 1, dx = (int)((kd >> 3) & 3) - 1, c0 = (int)(kd >> 5) * KSLAB;
           uint32_t sa = smem_base + stage * L::STAGE_BYTES;
           uint32_t sb = sa + A_STAGE_BYTES;
           mbar_expect_tx(full_bar(stage), L::STAGE_BYTES);
           tma_load_4d(sa, src ? &tmA1 : &tmA0, full_bar(stage), c0, x0 + dx, y0 + dy, b0);
-          tma_load_2d(sb, &tmB, full_bar(stage), ks * KSLAB, nt * BN);
+          tma_load_2d(sb, &tmB, full_bar(stage), ks * KSLAB, brow);
         }
         __syncwarp();
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -323,52 +304,119 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
     const int tx_in = row & (TW - 1);
     const int ty_in = (row >> p.tw_log) & (TH - 1);
     const int tb_in = row >> (p.tw_log + p.th_log);
+    const bool leader = (threadIdx.x == 64);  // issues, commits and waits on every TMA store
+    const uint32_t stg_base = smem_base + L::STG_OFFSET;
+    const uint32_t stg_row = (uint32_t)row * 128u;
+    const uint32_t sw = (uint32_t)(row & 7);
+    const EpiParams& e = p.e;
+    int sbuf = 0;
     int it = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
       const int as = it & 1;
       const uint32_t aphase = (it >> 1) & 1;
-      int nt = tile % p.tiles_n, mt = tile / p.tiles_n;
-      int tb = mt / tiles_xy, r = mt - tb * tiles_xy;
-      int ty = r / p.tiles_x, tx = r - ty * p.tiles_x;
-      const int x = (tx << p.tw_log) + tx_in, y = (ty << p.th_log) + ty_in, b = (tb << p.tn_log) + tb_in;
-      const bool valid = (x < p.e.W) && (y < p.e.H) && (b < p.e.B);
+      int g, nt, x0, y0, b0;
+      decode(tile, g, nt, x0, y0, b0);
+      const int x = x0 + tx_in, y = y0 + ty_in, b = b0 + tb_in;
+      const bool valid = (x < e.W) && (y < e.H) && (b < e.B);
       mbar_wait(tfull_bar(as), aphase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
-      if constexpr (BN >= 32) {
+      if constexpr (BN >= 64) {
+        const bool dual = (e.out2 != nullptr);
+        const bf16* addp = nullptr;
+        if (e.add_src != nullptr && valid) {
+          const int s = e.add_shift;
+          const int Ha = (e.H + (1 << s) - 1) >> s, Wa = (e.W + (1 << s) - 1) >> s;
+          addp = e.add_src + (((int64_t)b * Ha + (y >> s)) * Wa + (x >> s)) * e.Cout;
+        }
 #pragma unroll 1
-        for (int c = 0; c < BN; c += 32) {
-          uint32_t rr[32];
-          tmem_ld32(taddr + c, rr);
-          tmem_ld_wait();
-          int col = nt * BN + c;
-          if (valid && col < p.e.Cout) {
+        for (int c64 = 0; c64 < BN; c64 += 64) {
+          const int col = nt * BN + c64;                        // column within the group
+          int par = 0, ch0 = col;
+          if (e.mode == EPI_PAR) { par = g * e.ppg + col / e.Cout; ch0 = col % e.Cout; }
+          // the staging buffer(s) about to be written must have been read out by their last store
+          if (leader) { if (dual) tma_store_wait_read<0>(); else tma_store_wait_read<1>(); }
+          epi_bar_sync();
+          const uint32_t buf0 = stg_base + (dual ? 0 : sbuf * STG_BYTES) + stg_row;
+          const uint32_t buf1 = stg_base + STG_BYTES + stg_row;
+#pragma unroll
+          for (int half = 0; half < 2; ++half) {
+            uint32_t rr[32];
+            tmem_ld32(taddr + c64 + half * 32, rr);
+            tmem_ld_wait();
             float v[32];
 #pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(rr[i]);
-            epilogue32(p.e, b, y, x, col, v);
+            for (int i = 0; i < 32; i += 4) {
+              float4 s = __ldg(reinterpret_cast<const float4*>(e.shift + ch0 + half * 32 + i));
+              v[i] = __uint_as_float(rr[i]) + s.x; v[i + 1] = __uint_as_float(rr[i + 1]) + s.y;
+              v[i + 2] = __uint_as_float(rr[i + 2]) + s.z; v[i + 3] = __uint_as_float(rr[i + 3]) + s.w;
+            }
+            if (addp != nullptr) {
+              const uint4* ap = reinterpret_cast<const uint4*>(addp + ch0 + half * 32);
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                uint4 u = __ldg(ap + j);
+                const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                  float2 t = __bfloat1622float2(h[i]);
+                  v[8 * j + 2 * i] += t.x; v[8 * j + 2 * i + 1] += t.y;
+                }
+              }
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const uint32_t off = (((uint32_t)(half * 4 + j)) ^ sw) << 4;   // 128-byte swizzle: chunk ^= row % 8
+              float f[8];
+#pragma unroll
+              for (int i = 0; i < 8; ++i) f[i] = e.relu ? fmaxf(v[8 * j + i], 0.f) : v[8 * j + i];
+              uint4 o;
+              o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]);
+              o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
+              st_shared_v4(buf0 + off, o);
+              if (dual) {
+                o.x = pack_bf16x2(fmaxf(v[8 * j], 0.f), fmaxf(v[8 * j + 1], 0.f));
+                o.y = pack_bf16x2(fmaxf(v[8 * j + 2], 0.f), fmaxf(v[8 * j + 3], 0.f));
+                o.z = pack_bf16x2(fmaxf(v[8 * j + 4], 0.f), fmaxf(v[8 * j + 5], 0.f));
+                o.w = pack_bf16x2(fmaxf(v[8 * j + 6], 0.f), fmaxf(v[8 * j + 7], 0.f));
+                st_shared_v4(buf1 + off, o);
+              }
+            }
           }
+          if (c64 + 64 >= BN) {                  // accumulator fully read: hand the TMEM buffer back
+            tc_fence_before();
+            mbar_arrive(tempty_bar(as));
+          }
+          fence_proxy_async();                   // generic-proxy smem writes -> visible to the TMA unit
+          epi_bar_sync();
+          if (leader) {
+            tma_store_4d(&om.m[par], buf0 - stg_row, ch0, x0, y0, b0);
+            if (dual) tma_store_4d(&om.m2, buf1 - stg_row, ch0, x0, y0, b0);
+            tma_store_commit();
+          }
+          if (!dual) sbuf ^= 1;
         }
       } else {
         // head: 4 output-pixel parities in columns 0..3
         uint32_t rr[16];
         tmem_ld16(taddr, rr);
         tmem_ld_wait();
+        tc_fence_before();
+        mbar_arrive(tempty_bar(as));
         if (valid) {
           float o[4];
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
-            float v = __uint_as_float(rr[i]) + __ldg(p.e.shift + i);
-            o[i] = p.e.logits ? v : sigmoid_f(v);
+            float v = __uint_as_float(rr[i]) + __ldg(e.shift + i);
+            o[i] = e.logits ? v : sigmoid_f(v);
           }
-          float* dst = p.e.out_f32 + ((int64_t)b * 2 * p.e.H + 2 * y) * (2 * p.e.W) + 2 * x;
+          float* dst = e.out_f32 + ((int64_t)b * 2 * e.H + 2 * y) * (2 * e.W) + 2 * x;
           *reinterpret_cast<float2*>(dst) = make_float2(o[0], o[1]);
-          *reinterpret_cast<float2*>(dst + 2 * p.e.W) = make_float2(o[2], o[3]);
+          *reinterpret_cast<float2*>(dst + 2 * e.W) = make_float2(o[2], o[3]);
         }
       }
-      tc_fence_before();
-      mbar_arrive(tempty_bar(as));
     }
+    if (leader) tma_store_wait_all();            // smem must outlive the last store's read
   }
 
   tc_fence_before();
@@ -396,11 +444,15 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 // NHWC activation tensor (B, H, W, C) bf16 -> 4-D map, box = (64 ch, TW, TH, TN), 128B swizzle, zero OOB fill
-static int make_act_map(CUtensorMap* m, const bf16* base, int B, int H, int W, int C, int TW, int TH, int TN) {
+// (sx, sy = pixel strides in units of pixels of the underlying dense tensor of row length Wfull, height Hfull:
+//  the parity views of EPI_PAR use sx = sy = 2)
+static int make_act_map(CUtensorMap* m, const bf16* base, int B, int H, int W, int C, int TW, int TH, int TN,
+                        int sx = 1, int sy = 1) {
   EncodeTiledFn enc = get_encode_fn();
   if (!enc) { tmat_set_error("conv_tc: cuTensorMapEncodeTiled unavailable"); return TMAT_ERR_CUDA; }
+  const cuuint64_t Wfull = (cuuint64_t)W * sx, Hfull = (cuuint64_t)H * sy;
   cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
-  cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  cuuint64_t strides[3] = {(cuuint64_t)C * 2 * sx, Wfull * C * 2 * sy, Hfull * Wfull * C * 2};
   cuuint32_t box[4] = {(cuuint32_t)KSLAB, (cuuint32_t)TW, (cuuint32_t)TH, (cuuint32_t)TN};
   cuuint32_t estr[4] = {1, 1, 1, 1};
   CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, (void*)base, dims, strides, box, estr,
@@ -445,15 +497,18 @@ static void choose_tile(int B, int H, int W, int* tw_log, int* th_log, int* tn_l
 
 bool conv_tc_supported(const ConvOp& op) {
   if (op.a0_C % KSLAB != 0 || (op.a1 && op.a1_C % KSLAB != 0)) return false;
+  if (op.ngroups < 1 || op.ngroups > CONV_MAX_GROUPS || (op.ngroups > 1 && op.a1)) return false;
   int nk = op.ntaps * (op.a0_C / KSLAB) + (op.a1 ? op.a1_C / KSLAB : 0);
-  if (nk > MAX_KSTEPS) return false;
-  if (op.epi == EPI_HEAD) return op.Npad == 16;
-  return (op.Cout % 64 == 0) && op.Npad == op.Cout;
+  if (nk * op.ngroups > MAX_KSTEPS) return false;
+  if (op.epi == EPI_HEAD) return op.Npad == 16 && op.ngroups == 1;
+  if (op.Cout % 64 != 0) return false;
+  if (op.epi == EPI_PAR) return op.Npad % op.Cout == 0 && op.ngroups * (op.Npad / op.Cout) == 4 && !op.out2 && !op.add_src;
+  return op.Npad == op.Cout && op.ngroups == 1;
 }
 
 template <int BN, int STAGES>
 static int launch_tc(tmat_ctx* ctx, const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& b,
-                     const TcParams& p, cudaStream_t st) {
+                     const TcOutMaps& om, const TcParams& p, cudaStream_t st) {
   using L = TcSmem<BN, STAGES>;
   static bool configured = false;
   if (!configured) {
@@ -467,10 +522,10 @@ static int launch_tc(tmat_ctx* ctx, const CUtensorMap& a0, const CUtensorMap& a1
       if (!ctx->event_pool.empty()) { *e = ctx->event_pool.back(); ctx->event_pool.pop_back(); }
       else CUDA_TRY(cudaEventCreate(e));
     }
-    rec.flops = 2.0 * p.e.B * p.e.H * p.e.W * (double)(p.tiles_n * BN) * (double)(p.nk * KSLAB);
+    rec.flops = 2.0 * p.e.B * p.e.H * p.e.W * (double)(p.ngroups * p.tiles_n * BN) * (double)(p.nk * KSLAB);
     CUDA_TRY(cudaEventRecord(rec.a, st));
   }
-  conv_tc_kernel<BN, STAGES><<<grid, TC_THREADS, L::BYTES, st>>>(a0, a1, b, p);
+  conv_tc_kernel<BN, STAGES><<<grid, TC_THREADS, L::BYTES, st>>>(a0, a1, b, om, p);
   KERNEL_CHECK(ctx);
   if (ctx->profiling) {
     CUDA_TRY(cudaEventRecord(rec.b, st));
@@ -485,34 +540,55 @@ int conv_run_tc(tmat_ctx* ctx, const ConvOp& op, cudaStream_t st) {
   memset(&p, 0, sizeof(p));
   choose_tile(op.B, op.H, op.W, &p.tw_log, &p.th_log, &p.tn_log);
   const int TW = 1 << p.tw_log, TH = 1 << p.th_log, TN = 1 << p.tn_log;
-  int BN = op.epi == EPI_HEAD ? 16 : (op.Cout % 256 == 0 ? 256 : (op.Cout % 128 == 0 ? 128 : 64));
+  int BN = op.epi == EPI_HEAD ? 16 : (op.Npad % 256 == 0 ? 256 : (op.Npad % 128 == 0 ? 128 : 64));
   p.tiles_x = cdiv(op.W, TW);
   p.tiles_y = cdiv(op.H, TH);
   p.tiles_b = cdiv(op.B, TN);
   p.tiles_n = op.Npad / BN;
-  int64_t total = (int64_t)p.tiles_x * p.tiles_y * p.tiles_b * p.tiles_n;
+  p.ngroups = op.ngroups;
+  p.npad = op.Npad;
+  int64_t total = (int64_t)p.tiles_x * p.tiles_y * p.tiles_b * p.tiles_n * p.ngroups;
   TMAT_REQUIRE(total < (1ll << 31), "conv_tc(%s): too many tiles", op.name);
   p.total_tiles = (int)total;
   int nk = 0;
-  for (int t = 0; t < op.ntaps; ++t)
-    for (int c = 0; c < op.a0_C / KSLAB; ++c)
-      p.kstep[nk++] = (uint16_t)(0 | ((op.dy[t] + 1) << 1) | ((op.dx[t] + 1) << 3) | (c << 5));
-  if (op.a1)
-    for (int c = 0; c < op.a1_C / KSLAB; ++c) p.kstep[nk++] = (uint16_t)(1 | (1 << 1) | (1 << 3) | (c << 5));
+  for (int g = 0; g < op.ngroups; ++g) {
+    nk = 0;
+    uint16_t* tab = p.kstep + g * (op.K / KSLAB);
+    for (int t = 0; t < op.ntaps; ++t)
+      for (int c = 0; c < op.a0_C / KSLAB; ++c)
+        tab[nk++] = (uint16_t)(0 | ((op.dy[g][t] + 1) << 1) | ((op.dx[g][t] + 1) << 3) | (c << 5));
+    if (op.a1)
+      for (int c = 0; c < op.a1_C / KSLAB; ++c) tab[nk++] = (uint16_t)(1 | (1 << 1) | (1 << 3) | (c << 5));
+  }
   p.nk = nk;
   TMAT_REQUIRE(nk * KSLAB == op.K, "conv_tc(%s): K mismatch (%d k-steps, K=%d)", op.name, nk, op.K);
   p.e = epi_of(op);
 
   CUtensorMap mA0, mA1, mB;
+  TcOutMaps om;
   TMAT_TRY(make_act_map(&mA0, op.a0, op.B, op.H, op.W, op.a0_C, TW, TH, TN));
   if (op.a1) TMAT_TRY(make_act_map(&mA1, op.a1, op.B, op.H, op.W, op.a1_C, TW, TH, TN));
   else mA1 = mA0;
-  TMAT_TRY(make_weight_map(&mB, op.wmat, op.Npad, op.K, BN));
+  TMAT_TRY(make_weight_map(&mB, op.wmat, op.ngroups * op.Npad, op.K, BN));
+  if (op.epi == EPI_STORE) {
+    TMAT_TRY(make_act_map(&om.m[0], op.out, op.B, op.H, op.W, op.Cout, TW, TH, TN));
+    om.m[1] = om.m[2] = om.m[3] = om.m[0];
+    if (op.out2) TMAT_TRY(make_act_map(&om.m2, op.out2, op.B, op.H, op.W, op.Cout, TW, TH, TN));
+    else om.m2 = om.m[0];
+  } else if (op.epi == EPI_PAR) {
+    for (int q = 0; q < 4; ++q) {
+      const bf16* base = op.out + ((int64_t)(q >> 1) * 2 * op.W + (q & 1)) * op.Cout;
+      TMAT_TRY(make_act_map(&om.m[q], base, op.B, op.H, op.W, op.Cout, TW, TH, TN, 2, 2));
+    }
+    om.m2 = om.m[0];
+  } else {
+    om.m[0] = om.m[1] = om.m[2] = om.m[3] = om.m2 = mA0;   // unused by the head
+  }
   switch (BN) {
-    case 256: return launch_tc<256, 4>(ctx, mA0, mA1, mB, p, st);
-    case 128: return launch_tc<128, 6>(ctx, mA0, mA1, mB, p, st);
-    case 64: return launch_tc<64, 8>(ctx, mA0, mA1, mB, p, st);
-    case 16: return launch_tc<16, 8>(ctx, mA0, mA1, mB, p, st);
+    case 256: return launch_tc<256, 4>(ctx, mA0, mA1, mB, om, p, st);
+    case 128: return launch_tc<128, 6>(ctx, mA0, mA1, mB, om, p, st);
+    case 64: return launch_tc<64, 8>(ctx, mA0, mA1, mB, om, p, st);
+    case 16: return launch_tc<16, 8>(ctx, mA0, mA1, mB, om, p, st);
   }
   return TMAT_ERR_INVALID;
 }

@@ -6,17 +6,23 @@
 //   * BatchNorm (inference, eps = 1e-3) and the conv bias fold into a per-channel scale (multiplied
 //     into the bf16 weights) and a per-channel fp32 shift applied in the epilogue.
 //   * Conv2DTranspose(3, stride 1, same) is a 3x3 correlation with the spatially flipped kernel.
-//   * Up block: up2(BN(ct2)) + conv1x1(up2(prev)) = up2(BN(ct2) + conv1x1(prev)); the 1x1 residual
-//     becomes extra k-steps of the ct2 GEMM and the upsample is a 4-way store in its epilogue.
-//   * Head: a 3x3 conv on an upsampled tensor = four parity-specific 3x3 convs on the low-res tensor
-//     (taps that hit the same low-res pixel are summed), so the 320x320x64 tensor never exists.
+//   * Up block: up2(BN(ct2)) + conv1x1(up2(prev)) = up2(Y), Y = BN(ct2) + conv1x1(prev).  Only the
+//     low-resolution Y is ever stored; the UpSampling2D tensors never exist:
+//       - the next block's ct1, a 3x3 conv on up2(relu(Y)), is evaluated per output-pixel parity on
+//         relu(Y) itself (taps that hit the same low-res pixel are summed: 4 taps per parity instead
+//         of 9), written to the fine grid by parity-strided TMA stores (EPI_PAR);
+//       - the next block's residual conv1x1(up2(up2(Y)..)) commutes with the upsampling: Z = conv1x1(Y)
+//         is a small GEMM at Y's resolution, added as Z[y/2, x/2] in the ct2 epilogue.
+//     In block 0 the residual input has the GEMM's own resolution and rides as extra k-steps of ct2.
+//   * Head: the same parity evaluation (N = 4 parities) on the last block's Y, so the 320x320x64
+//     tensor never exists.
 #include "unet.cuh"
 #include <math.h>
 #include <stdlib.h>
 #include <algorithm>
 
 struct Tap {
-  const void* ptr; int B, H, W, C; int is_f32;
+  const void* ptr; int B, H, W, C; int is_f32; int up;   // up: report the 2x nearest-upsampled tensor
 };
 
 struct tmat_unet {
@@ -27,7 +33,9 @@ struct tmat_unet {
   std::vector<void*> allocs;
   float* stem_w = nullptr; float* stem_shift = nullptr;
   struct Down { int cin, f; float *dw1, *dw2; bf16 *pw1, *pw2, *res; float *sh1, *sh2, *shres; } down[3];
-  struct Up { int cin, f; bf16 *ct1, *ct2res; float *sh1, *sh2; } up[4];
+  // up[0]: ct1 plain [f][9 cin], ct2 = [f][9 f + cin] (residual as extra k-steps);
+  // up[i>0]: ct1 parity-packed [4 f][gtaps cin], ct2 = [f][9 f], z = [f][cin] (residual at low resolution)
+  struct Up { int cin, f; bf16 *ct1, *ct2, *z; float *sh1, *sh2, *shz; int ngroups, gtaps; } up[4];
   bf16* head_w = nullptr; float* head_shift = nullptr;
   std::map<std::string, Tap> taps;
   bool keep_taps = false;
@@ -88,6 +96,36 @@ int upload_bf16(tmat_unet* net, const std::vector<float>& h, bf16** d) {
   return upload(net, hb, d);
 }
 
+// Parity evaluation of a 3x3 'same' convolution on UpSampling2D(2)(x): output pixel (2y+py, 2x+px)
+// reads fine pixel (2y+py+ky-1, ..) = low-res pixel y + lowtap(py, ky): lowtap(0,.) = {-1,0,0},
+// lowtap(1,.) = {0,0,1}.  The fine zero padding coincides with the low-res zero padding.
+int parity_lowtap(int par, int kk) { int v = par + kk - 1; return v < 0 ? -1 : v / 2; }
+
+// Column groups of the parity GEMM: enough parities are merged into one group (sharing the union of
+// their taps, with zero weight blocks) to give the MMA an N of 256 where Cout allows it.
+struct ParityPlan { int ngroups, gtaps, ppg; int8_t dy[CONV_MAX_GROUPS][9], dx[CONV_MAX_GROUPS][9]; };
+ParityPlan parity_plan(int f) {
+  ParityPlan pl;
+  memset(&pl, 0, sizeof(pl));
+  pl.ngroups = f >= 256 ? 4 : (f >= 128 ? 2 : 1);
+  pl.ppg = 4 / pl.ngroups;
+  for (int g = 0; g < pl.ngroups; ++g) {
+    int n = 0;
+    for (int ly = -1; ly <= 1; ++ly)
+      for (int lx = -1; lx <= 1; ++lx) {
+        bool used = false;
+        for (int ql = 0; ql < pl.ppg; ++ql) {
+          int q = g * pl.ppg + ql, py = q >> 1, px = q & 1;
+          bool uy = (ly == py - 1 || ly == py), ux = (lx == px - 1 || lx == px);
+          used = used || (uy && ux);
+        }
+        if (used) { pl.dy[g][n] = (int8_t)ly; pl.dx[g][n] = (int8_t)lx; ++n; }
+      }
+    pl.gtaps = n;   // 4, 6 or 9 -- the same for every group of a plan
+  }
+  return pl;
+}
+
 int pack_weights(tmat_unet* net, const WeightSet& ws) {
   const int ch = net->desc.channels;
   const int* fc = net->fc;
@@ -145,18 +183,42 @@ int pack_weights(tmat_unet* net, const WeightSet& ws) {
     TMAT_TRY(ws.get(p + ".ct1.kernel", 9ll * f * cin, &k));
     TMAT_TRY(ws.get(p + ".ct1.bias", f, &b));
     TMAT_TRY(bn_fold(ws, p + ".bn1", b, f, scale, shift));
-    {
+    auto wc1 = [&](int ky, int kx, int co, int c) {
+      return k[((size_t)((2 - ky) * 3 + (2 - kx)) * f + co) * cin + c] * scale[co];
+    };
+    if (i == 0) {
       int K = 9 * cin;
       std::vector<float> w((size_t)f * K);
       for (int co = 0; co < f; ++co)
         for (int ky = 0; ky < 3; ++ky)
           for (int kx = 0; kx < 3; ++kx)
-            for (int c = 0; c < cin; ++c)
-              w[(size_t)co * K + (ky * 3 + kx) * cin + c] =
-                  k[((size_t)((2 - ky) * 3 + (2 - kx)) * f + co) * cin + c] * scale[co];
+            for (int c = 0; c < cin; ++c) w[(size_t)co * K + (ky * 3 + kx) * cin + c] = wc1(ky, kx, co, c);
+      U.ngroups = 1; U.gtaps = 9;
       TMAT_TRY(upload_bf16(net, w, &U.ct1));
-      TMAT_TRY(upload(net, shift, &U.sh1));
+    } else {
+      // input is UpSampling2D(2) of the previous block's low-res output: evaluate per output parity
+      ParityPlan pl = parity_plan(f);
+      U.ngroups = pl.ngroups; U.gtaps = pl.gtaps;
+      int K = pl.gtaps * cin;
+      std::vector<float> w((size_t)4 * f * K, 0.f);
+      for (int g = 0; g < pl.ngroups; ++g)
+        for (int ql = 0; ql < pl.ppg; ++ql) {
+          int q = g * pl.ppg + ql, py = q >> 1, px = q & 1;
+          for (int t = 0; t < pl.gtaps; ++t)
+            for (int ky = 0; ky < 3; ++ky) {
+              if (parity_lowtap(py, ky) != pl.dy[g][t]) continue;
+              for (int kx = 0; kx < 3; ++kx) {
+                if (parity_lowtap(px, kx) != pl.dx[g][t]) continue;
+                for (int co = 0; co < f; ++co) {
+                  float* dst = &w[((size_t)(g * pl.ppg + ql) * f + co) * K + (size_t)t * cin];
+                  for (int c = 0; c < cin; ++c) dst[c] += wc1(ky, kx, co, c);
+                }
+              }
+            }
+        }
+      TMAT_TRY(upload_bf16(net, w, &U.ct1));
     }
+    TMAT_TRY(upload(net, shift, &U.sh1));
     const float *kr, *br;
     TMAT_TRY(ws.get(p + ".ct2.kernel", 9ll * f * f, &k));
     TMAT_TRY(ws.get(p + ".ct2.bias", f, &b));
@@ -164,7 +226,7 @@ int pack_weights(tmat_unet* net, const WeightSet& ws) {
     TMAT_TRY(ws.get(p + ".res.kernel", (int64_t)cin * f, &kr));
     TMAT_TRY(ws.get(p + ".res.bias", f, &br));
     {
-      int K = 9 * f + cin;
+      int K = 9 * f + (i == 0 ? cin : 0);
       std::vector<float> w((size_t)f * K);
       for (int co = 0; co < f; ++co) {
         for (int ky = 0; ky < 3; ++ky)
@@ -172,11 +234,21 @@ int pack_weights(tmat_unet* net, const WeightSet& ws) {
             for (int c = 0; c < f; ++c)
               w[(size_t)co * K + (ky * 3 + kx) * f + c] =
                   k[((size_t)((2 - ky) * 3 + (2 - kx)) * f + co) * f + c] * scale[co];
-        for (int c = 0; c < cin; ++c) w[(size_t)co * K + 9 * f + c] = kr[(size_t)c * f + co];
-        shift[co] += br[co];
+        if (i == 0) {
+          for (int c = 0; c < cin; ++c) w[(size_t)co * K + 9 * f + c] = kr[(size_t)c * f + co];
+          shift[co] += br[co];
+        }
       }
-      TMAT_TRY(upload_bf16(net, w, &U.ct2res));
+      TMAT_TRY(upload_bf16(net, w, &U.ct2));
       TMAT_TRY(upload(net, shift, &U.sh2));
+    }
+    U.z = nullptr; U.shz = nullptr;
+    if (i > 0) {
+      std::vector<float> wz((size_t)f * cin), sz(br, br + f);
+      for (int co = 0; co < f; ++co)
+        for (int c = 0; c < cin; ++c) wz[(size_t)co * cin + c] = kr[(size_t)c * f + co];
+      TMAT_TRY(upload_bf16(net, wz, &U.z));
+      TMAT_TRY(upload(net, sz, &U.shz));
     }
     cin = f;
   }
@@ -213,18 +285,25 @@ const int8_t TAP_DY[9] = {-1, -1, -1, 0, 0, 0, 1, 1, 1};
 const int8_t TAP_DX[9] = {-1, 0, 1, -1, 0, 1, -1, 0, 1};
 
 void set_taps3x3(ConvOp& op) {
-  op.ntaps = 9;
-  for (int t = 0; t < 9; ++t) { op.dy[t] = TAP_DY[t]; op.dx[t] = TAP_DX[t]; }
+  op.ngroups = 1; op.ntaps = 9;
+  for (int t = 0; t < 9; ++t) { op.dy[0][t] = TAP_DY[t]; op.dx[0][t] = TAP_DX[t]; }
 }
-void set_tap1x1(ConvOp& op) { op.ntaps = 1; op.dy[0] = 0; op.dx[0] = 0; }
+void set_tap1x1(ConvOp& op) { op.ngroups = 1; op.ntaps = 1; op.dy[0][0] = 0; op.dx[0][0] = 0; }
+void set_taps_parity(ConvOp& op, int f) {
+  ParityPlan pl = parity_plan(f);
+  op.ngroups = pl.ngroups; op.ntaps = pl.gtaps;
+  memcpy(op.dy, pl.dy, sizeof(op.dy));
+  memcpy(op.dx, pl.dx, sizeof(op.dx));
+  op.Cout = f; op.Npad = pl.ppg * f; op.epi = EPI_PAR;
+}
 
 int run_op(tmat_ctx* ctx, tmat_unet* net, const ConvOp& op, cudaStream_t st) {
   if (net->use_tc) return conv_run_tc(ctx, op, st);
   return conv_run_simt(ctx, op, st);
 }
 
-void record(tmat_unet* net, const char* name, const void* p, int B, int H, int W, int C, int f32 = 0) {
-  if (net->keep_taps) net->taps[name] = Tap{p, B, H, W, C, f32};
+void record(tmat_unet* net, const char* name, const void* p, int B, int H, int W, int C, int f32 = 0, int up = 0) {
+  if (net->keep_taps) net->taps[name] = Tap{p, B, H, W, C, f32, up};
 }
 
 // bytes of activation scratch one forward over B patches takes from the arena
@@ -233,22 +312,20 @@ size_t forward_scratch_bytes(const tmat_unet* net, int B) {
   size_t S = net->desc.patch / 2;
   size_t px = (size_t)B * S * S;
   size_t total = px * fc[0] * 2 + 4096;            // stem out
-  size_t s2 = px;
   int cin = fc[0];
   for (int i = 0; i < 3; ++i) {
     int f = fc[i + 1];
-    total += s2 * cin * 2 + s2 / 4 * cin * 2;        // dw1 out, subsampled input
-    total += s2 * f * 2 * 3;                         // pw1 out, dw2 out, pw2 out
-    total += s2 / 4 * f * 2 * 2;                     // block out (P and, for the last block, R)
+    total += px * cin * 2 + px / 4 * cin * 2;        // dw1 out, subsampled input
+    total += px * f * 2 * 3;                         // pw1 out, dw2 out, pw2 out
+    total += px / 4 * f * 2 * 3;                     // pooled, block out (P and, for the last block, R)
     total += 8 * 512;
-    s2 /= 4; cin = f;
+    px /= 4; cin = f;
   }
   for (int i = 0; i < 4; ++i) {
     int f = fc[3 - i];
-    total += s2 * f * 2;                             // ct1 out
-    total += (i < 3 ? s2 * 4 * f * 2 * 2 : s2 * f * 2);
+    if (i > 0) { total += px * f * 2; px *= 4; }     // Z at the previous resolution
+    total += px * f * 2 * 3;                         // ct1 out, Y (P and R)
     total += 4 * 512;
-    s2 *= 4;
   }
   return total + (1 << 16);
 }
@@ -268,12 +345,13 @@ int unet_forward(tmat_ctx* ctx, tmat_unet* net, const StemSrc& src, int B, float
   for (int i = 0; i < 3; ++i) {
     auto& D = net->down[i];
     size_t px = (size_t)B * S * S;
-    bf16 *d1, *xs, *a1, *d2, *b2, *out, *outr = nullptr;
+    bf16 *d1, *xs, *a1, *d2, *b2, *pooled, *out, *outr = nullptr;
     TMAT_TRY(arena_get(ctx, px * D.cin, &d1));
     TMAT_TRY(arena_get(ctx, px / 4 * D.cin, &xs));
     TMAT_TRY(arena_get(ctx, px * D.f, &a1));
     TMAT_TRY(arena_get(ctx, px * D.f, &d2));
     TMAT_TRY(arena_get(ctx, px * D.f, &b2));
+    TMAT_TRY(arena_get(ctx, px / 4 * D.f, &pooled));
     TMAT_TRY(arena_get(ctx, px / 4 * D.f, &out));
     if (i == 2) TMAT_TRY(arena_get(ctx, px / 4 * D.f, &outr));
     // [ReLU] -> depthwise 3x3 ; also the stride-2 sample of the block input for the residual conv
@@ -291,44 +369,59 @@ int unet_forward(tmat_ctx* ctx, tmat_unet* net, const StemSrc& src, int B, float
     op2.out = b2;
     TMAT_TRY(run_op(ctx, net, op2, st));
     record(net, (std::string("down") + std::to_string(i) + ".b2").c_str(), b2, B, S, S, D.f);
-    // residual 1x1 stride-2 conv + MaxPool(3, 2, same)(b2)
+    // MaxPool(3, 2, same)(b2) + residual 1x1 stride-2 conv of the block input
+    TMAT_TRY(maxpool_run(ctx, b2, B, S, D.f, pooled, st));
     ConvOp op3;
     op3.name = "down.res"; op3.a0 = xs; op3.a0_C = D.cin; op3.B = B; op3.H = S / 2; op3.W = S / 2; set_tap1x1(op3);
-    op3.wmat = D.res; op3.K = D.cin; op3.shift = D.shres; op3.Cout = op3.Npad = D.f; op3.epi = EPI_POOLADD;
-    op3.relu = 0; op3.pool_src = b2; op3.out = out; op3.out2 = outr;
+    op3.wmat = D.res; op3.K = D.cin; op3.shift = D.shres; op3.Cout = op3.Npad = D.f; op3.epi = EPI_STORE;
+    op3.relu = 0; op3.add_src = pooled; op3.add_shift = 0; op3.out = out; op3.out2 = outr;
     TMAT_TRY(run_op(ctx, net, op3, st));
     S /= 2;
     record(net, (std::string("down") + std::to_string(i)).c_str(), out, B, S, S, D.f);
     P = out; R = outr;
   }
+  // up blocks: block i runs at resolution S and leaves its LOW-RES output Y_i = BN(ct2) + residual
+  // (pre-activation P and ReLU'd R); the reference's block output is UpSampling2D(2)(Y_i).
   for (int i = 0; i < 4; ++i) {
     auto& U = net->up[i];
+    bf16* Z = nullptr;
+    if (i > 0) {
+      // residual of this block at the previous block's resolution: Z = conv1x1(Y_{i-1}) + bias
+      TMAT_TRY(arena_get(ctx, (size_t)B * S * S * U.f, &Z));
+      ConvOp oz;
+      oz.name = "up.res"; oz.a0 = P; oz.a0_C = U.cin; oz.B = B; oz.H = S; oz.W = S; set_tap1x1(oz);
+      oz.wmat = U.z; oz.K = U.cin; oz.shift = U.shz; oz.Cout = oz.Npad = U.f; oz.epi = EPI_STORE; oz.relu = 0;
+      oz.out = Z;
+      TMAT_TRY(run_op(ctx, net, oz, st));
+    }
+    const int Sin = S;              // resolution of the block's stored input (R, P)
+    if (i > 0) S *= 2;
     size_t px = (size_t)B * S * S;
     bf16 *a1, *outp, *outr = nullptr;
     TMAT_TRY(arena_get(ctx, px * U.f, &a1));
     ConvOp op;
-    op.name = "up.ct1"; op.a0 = R; op.a0_C = U.cin; op.B = B; op.H = S; op.W = S; set_taps3x3(op);
-    op.wmat = U.ct1; op.K = 9 * U.cin; op.shift = U.sh1; op.Cout = op.Npad = U.f; op.epi = EPI_STORE; op.relu = 1;
-    op.out = a1;
+    op.name = "up.ct1"; op.a0 = R; op.a0_C = U.cin; op.B = B; op.H = Sin; op.W = Sin;
+    op.wmat = U.ct1; op.shift = U.sh1; op.relu = 1; op.out = a1;
+    if (i == 0) {
+      set_taps3x3(op);
+      op.K = 9 * U.cin; op.Cout = op.Npad = U.f; op.epi = EPI_STORE;
+    } else {
+      set_taps_parity(op, U.f);
+      op.K = op.ntaps * U.cin;
+    }
     TMAT_TRY(run_op(ctx, net, op, st));
     record(net, (std::string("up") + std::to_string(i) + ".r1").c_str(), a1, B, S, S, U.f);
+    TMAT_TRY(arena_get(ctx, px * U.f, &outp));
+    if (i < 3) TMAT_TRY(arena_get(ctx, px * U.f, &outr));
     ConvOp op2;
-    op2.name = "up.ct2"; op2.a0 = a1; op2.a0_C = U.f; op2.a1 = P; op2.a1_C = U.cin; op2.B = B; op2.H = S; op2.W = S;
+    op2.name = "up.ct2"; op2.a0 = a1; op2.a0_C = U.f; op2.B = B; op2.H = S; op2.W = S;
     set_taps3x3(op2);
-    op2.wmat = U.ct2res; op2.K = 9 * U.f + U.cin; op2.shift = U.sh2; op2.Cout = op2.Npad = U.f; op2.relu = 0;
-    if (i < 3) {
-      TMAT_TRY(arena_get(ctx, px * 4 * U.f, &outp));
-      TMAT_TRY(arena_get(ctx, px * 4 * U.f, &outr));
-      op2.epi = EPI_UP2; op2.out = outp; op2.out2 = outr;
-      TMAT_TRY(run_op(ctx, net, op2, st));
-      S *= 2;
-      record(net, (std::string("up") + std::to_string(i)).c_str(), outp, B, S, S, U.f);
-    } else {
-      TMAT_TRY(arena_get(ctx, px * U.f, &outp));
-      op2.epi = EPI_STORE; op2.out = outp;
-      TMAT_TRY(run_op(ctx, net, op2, st));
-      record(net, "up3.lowres", outp, B, S, S, U.f);
-    }
+    op2.wmat = U.ct2; op2.shift = U.sh2; op2.Cout = op2.Npad = U.f; op2.relu = 0; op2.epi = EPI_STORE;
+    op2.out = outp; op2.out2 = outr;
+    if (i == 0) { op2.a1 = P; op2.a1_C = U.cin; op2.K = 9 * U.f + U.cin; }
+    else { op2.K = 9 * U.f; op2.add_src = Z; op2.add_shift = 1; }
+    TMAT_TRY(run_op(ctx, net, op2, st));
+    record(net, (std::string("up") + std::to_string(i)).c_str(), outp, B, S, S, U.f, 0, 1);
     P = outp; R = outr;
   }
   ConvOp oh;
@@ -542,9 +635,17 @@ extern "C" int tmat_stp_predict_host(tmat_ctx* ctx, tmat_unet* net, const float*
 }
 
 namespace {
-__global__ void tap_to_f32(const bf16* in, int64_t n, float* out) {
+// bf16 (B,H,W,C) -> float32, optionally 2x nearest-upsampled to (B,2H,2W,C)
+__global__ void tap_to_f32(const bf16* in, int64_t n, int H, int W, int C, int up, float* out) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) out[i] = __bfloat162float(in[i]);
+  if (i >= n) return;
+  if (!up) { out[i] = __bfloat162float(in[i]); return; }
+  int c = (int)(i % C);
+  int64_t pix = i / C;
+  int x = (int)(pix % (2 * W));
+  int y = (int)((pix / (2 * W)) % (2 * H));
+  int64_t b = pix / ((int64_t)4 * W * H);
+  out[i] = __bfloat162float(in[((b * H + (y >> 1)) * W + (x >> 1)) * C + c]);
 }
 }  // namespace
 
@@ -554,7 +655,7 @@ extern "C" int tmat_unet_debug_tap(tmat_ctx* ctx, tmat_unet* net, const char* na
   auto it = net->taps.find(name);
   TMAT_REQUIRE(it != net->taps.end(), "tmat_unet_debug_tap: no tap '%s' (taps are kept for single-chunk forwards)", name);
   const Tap& t = it->second;
-  int64_t n = (int64_t)t.B * t.H * t.W * t.C;
+  int64_t n = (int64_t)t.B * t.H * t.W * t.C * (t.up ? 4 : 1);
   *n_written = n;
   if (!out_host) return TMAT_OK;
   TMAT_REQUIRE(capacity >= n, "tmat_unet_debug_tap: capacity %lld < %lld", (long long)capacity, (long long)n);
@@ -566,7 +667,7 @@ extern "C" int tmat_unet_debug_tap(tmat_ctx* ctx, tmat_unet* net, const char* na
   }
   float* tmp;
   CUDA_TRY(cudaMalloc((void**)&tmp, n * 4));
-  tap_to_f32<<<(unsigned)cdiv64(n, 256), 256>>>((const bf16*)t.ptr, n, tmp);
+  tap_to_f32<<<(unsigned)cdiv64(n, 256), 256>>>((const bf16*)t.ptr, n, t.H, t.W, t.C, t.up, tmp);
   cudaError_t e = cudaMemcpy(out_host, tmp, n * 4, cudaMemcpyDeviceToHost);
   cudaFree(tmp);
   CUDA_TRY(e);
@@ -615,40 +716,53 @@ __global__ void max_abs_diff_kernel(const T* a, const T* b, int64_t n, float* ou
 }
 }  // namespace
 
+// epi: 0 = EPI_STORE, 1 = EPI_PAR (parity groups chosen from Cout as in the UNet), 3 = EPI_HEAD.
+// addend: 0 none, 1 same-resolution addend, 2 half-resolution addend (EPI_STORE only).
 extern "C" int tmat_debug_conv_selftest(tmat_ctx* ctx, int B, int H, int W, int C0, int C1, int Cout, int ntaps,
-                                        int epi, int relu, int dual, uint64_t seed, double* max_abs_diff,
-                                        double* max_abs_ref) {
+                                        int epi, int relu, int dual, int addend, uint64_t seed,
+                                        double* max_abs_diff, double* max_abs_ref) {
   TMAT_REQUIRE(ctx && max_abs_diff && max_abs_ref, "tmat_debug_conv_selftest: NULL argument");
   TMAT_REQUIRE(ntaps == 1 || ntaps == 9, "tmat_debug_conv_selftest: ntaps must be 1 or 9");
+  TMAT_REQUIRE(epi == EPI_STORE || epi == EPI_PAR || epi == EPI_HEAD, "tmat_debug_conv_selftest: bad epi %d", epi);
   TMAT_TRY(arena_reset(ctx));
   ConvOp op;
   op.name = "selftest";
   op.B = B; op.H = H; op.W = W; op.a0_C = C0; op.a1_C = C1;
-  if (ntaps == 9) set_taps3x3(op); else set_tap1x1(op);
-  op.K = ntaps * C0 + C1;
   op.epi = epi; op.relu = relu;
-  op.Cout = (epi == EPI_HEAD) ? 4 : Cout;
-  op.Npad = (epi == EPI_HEAD) ? 16 : Cout;
+  if (epi == EPI_PAR) {
+    TMAT_REQUIRE(C1 == 0 && !dual && !addend, "tmat_debug_conv_selftest: EPI_PAR takes no a1 / out2 / addend");
+    set_taps_parity(op, Cout);
+    op.K = op.ntaps * C0;
+  } else {
+    if (ntaps == 9) set_taps3x3(op); else set_tap1x1(op);
+    op.K = ntaps * C0 + C1;
+    op.Cout = (epi == EPI_HEAD) ? 4 : Cout;
+    op.Npad = (epi == EPI_HEAD) ? 16 : Cout;
+  }
+  const int rows = op.ngroups * op.Npad;
   size_t px = (size_t)B * H * W;
-  bf16 *a0, *a1 = nullptr, *w, *pool = nullptr;
+  bf16 *a0, *a1 = nullptr, *w, *add = nullptr;
   float* shift;
   TMAT_TRY(arena_get(ctx, px * C0, &a0));
   if (C1) TMAT_TRY(arena_get(ctx, px * C1, &a1));
-  TMAT_TRY(arena_get(ctx, (size_t)op.Npad * op.K, &w));
-  TMAT_TRY(arena_get(ctx, (size_t)op.Npad, &shift));
+  TMAT_TRY(arena_get(ctx, (size_t)rows * op.K, &w));
+  TMAT_TRY(arena_get(ctx, (size_t)rows, &shift));
   auto fill = [&](bf16* p, size_t n, uint64_t s, float sc) {
     fill_random_bf16<<<(unsigned)cdiv64(n, 256), 256>>>(p, (int64_t)n, s, sc);
   };
   fill(a0, px * C0, seed + 1, 1.f);
   if (C1) fill(a1, px * C1, seed + 2, 1.f);
-  fill(w, (size_t)op.Npad * op.K, seed + 3, 1.f / sqrtf((float)op.K));
-  fill_random_f32<<<1, 256>>>(shift, op.Npad, seed + 4, 0.5f);
-  size_t out_elems = px * op.Cout * (epi == EPI_UP2 ? 4 : 1);
-  if (epi == EPI_POOLADD) {
-    TMAT_TRY(arena_get(ctx, px * 4 * Cout, &pool));
-    fill(pool, px * 4 * Cout, seed + 5, 1.f);
+  fill(w, (size_t)rows * op.K, seed + 3, 1.f / sqrtf((float)op.K));
+  fill_random_f32<<<cdiv(rows, 256), 256>>>(shift, rows, seed + 4, 0.5f);
+  size_t out_elems = px * op.Cout * (epi == EPI_PAR ? 4 : 1);
+  if (addend) {
+    int s = addend - 1;
+    size_t n = (size_t)B * ((H + s) >> s) * ((W + s) >> s) * Cout;
+    TMAT_TRY(arena_get(ctx, n, &add));
+    fill(add, n, seed + 5, 1.f);
+    op.add_src = add; op.add_shift = s;
   }
-  op.a0 = a0; op.a1 = a1; op.wmat = w; op.shift = shift; op.pool_src = pool;
+  op.a0 = a0; op.a1 = a1; op.wmat = w; op.shift = shift;
   float* stats;
   TMAT_TRY(arena_get(ctx, 2, &stats));
   CUDA_TRY(cudaMemsetAsync(stats, 0, 8, 0));

@@ -11,28 +11,35 @@
 typedef __nv_bfloat16 bf16;
 
 enum EpiMode {
-  EPI_STORE = 0,    // out[b,y,x,:]  (same resolution)
-  EPI_UP2 = 1,      // out[b,2y+{0,1},2x+{0,1},:]   UpSampling2D(2) fused (models.py:157)
-  EPI_POOLADD = 2,  // v += MaxPool(3, s2, same)(pool_src)[b,y,x,:]   (models.py:139-146)
+  EPI_STORE = 0,    // out[b,y,x,:] (same resolution), optional addend and ReLU'd second copy
+  EPI_PAR = 1,      // parity store: GEMM column block q = (py,px) -> out[b,2y+py,2x+px,:]; this is a
+                    // 3x3 convolution applied to UpSampling2D(2)(a0) (models.py:150-157) evaluated on
+                    // the low-resolution tensor with per-parity summed taps
   EPI_HEAD = 3      // 4 output-pixel parities -> sigmoid -> float32 (B, 2H, 2W)  (models.py:166)
 };
 
+constexpr int CONV_MAX_GROUPS = 4;
+
 struct ConvOp {
-  // implicit-GEMM A operand: ntaps shifted views of a0 (channels a0_C), then one 1x1 view of a1
+  // implicit-GEMM A operand: per group g, gtaps shifted views of a0 (channels a0_C); then (only
+  // when ngroups == 1) one 1x1 view of a1
   const bf16* a0 = nullptr; int a0_C = 0;
   const bf16* a1 = nullptr; int a1_C = 0;
   int B = 0, H = 0, W = 0;          // pixel grid of the GEMM rows (= resolution of a0/a1)
-  int ntaps = 1;
-  int8_t dy[9] = {0}, dx[9] = {0};
-  const bf16* wmat = nullptr;       // [Npad][K] K-major, BN scale folded in; K = ntaps*a0_C + a1_C
+  int ngroups = 1;                  // independent column groups with their own tap lists
+  int ntaps = 1;                    // taps per group
+  int8_t dy[CONV_MAX_GROUPS][9] = {{0}}, dx[CONV_MAX_GROUPS][9] = {{0}};
+  const bf16* wmat = nullptr;       // [ngroups*Npad][K] K-major, BN scale folded in; K = ntaps*a0_C + a1_C
   int K = 0;
-  const float* shift = nullptr;     // [Npad] bias / BN shift
-  int Cout = 0, Npad = 0;
+  const float* shift = nullptr;     // [Cout] bias / BN shift (EPI_HEAD: [Npad])
+  int Cout = 0;                     // channels of the output tensor
+  int Npad = 0;                     // GEMM columns per group (EPI_STORE: Cout; EPI_PAR: Cout * parities per group)
   int epi = EPI_STORE;
   int relu = 0;                     // ReLU on `out`
   bf16* out = nullptr;
-  bf16* out2 = nullptr;             // optional: ReLU'd copy (when `out` must stay pre-activation)
-  const bf16* pool_src = nullptr;   // EPI_POOLADD: (B, 2H, 2W, Cout)
+  bf16* out2 = nullptr;             // EPI_STORE only: ReLU'd copy (when `out` must stay pre-activation)
+  const bf16* add_src = nullptr;    // EPI_STORE only: v += add_src[b, y >> add_shift, x >> add_shift, :]
+  int add_shift = 0;                //   add_src has shape (B, ceil(H / 2^s), ceil(W / 2^s), Cout)
   float* out_f32 = nullptr;         // EPI_HEAD
   int logits = 0;
   const char* name = "";
@@ -42,10 +49,12 @@ struct ConvOp {
 struct EpiParams {
   int mode, relu, logits;
   int B, H, W, Cout;
+  int ppg;                          // EPI_PAR: parities per group (Npad / Cout)
+  int add_shift;
   const float* shift;
   bf16* out;
   bf16* out2;
-  const bf16* pool_src;
+  const bf16* add_src;
   float* out_f32;
 };
 
@@ -53,7 +62,9 @@ static inline EpiParams epi_of(const ConvOp& op) {
   EpiParams e;
   e.mode = op.epi; e.relu = op.relu; e.logits = op.logits;
   e.B = op.B; e.H = op.H; e.W = op.W; e.Cout = op.Cout;
-  e.shift = op.shift; e.out = op.out; e.out2 = op.out2; e.pool_src = op.pool_src; e.out_f32 = op.out_f32;
+  e.ppg = (op.epi == EPI_PAR) ? op.Npad / op.Cout : 1;
+  e.add_shift = op.add_shift;
+  e.shift = op.shift; e.out = op.out; e.out2 = op.out2; e.add_src = op.add_src; e.out_f32 = op.out_f32;
   return e;
 }
 
@@ -80,3 +91,6 @@ int stem_run(tmat_ctx* ctx, const StemSrc& src, int B, int ws, const float* w /*
 // optional sub = in[:, ::2, ::2, :] (raw, for the stride-2 1x1 residual conv).
 int dwconv_run(tmat_ctx* ctx, const bf16* in, int B, int S, int C, const float* w /*[9][C]*/, int relu_in,
                bf16* out, bf16* sub, cudaStream_t st);
+// MaxPool2D(3, strides=2, padding="same") on an even size (pads 0 before / 1 after, padding excluded
+// from the max; models.py:139): in (B,S,S,C) bf16 -> out (B,S/2,S/2,C) bf16.
+int maxpool_run(tmat_ctx* ctx, const bf16* in, int B, int S, int C, bf16* out, cudaStream_t st);

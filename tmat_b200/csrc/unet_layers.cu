@@ -8,65 +8,87 @@ namespace {
 
 // ---- stem ------------------------------------------------------------------------------------
 // TF 'same' with stride 2 on an even size pads 0 before / 1 after: out[y,x] = sum in[2y+ky, 2x+kx].
-// One thread computes 8 output channels of one output pixel (16-byte bf16 store).
+// A block produces a strip of STEM_ROWS output rows x 32 output columns of one patch: the input
+// window (2*STEM_ROWS+1 rows x 65 columns) is fetched once into shared memory -- through the D4 tile
+// map when the patches come straight from the image -- and every thread computes 8 output channels
+// of one column for all rows of the strip with its 72 weights in registers.  A warp stores
+// 4 pixels x 128 bytes = 512 contiguous bytes.
+constexpr int STEM_ROWS = 8;
+constexpr int STEM_COLS = 32;
+
 __global__ void __launch_bounds__(256) stem_kernel(StemSrc src, int B, int ws, const float* __restrict__ w,
                                                    const float* __restrict__ shift, int C0,
                                                    bf16* __restrict__ out) {
+  constexpr int IR = 2 * STEM_ROWS + 1, IC = 2 * STEM_COLS + 1;
+  __shared__ float tile[IR][IC + 2];
   const int S = ws >> 1;
-  const int groups = C0 >> 3;
-  int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  int64_t total = (int64_t)B * S * S * groups;
-  if (idx >= total) return;
-  int cg = (int)(idx % groups);
-  int64_t pix = idx / groups;
-  int x = (int)(pix % S);
-  int y = (int)((pix / S) % S);
-  int b = (int)(pix / ((int64_t)S * S));
-  float in[9];
-  if (src.use_geom) {
-    const StpGeom& G = src.geom;
-    int p = src.first_patch + b;
-    int per = G.tiles_per_orient();
-    int g = p / per, t = p - g * per;
-    int tc = G.tile_cols(g);
-    int ti = t / tc, tj = t - ti * tc;
-    float minval = src.minmax[0];
-#pragma unroll
-    for (int ky = 0; ky < 3; ++ky)
-#pragma unroll
-      for (int kx = 0; kx < 3; ++kx) {
-        int i = 2 * y + ky, j = 2 * x + kx;
-        in[ky * 3 + kx] = (i < ws && j < ws) ? stp_tile_pixel(src.img, G, g, ti, tj, i, j, minval) : 0.f;
-      }
-  } else {
-    const float* pp = src.patches + (int64_t)b * ws * ws;
-#pragma unroll
-    for (int ky = 0; ky < 3; ++ky)
-#pragma unroll
-      for (int kx = 0; kx < 3; ++kx) {
-        int i = 2 * y + ky, j = 2 * x + kx;
-        in[ky * 3 + kx] = (i < ws && j < ws) ? __ldg(pp + (int64_t)i * ws + j) : 0.f;
-      }
+  const int b = blockIdx.z;
+  const int y0 = blockIdx.y * STEM_ROWS, x0 = blockIdx.x * STEM_COLS;
+  {
+    int g = 0, ti = 0, tj = 0;
+    float minval = 0.f;
+    const float* pp = nullptr;
+    if (src.use_geom) {
+      const StpGeom& G = src.geom;
+      int p = src.first_patch + b;
+      int per = G.tiles_per_orient();
+      g = p / per;
+      int t = p - g * per;
+      int tc = G.tile_cols(g);
+      ti = t / tc; tj = t - ti * tc;
+      minval = src.minmax[0];
+    } else {
+      pp = src.patches + (int64_t)b * ws * ws;
+    }
+    for (int idx = threadIdx.x; idx < IR * IC; idx += blockDim.x) {
+      int r = idx / IC, c = idx - r * IC;
+      int i = 2 * y0 + r, j = 2 * x0 + c;
+      float v = 0.f;
+      if (i < ws && j < ws)
+        v = src.use_geom ? stp_tile_pixel(src.img, src.geom, g, ti, tj, i, j, minval) : __ldg(pp + (int64_t)i * ws + j);
+      tile[r][c] = v;
+    }
   }
-  float acc[8];
-#pragma unroll
-  for (int c = 0; c < 8; ++c) acc[c] = __ldg(shift + cg * 8 + c);
+  __syncthreads();
+  const int groups = C0 >> 3;                  // 8 when C0 == 64
+  const int px_per_pass = blockDim.x / groups;
+  const int cg = threadIdx.x % groups;
+  float wr[9][8], sh[8];
 #pragma unroll
   for (int t = 0; t < 9; ++t) {
     const float4* wp = reinterpret_cast<const float4*>(w + t * C0 + cg * 8);
     float4 w0 = __ldg(wp), w1 = __ldg(wp + 1);
-    acc[0] = fmaf(in[t], w0.x, acc[0]); acc[1] = fmaf(in[t], w0.y, acc[1]);
-    acc[2] = fmaf(in[t], w0.z, acc[2]); acc[3] = fmaf(in[t], w0.w, acc[3]);
-    acc[4] = fmaf(in[t], w1.x, acc[4]); acc[5] = fmaf(in[t], w1.y, acc[5]);
-    acc[6] = fmaf(in[t], w1.z, acc[6]); acc[7] = fmaf(in[t], w1.w, acc[7]);
+    wr[t][0] = w0.x; wr[t][1] = w0.y; wr[t][2] = w0.z; wr[t][3] = w0.w;
+    wr[t][4] = w1.x; wr[t][5] = w1.y; wr[t][6] = w1.z; wr[t][7] = w1.w;
   }
-  uint4 o;
-  __nv_bfloat162 h;
-  h = __floats2bfloat162_rn(fmaxf(acc[0], 0.f), fmaxf(acc[1], 0.f)); o.x = *reinterpret_cast<uint32_t*>(&h);
-  h = __floats2bfloat162_rn(fmaxf(acc[2], 0.f), fmaxf(acc[3], 0.f)); o.y = *reinterpret_cast<uint32_t*>(&h);
-  h = __floats2bfloat162_rn(fmaxf(acc[4], 0.f), fmaxf(acc[5], 0.f)); o.z = *reinterpret_cast<uint32_t*>(&h);
-  h = __floats2bfloat162_rn(fmaxf(acc[6], 0.f), fmaxf(acc[7], 0.f)); o.w = *reinterpret_cast<uint32_t*>(&h);
-  *reinterpret_cast<uint4*>(out + pix * C0 + cg * 8) = o;
+#pragma unroll
+  for (int c = 0; c < 8; ++c) sh[c] = __ldg(shift + cg * 8 + c);
+  for (int xl = threadIdx.x / groups; xl < STEM_COLS; xl += px_per_pass) {
+    const int x = x0 + xl;
+    if (x >= S) break;
+    for (int r = 0; r < STEM_ROWS; ++r) {
+      const int y = y0 + r;
+      if (y >= S) break;
+      float acc[8];
+#pragma unroll
+      for (int c = 0; c < 8; ++c) acc[c] = sh[c];
+#pragma unroll
+      for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+        for (int kx = 0; kx < 3; ++kx) {
+          float v = tile[2 * r + ky][2 * xl + kx];
+#pragma unroll
+          for (int c = 0; c < 8; ++c) acc[c] = fmaf(v, wr[ky * 3 + kx][c], acc[c]);
+        }
+      uint4 o;
+      __nv_bfloat162 h;
+      h = __floats2bfloat162_rn(fmaxf(acc[0], 0.f), fmaxf(acc[1], 0.f)); o.x = *reinterpret_cast<uint32_t*>(&h);
+      h = __floats2bfloat162_rn(fmaxf(acc[2], 0.f), fmaxf(acc[3], 0.f)); o.y = *reinterpret_cast<uint32_t*>(&h);
+      h = __floats2bfloat162_rn(fmaxf(acc[4], 0.f), fmaxf(acc[5], 0.f)); o.z = *reinterpret_cast<uint32_t*>(&h);
+      h = __floats2bfloat162_rn(fmaxf(acc[6], 0.f), fmaxf(acc[7], 0.f)); o.w = *reinterpret_cast<uint32_t*>(&h);
+      *reinterpret_cast<uint4*>(out + (((int64_t)b * S + y) * S + x) * C0 + cg * 8) = o;
+    }
+  }
 }
 
 // ---- depthwise 3x3 ---------------------------------------------------------------------------
@@ -87,49 +109,128 @@ __device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
   h = __floats2bfloat162_rn(f[6], f[7]); o.w = *reinterpret_cast<uint32_t*>(&h);
   return o;
 }
+__device__ __forceinline__ void unpack4(const uint2& v, bool relu, float (&f)[4]) {
+  __nv_bfloat162 h0 = *reinterpret_cast<const __nv_bfloat162*>(&v.x);
+  __nv_bfloat162 h1 = *reinterpret_cast<const __nv_bfloat162*>(&v.y);
+  if (relu) {
+    const __nv_bfloat162 z = __floats2bfloat162_rn(0.f, 0.f);
+    h0 = __hmax2(h0, z); h1 = __hmax2(h1, z);
+  }
+  float2 a = __bfloat1622float2(h0), b = __bfloat1622float2(h1);
+  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y;
+}
 
-// one thread: 8 channels of one pixel
-__global__ void __launch_bounds__(256) dwconv_kernel(const bf16* __restrict__ in, int B, int S, int C,
+// Column-sliding depthwise 3x3: a thread owns 4 channels of one image column x and walks down a strip
+// of rows.  Each input row (3 x-neighbours, 8 bytes each) is loaded and converted once and scattered
+// into the three output rows it contributes to; the 36 weights stay in registers.  Consecutive
+// threads are consecutive (x, channel-quad) pairs, so every load / store of a warp is 256 contiguous
+// bytes and the x-neighbour loads hit L1.
+__global__ void __launch_bounds__(256) dwconv_kernel(const bf16* __restrict__ in, int B, int S, int C, int rows,
                                                      const float* __restrict__ w, int relu_in,
                                                      bf16* __restrict__ out, bf16* __restrict__ sub) {
+  const int quads = C >> 2;
+  const int col = blockIdx.x * blockDim.x + threadIdx.x;   // (x, channel quad)
+  if (col >= S * quads) return;
+  const int x = col / quads, cq = col - x * quads;
+  const int y0 = blockIdx.y * rows;
+  const int y1 = min(S, y0 + rows);
+  const int b = blockIdx.z;
+  float wr[9][4];
+#pragma unroll
+  for (int t = 0; t < 9; ++t) {
+    float4 wv = __ldg(reinterpret_cast<const float4*>(w + t * C + cq * 4));
+    wr[t][0] = wv.x; wr[t][1] = wv.y; wr[t][2] = wv.z; wr[t][3] = wv.w;
+  }
+  const bool relu = relu_in != 0;
+  const bool has_l = x > 0, has_r = x + 1 < S;
+  const bf16* base = in + ((int64_t)b * S * S + x) * C + cq * 4;        // row 0, this column
+  bf16* obase = out + ((int64_t)b * S * S + x) * C + cq * 4;
+  const int64_t rstride = (int64_t)S * C;
+  // acc0: output row r-1 (complete after input row r), acc1: output row r, acc2: output row r+1
+  float acc0[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f}, acc2[4];
+  const int rbeg = max(y0 - 1, 0), rend = min(y1 + 1, S);   // input rows needed
+  uint2 nl = make_uint2(0, 0), nc = nl, nr = nl;
+  {
+    const bf16* p = base + rbeg * rstride;
+    nc = __ldg(reinterpret_cast<const uint2*>(p));
+    if (has_l) nl = __ldg(reinterpret_cast<const uint2*>(p - C));
+    if (has_r) nr = __ldg(reinterpret_cast<const uint2*>(p + C));
+  }
+  for (int r = rbeg; r < rend; ++r) {
+    const uint2 cl = nl, cc = nc, cr = nr;
+    if (r + 1 < rend) {                               // prefetch the next input row
+      const bf16* p = base + (int64_t)(r + 1) * rstride;
+      nc = __ldg(reinterpret_cast<const uint2*>(p));
+      if (has_l) nl = __ldg(reinterpret_cast<const uint2*>(p - C));
+      if (has_r) nr = __ldg(reinterpret_cast<const uint2*>(p + C));
+    }
+    if (sub != nullptr && ((r | x) & 1) == 0 && r >= y0 && r < y1) {
+      const int S2 = S >> 1;
+      *reinterpret_cast<uint2*>(sub + (((int64_t)b * S2 + (r >> 1)) * S2 + (x >> 1)) * C + cq * 4) = cc;
+    }
+    float fl[4], fc[4], fr[4];
+    unpack4(cl, relu, fl); unpack4(cc, relu, fc); unpack4(cr, relu, fr);
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      // input row r is tap row ky=2 of output r-1, ky=1 of output r, ky=0 of output r+1
+      acc0[c] = fmaf(fl[c], wr[6][c], acc0[c]); acc0[c] = fmaf(fc[c], wr[7][c], acc0[c]); acc0[c] = fmaf(fr[c], wr[8][c], acc0[c]);
+      acc1[c] = fmaf(fl[c], wr[3][c], acc1[c]); acc1[c] = fmaf(fc[c], wr[4][c], acc1[c]); acc1[c] = fmaf(fr[c], wr[5][c], acc1[c]);
+      acc2[c] = fl[c] * wr[0][c];               acc2[c] = fmaf(fc[c], wr[1][c], acc2[c]); acc2[c] = fmaf(fr[c], wr[2][c], acc2[c]);
+    }
+    const int yo = r - 1;                             // output row completed by this input row
+    if (yo >= y0 && yo < y1) {
+      __nv_bfloat162 h0 = __floats2bfloat162_rn(acc0[0], acc0[1]), h1 = __floats2bfloat162_rn(acc0[2], acc0[3]);
+      uint2 o = make_uint2(*reinterpret_cast<uint32_t*>(&h0), *reinterpret_cast<uint32_t*>(&h1));
+      *reinterpret_cast<uint2*>(obase + (int64_t)yo * rstride) = o;
+    }
+#pragma unroll
+    for (int c = 0; c < 4; ++c) { acc0[c] = acc1[c]; acc1[c] = acc2[c]; }
+  }
+  // last output row of the strip when it is the last image row (no input row below it)
+  if (rend == S && y1 == S) {
+    const int yo = S - 1;
+    if (yo >= y0) {
+      __nv_bfloat162 h0 = __floats2bfloat162_rn(acc0[0], acc0[1]), h1 = __floats2bfloat162_rn(acc0[2], acc0[3]);
+      uint2 o = make_uint2(*reinterpret_cast<uint32_t*>(&h0), *reinterpret_cast<uint32_t*>(&h1));
+      *reinterpret_cast<uint2*>(obase + (int64_t)yo * rstride) = o;
+    }
+  }
+}
+
+// ---- MaxPool(3, stride 2, same) ----------------------------------------------------------------
+// one thread: 8 channels of one output pixel; window rows 2y..2y+2, cols 2x..2x+2 clipped to the image
+__global__ void __launch_bounds__(256) maxpool_kernel(const bf16* __restrict__ in, int B, int S, int C,
+                                                      bf16* __restrict__ out) {
   const int groups = C >> 3;
+  const int S2 = S >> 1;
   int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  int64_t total = (int64_t)B * S * S * groups;
+  int64_t total = (int64_t)B * S2 * S2 * groups;
   if (idx >= total) return;
   int cg = (int)(idx % groups);
   int64_t pix = idx / groups;
-  int x = (int)(pix % S);
-  int y = (int)((pix / S) % S);
-  int b = (int)(pix / ((int64_t)S * S));
-  float acc[8];
-#pragma unroll
-  for (int c = 0; c < 8; ++c) acc[c] = 0.f;
+  int x = (int)(pix % S2);
+  int y = (int)((pix / S2) % S2);
+  int b = (int)(pix / ((int64_t)S2 * S2));
+  const __nv_bfloat162 ninf = __floats2bfloat162_rn(-INFINITY, -INFINITY);
+  __nv_bfloat162 m[4] = {ninf, ninf, ninf, ninf};
 #pragma unroll
   for (int ky = 0; ky < 3; ++ky) {
-    int yy = y + ky - 1;
-    if (yy < 0 || yy >= S) continue;
+    int yy = 2 * y + ky;
+    if (yy >= S) continue;
 #pragma unroll
     for (int kx = 0; kx < 3; ++kx) {
-      int xx = x + kx - 1;
-      if (xx < 0 || xx >= S) continue;
+      int xx = 2 * x + kx;
+      if (xx >= S) continue;
       uint4 v = __ldg(reinterpret_cast<const uint4*>(in + (((int64_t)b * S + yy) * S + xx) * C + cg * 8));
-      if (ky == 1 && kx == 1 && sub != nullptr && ((x | y) & 1) == 0) {
-        int S2 = S >> 1;
-        *reinterpret_cast<uint4*>(sub + (((int64_t)b * S2 + (y >> 1)) * S2 + (x >> 1)) * C + cg * 8) = v;
-      }
-      float f[8];
-      unpack8(v, f);
-      const float4* wp = reinterpret_cast<const float4*>(w + (ky * 3 + kx) * C + cg * 8);
-      float4 w0 = __ldg(wp), w1 = __ldg(wp + 1);
-      float wv[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
 #pragma unroll
-      for (int c = 0; c < 8; ++c) {
-        float a = relu_in ? fmaxf(f[c], 0.f) : f[c];
-        acc[c] = fmaf(a, wv[c], acc[c]);
-      }
+      for (int i = 0; i < 4; ++i) m[i] = __hmax2(m[i], h[i]);
     }
   }
-  *reinterpret_cast<uint4*>(out + pix * C + cg * 8) = pack8(acc);
+  uint4 o;
+  o.x = *reinterpret_cast<uint32_t*>(&m[0]); o.y = *reinterpret_cast<uint32_t*>(&m[1]);
+  o.z = *reinterpret_cast<uint32_t*>(&m[2]); o.w = *reinterpret_cast<uint32_t*>(&m[3]);
+  *reinterpret_cast<uint4*>(out + pix * C + cg * 8) = o;
 }
 
 }  // namespace
@@ -137,16 +238,32 @@ __global__ void __launch_bounds__(256) dwconv_kernel(const bf16* __restrict__ in
 int stem_run(tmat_ctx* ctx, const StemSrc& src, int B, int ws, const float* w, const float* shift, int C0,
              bf16* out, cudaStream_t st) {
   int S = ws / 2;
-  int64_t total = (int64_t)B * S * S * (C0 / 8);
-  stem_kernel<<<(unsigned)cdiv64(total, 256), 256, 0, st>>>(src, B, ws, w, shift, C0, out);
+  TMAT_REQUIRE(C0 % 8 == 0 && C0 / 8 <= 256 && 256 % (C0 / 8) == 0, "stem: unsupported channel count %d", C0);
+  TMAT_REQUIRE(B <= 65535, "stem: batch %d too large", B);
+  dim3 grid(cdiv(S, STEM_COLS), cdiv(S, STEM_ROWS), B);
+  stem_kernel<<<grid, 256, 0, st>>>(src, B, ws, w, shift, C0, out);
   KERNEL_CHECK(ctx);
   return TMAT_OK;
 }
 
 int dwconv_run(tmat_ctx* ctx, const bf16* in, int B, int S, int C, const float* w, int relu_in, bf16* out,
                bf16* sub, cudaStream_t st) {
-  int64_t total = (int64_t)B * S * S * (C / 8);
-  dwconv_kernel<<<(unsigned)cdiv64(total, 256), 256, 0, st>>>(in, B, S, C, w, relu_in, out, sub);
+  TMAT_REQUIRE(C % 4 == 0 && B <= 65535, "dwconv: unsupported shape (C=%d, B=%d)", C, B);
+  // strips of ~20 rows: 2 halo rows per strip are re-read (10 %), and the grid stays >= 2 waves
+  int nstrips = cdiv(S, 20);
+  int rows = cdiv(S, nstrips);
+  if (sub && (rows & 1)) rows++;                // keep strip boundaries even (stride-2 sample rows)
+  nstrips = cdiv(S, rows);
+  dim3 grid(cdiv(S * (C / 4), 256), nstrips, B);
+  dwconv_kernel<<<grid, 256, 0, st>>>(in, B, S, C, rows, w, relu_in, out, sub);
+  KERNEL_CHECK(ctx);
+  return TMAT_OK;
+}
+
+int maxpool_run(tmat_ctx* ctx, const bf16* in, int B, int S, int C, bf16* out, cudaStream_t st) {
+  TMAT_REQUIRE(C % 8 == 0 && S % 2 == 0, "maxpool: unsupported shape (S=%d, C=%d)", S, C);
+  int64_t total = (int64_t)B * (S / 2) * (S / 2) * (C / 8);
+  maxpool_kernel<<<(unsigned)cdiv64(total, 256), 256, 0, st>>>(in, B, S, C, out);
   KERNEL_CHECK(ctx);
   return TMAT_OK;
 }
