@@ -142,6 +142,10 @@ int tmat_unet_debug_tap(tmat_ctx* ctx, tmat_unet* net, const char* name, float* 
 int tmat_debug_conv_selftest(tmat_ctx* ctx, int B, int H, int W, int C0, int C1, int Cout, int ntaps,
                              int epi, int relu, int dual, int addend, uint64_t seed,
                              double* max_abs_diff, double* max_abs_ref);
+/* Self-test hook: the fused SeparableConv2D kernel (depthwise 3x3 computed into the tcgen05 A operand)
+ * vs the unfused pair (depthwise kernel, CUDA-core GEMM) on random data. */
+int tmat_debug_dwpw_selftest(tmat_ctx* ctx, int B, int S, int C, int N, int relu_in, int relu_out,
+                             uint64_t seed, double* max_abs_diff, double* max_abs_ref);
 /* FLOPs (2*MAC of every convolution as written in models.py:110-171) of one patch */
 int tmat_unet_flops_per_patch(const tmat_unet_desc* desc, double* flops);
 

@@ -41,6 +41,25 @@ def test_tcgen05_conv_matches_cuda_core_conv(case):
     assert d.value <= m.value * 2 ** -7, (d.value, m.value)
 
 
+DWPW_CASES = [
+    # B, S, C, N, relu_in, relu_out
+    (2, 32, 64, 128, 0, 1), (1, 160, 64, 128, 0, 1), (1, 160, 128, 128, 0, 0), (2, 80, 128, 256, 1, 1),
+    (2, 80, 256, 256, 0, 0), (3, 40, 256, 512, 1, 1), (2, 40, 512, 512, 0, 0), (5, 13, 64, 64, 1, 0),
+    (9, 6, 128, 64, 0, 1), (3, 16, 64, 192, 0, 0),
+]
+
+
+@pytest.mark.parametrize("case", DWPW_CASES)
+def test_fused_separable_conv_matches_unfused(case):
+    """conv_dwpw_kernel (depthwise computed into the tcgen05 A operand) vs depthwise kernel + CUDA-core GEMM."""
+    from tmat_b200 import _ffi
+    ctx = _ffi.default_context()
+    d, m = C.c_double(), C.c_double()
+    _ffi.check(_ffi.lib().tmat_debug_dwpw_selftest(ctx.handle, *case, 11, C.byref(d), C.byref(m)))
+    assert m.value > 0.1
+    assert d.value <= m.value * 2 ** -7, (d.value, m.value)
+
+
 @pytest.mark.parametrize("fc,ws,n,impl", [((8, 16, 32, 64), 64, 2, "simt"), ((64, 128, 256, 512), 64, 3, "tc"),
                                           ((64, 128, 256, 512), 96, 5, "tc"), ((64, 64, 128, 128), 64, 2, "tc")])
 def test_unet_forward_vs_oracle(fc, ws, n, impl):

@@ -1,0 +1,376 @@
+// Fused SeparableConv2D (models.py:129,134): [ReLU] -> depthwise 3x3 -> pointwise 1x1 + bias + BN [+ ReLU]
+// as ONE tcgen05 kernel.  The depthwise result never goes to HBM: it is produced straight into the
+// 128-byte-swizzled A-operand stage of the pointwise GEMM.
+//
+//   warp 0       TMA producer: per (tile, 64-channel slab) one haloed raw input tile
+//                (64 ch x (TW+2) x (TH+2) x TN, zero-filled outside the image = 'same' padding) into the raw
+//                ring, and the slab's pointwise weights [BN x 64] into the B half of a GEMM stage
+//   warps 6..13  depthwise: each thread owns 4 channels of one tile column and slides down the rows
+//                (one 8-byte ld.shared per tap column per row, 36 fp32 weights in registers, fp32
+//                accumulate), rounds to bf16 and writes the A half of the stage in UMMA layout
+//   warp 1       MMA issuer (tcgen05.mma M=128, N=BN, K=16 x4 per slab), accumulator double-buffered in TMEM
+//   warps 2..5   epilogue: tcgen05.ld -> +shift, ReLU -> bf16 -> swizzled staging tile -> TMA store
+#include "tc_ptx.cuh"
+#include <algorithm>
+
+using namespace tcptx;
+
+namespace {
+
+constexpr int DW_THREADS = 448;
+constexpr int DW_WARPS = 8;          // depthwise warps (6..13)
+constexpr int MAX_STAGES = 8;
+constexpr int MAX_RAW = 4;
+
+struct DwpwParams {
+  int tw_log, th_log, tn_log;
+  int tiles_x, tiles_y, tiles_b, tiles_n, total_tiles;
+  int nk;            // 64-channel slabs of the input
+  int C;             // input channels
+  int relu_in;
+  int raw_bytes;     // one raw ring slot (1024-aligned)
+  int raw_tx;        // bytes one raw TMA load delivers
+  int n_raw, n_stage;
+  const float* dw;   // [9][C]
+  EpiParams e;
+};
+
+__device__ __forceinline__ uint2 ld_shared_v2(uint32_t addr) {
+  uint2 v;
+  asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void st_shared_v2(uint32_t addr, uint2 v) {
+  asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(addr), "r"(v.x), "r"(v.y) : "memory");
+}
+__device__ __forceinline__ void unpack4s(const uint2& v, bool relu, float (&f)[4]) {
+  __nv_bfloat162 h0 = *reinterpret_cast<const __nv_bfloat162*>(&v.x);
+  __nv_bfloat162 h1 = *reinterpret_cast<const __nv_bfloat162*>(&v.y);
+  if (relu) {
+    const __nv_bfloat162 z = __floats2bfloat162_rn(0.f, 0.f);
+    h0 = __hmax2(h0, z); h1 = __hmax2(h1, z);
+  }
+  float2 a = __bfloat1622float2(h0), b = __bfloat1622float2(h1);
+  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y;
+}
+
+template <int BN>
+__global__ void __launch_bounds__(DW_THREADS, 1)
+conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constant__ CUtensorMap tmB,
+                 const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ DwpwParams p) {
+  constexpr int B_STAGE_BYTES = BN * KSLAB * 2;
+  constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+  constexpr int TMEM_COLS = 2 * BN;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t raw_base = smem_base + p.n_stage * STAGE_BYTES;
+  const uint32_t stg_base = raw_base + p.n_raw * p.raw_bytes;
+  const uint32_t bar_base = stg_base + 2 * STG_BYTES;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (MAX_STAGES + s); };
+  auto rfull_bar = [&](int s) { return bar_base + 8u * (2 * MAX_STAGES + s); };
+  auto rempty_bar = [&](int s) { return bar_base + 8u * (2 * MAX_STAGES + MAX_RAW + s); };
+  auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * MAX_STAGES + 2 * MAX_RAW + s); };
+  auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * MAX_STAGES + 2 * MAX_RAW + 2 + s); };
+  constexpr int TMEM_SLOT = 8 * (2 * MAX_STAGES + 2 * MAX_RAW + 4);
+  const uint32_t tmem_slot = bar_base + TMEM_SLOT;
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+  volatile uint32_t* tmem_slot_gen =
+      reinterpret_cast<volatile uint32_t*>(smem_gen + (bar_base - smem_base) + TMEM_SLOT);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < p.n_stage; ++s) { mbar_init(full_bar(s), 1 + DW_WARPS); mbar_init(empty_bar(s), 1); }
+    for (int s = 0; s < p.n_raw; ++s) { mbar_init(rfull_bar(s), 1); mbar_init(rempty_bar(s), DW_WARPS); }
+    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 128); }
+    fence_barrier_init();
+    fence_proxy_async();
+    tma_prefetch_desc(&tmRaw);
+    tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmOut);
+  }
+  if (warp == 1) tmem_alloc<TMEM_COLS>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_gen;
+
+  const int TW = 1 << p.tw_log, TH = 1 << p.th_log, TN = 1 << p.tn_log;
+  const int tiles_xy = p.tiles_x * p.tiles_y;
+  auto decode = [&](int tile, int& nt, int& x0, int& y0, int& b0) {
+    int mt = tile / p.tiles_n;
+    nt = tile - mt * p.tiles_n;
+    int tb = mt / tiles_xy, rr = mt - tb * tiles_xy;
+    int ty = rr / p.tiles_x, tx = rr - ty * p.tiles_x;
+    x0 = tx << p.tw_log; y0 = ty << p.th_log; b0 = tb << p.tn_log;
+  };
+
+  if (warp == 0) {
+    // ================= TMA producer =================
+    int stage = 0, rs = 0; uint32_t phase = 0, rphase = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+      int nt, x0, y0, b0;
+      decode(tile, nt, x0, y0, b0);
+      for (int ks = 0; ks < p.nk; ++ks) {
+        mbar_wait(rempty_bar(rs), rphase ^ 1);
+        if (lane == 0) {
+          mbar_expect_tx(rfull_bar(rs), p.raw_tx);
+          tma_load_4d(raw_base + rs * p.raw_bytes, &tmRaw, rfull_bar(rs), ks * KSLAB, x0 - 1, y0 - 1, b0);
+        }
+        mbar_wait(empty_bar(stage), phase ^ 1);
+        if (lane == 0) {
+          mbar_expect_tx(full_bar(stage), B_STAGE_BYTES);
+          tma_load_2d(smem_base + stage * STAGE_BYTES + A_STAGE_BYTES, &tmB, full_bar(stage), ks * KSLAB, nt * BN);
+        }
+        __syncwarp();
+        if (++stage == p.n_stage) { stage = 0; phase ^= 1; }
+        if (++rs == p.n_raw) { rs = 0; rphase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer =================
+    constexpr uint32_t idesc = umma_idesc<BN>();
+    int stage = 0; uint32_t phase = 0;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+      const int as = it & 1;
+      const uint32_t aphase = (it >> 1) & 1;
+      mbar_wait(tempty_bar(as), aphase ^ 1);
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + as * BN;
+      for (int ks = 0; ks < p.nk; ++ks) {
+        mbar_wait(full_bar(stage), phase);
+        tc_fence_after();
+        if (lane == 0) {
+          uint32_t sa = smem_base + stage * STAGE_BYTES;
+          uint64_t adesc = umma_desc_sw128(sa);
+          uint64_t bdesc = umma_desc_sw128(sa + A_STAGE_BYTES);
+#pragma unroll
+          for (int k = 0; k < KSLAB / 16; ++k) umma_bf16(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (ks | k) != 0);
+          umma_commit(empty_bar(stage));
+          if (ks == p.nk - 1) umma_commit(tfull_bar(as));
+        }
+        __syncwarp();
+        if (++stage == p.n_stage) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp < 6) {
+    // ================= epilogue (warps 2..5) =================
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    const bool leader = (threadIdx.x == 64);
+    const uint32_t stg_row = (uint32_t)row * 128u;
+    const uint32_t sw = (uint32_t)(row & 7);
+    const EpiParams& e = p.e;
+    int sbuf = 0;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+      const int as = it & 1;
+      const uint32_t aphase = (it >> 1) & 1;
+      int nt, x0, y0, b0;
+      decode(tile, nt, x0, y0, b0);
+      mbar_wait(tfull_bar(as), aphase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
+#pragma unroll 1
+      for (int c64 = 0; c64 < BN; c64 += 64) {
+        const int ch0 = nt * BN + c64;
+        if (leader) tma_store_wait_read<1>();
+        epi_bar_sync();
+        const uint32_t buf = stg_base + sbuf * STG_BYTES;
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          uint32_t rr[32];
+          tmem_ld32(taddr + c64 + half * 32, rr);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            float f[8];
+#pragma unroll
+            for (int i = 0; i < 8; i += 4) {
+              float4 s = __ldg(reinterpret_cast<const float4*>(e.shift + ch0 + half * 32 + 8 * j + i));
+              f[i] = __uint_as_float(rr[8 * j + i]) + s.x; f[i + 1] = __uint_as_float(rr[8 * j + i + 1]) + s.y;
+              f[i + 2] = __uint_as_float(rr[8 * j + i + 2]) + s.z; f[i + 3] = __uint_as_float(rr[8 * j + i + 3]) + s.w;
+            }
+            if (e.relu) {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) f[i] = fmaxf(f[i], 0.f);
+            }
+            uint4 o;
+            o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]);
+            o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
+            st_shared_v4(buf + stg_row + ((((uint32_t)(half * 4 + j)) ^ sw) << 4), o);
+          }
+        }
+        if (c64 + 64 >= BN) {
+          tc_fence_before();
+          mbar_arrive(tempty_bar(as));
+        }
+        fence_proxy_async();
+        epi_bar_sync();
+        if (leader) {
+          tma_store_4d(&tmOut, buf, ch0, x0, y0, b0);
+          tma_store_commit();
+        }
+        sbuf ^= 1;
+      }
+    }
+    if (leader) tma_store_wait_all();
+  } else {
+    // ================= depthwise (warps 6..13) =================
+    const int t = threadIdx.x - 192;        // 0..255
+    const int h = t & 15;                   // 4-channel group within the 64-channel slab
+    const uint32_t jch = (uint32_t)(h >> 1);            // 16-byte chunk
+    const uint32_t sub = (uint32_t)(h & 1) << 3;        // 8-byte half of the chunk
+    const int cslot = t >> 4;               // column slot 0..15
+    const int ncols = TW * TN;
+    const int RW = TW + 2, RH = TH + 2;
+    const bool relu = p.relu_in != 0;
+    int stage = 0, rs = 0; uint32_t phase = 0, rphase = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+      for (int ks = 0; ks < p.nk; ++ks) {
+        float wr[9][4];
+#pragma unroll
+        for (int tp = 0; tp < 9; ++tp) {
+          float4 wv = __ldg(reinterpret_cast<const float4*>(p.dw + tp * p.C + ks * KSLAB + h * 4));
+          wr[tp][0] = wv.x; wr[tp][1] = wv.y; wr[tp][2] = wv.z; wr[tp][3] = wv.w;
+        }
+        mbar_wait(rfull_bar(rs), rphase);
+        mbar_wait(empty_bar(stage), phase ^ 1);
+        const uint32_t rbase = raw_base + rs * p.raw_bytes;
+        const uint32_t abase = smem_base + stage * STAGE_BYTES;
+        for (int ci = cslot; ci < ncols; ci += 16) {
+          const int n = ci >> p.tw_log, x = ci & (TW - 1);
+          float acc0[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f}, acc2[4];
+          uint32_t rp = (uint32_t)((n * RH) * RW + x);          // raw pixel (n, yy = 0, xx = x)
+          uint32_t ar = (uint32_t)((n * TH) * TW + x);          // A row of output (n, y = 0, x)
+          for (int yy = 0; yy < RH; ++yy, rp += RW) {
+            float fl[4], fc[4], fr[4];
+            unpack4s(ld_shared_v2(rbase + rp * 128u + (((jch ^ (rp & 7u)) << 4) | sub)), relu, fl);
+            unpack4s(ld_shared_v2(rbase + (rp + 1) * 128u + (((jch ^ ((rp + 1) & 7u)) << 4) | sub)), relu, fc);
+            unpack4s(ld_shared_v2(rbase + (rp + 2) * 128u + (((jch ^ ((rp + 2) & 7u)) << 4) | sub)), relu, fr);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              // raw row yy is tap row ky=2 of output yy-2, ky=1 of output yy-1, ky=0 of output yy
+              acc0[c] = fmaf(fl[c], wr[6][c], acc0[c]); acc0[c] = fmaf(fc[c], wr[7][c], acc0[c]); acc0[c] = fmaf(fr[c], wr[8][c], acc0[c]);
+              acc1[c] = fmaf(fl[c], wr[3][c], acc1[c]); acc1[c] = fmaf(fc[c], wr[4][c], acc1[c]); acc1[c] = fmaf(fr[c], wr[5][c], acc1[c]);
+              acc2[c] = fl[c] * wr[0][c];               acc2[c] = fmaf(fc[c], wr[1][c], acc2[c]); acc2[c] = fmaf(fr[c], wr[2][c], acc2[c]);
+            }
+            if (yy >= 2) {
+              uint2 o = make_uint2(pack_bf16x2(acc0[0], acc0[1]), pack_bf16x2(acc0[2], acc0[3]));
+              st_shared_v2(abase + ar * 128u + (((jch ^ (ar & 7u)) << 4) | sub), o);
+              ar += TW;
+            }
+#pragma unroll
+            for (int c = 0; c < 4; ++c) { acc0[c] = acc1[c]; acc1[c] = acc2[c]; }
+          }
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          mbar_arrive(full_bar(stage));
+          mbar_arrive(rempty_bar(rs));
+        }
+        if (++stage == p.n_stage) { stage = 0; phase ^= 1; }
+        if (++rs == p.n_raw) { rs = 0; rphase ^= 1; }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<TMEM_COLS>(tmem_base);
+}
+
+struct DwpwPlan {
+  int tw_log, th_log, tn_log, BN, n_raw, n_stage, raw_bytes, raw_tx, smem;
+};
+
+bool plan_dwpw(int B, int S, int C, int N, DwpwPlan* pl) {
+  if (C % KSLAB != 0 || N % 64 != 0 || C / KSLAB > 64) return false;
+  tc_choose_tile(B, S, S, &pl->tw_log, &pl->th_log, &pl->tn_log);
+  const int TW = 1 << pl->tw_log, TH = 1 << pl->th_log, TN = 1 << pl->tn_log;
+  if (TW * TN < 1 || TW + 2 > 256 || TH + 2 > 256) return false;
+  pl->BN = N % 256 == 0 ? 256 : (N % 128 == 0 ? 128 : 64);
+  pl->raw_tx = (TW + 2) * (TH + 2) * TN * 128;
+  pl->raw_bytes = (pl->raw_tx + 1023) / 1024 * 1024;
+  const int stage_bytes = A_STAGE_BYTES + pl->BN * KSLAB * 2;
+  const int budget = 227 * 1024 - 2048 - 2 * STG_BYTES;
+  for (int n_raw = 3; n_raw >= 2; --n_raw) {
+    int left = budget - n_raw * pl->raw_bytes;
+    int n_stage = left / stage_bytes;
+    if (n_stage > 4) n_stage = 4;
+    if (n_stage >= 2) {
+      pl->n_raw = n_raw; pl->n_stage = n_stage;
+      pl->smem = n_stage * stage_bytes + n_raw * pl->raw_bytes + 2 * STG_BYTES + 2048;
+      return true;
+    }
+  }
+  return false;
+}
+
+template <int BN>
+int launch_dwpw(tmat_ctx* ctx, const CUtensorMap& raw, const CUtensorMap& b, const CUtensorMap& out,
+                const DwpwParams& p, int smem, cudaStream_t st) {
+  static int configured = 0;
+  if (configured < smem) {
+    CUDA_TRY(cudaFuncSetAttribute(conv_dwpw_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    configured = 227 * 1024;
+  }
+  int grid = std::min(p.total_tiles, ctx->sm_count);
+  tmat_ctx::ProfRec rec{nullptr, nullptr, 0.0};
+  if (ctx->profiling) {
+    for (cudaEvent_t* e : {&rec.a, &rec.b}) {
+      if (!ctx->event_pool.empty()) { *e = ctx->event_pool.back(); ctx->event_pool.pop_back(); }
+      else CUDA_TRY(cudaEventCreate(e));
+    }
+    rec.flops = 2.0 * p.e.B * p.e.H * p.e.W * ((double)(p.tiles_n * BN) * (double)p.C + 9.0 * p.C);
+    CUDA_TRY(cudaEventRecord(rec.a, st));
+  }
+  conv_dwpw_kernel<BN><<<grid, DW_THREADS, smem, st>>>(raw, b, out, p);
+  KERNEL_CHECK(ctx);
+  if (ctx->profiling) {
+    CUDA_TRY(cudaEventRecord(rec.b, st));
+    ctx->prof.push_back(rec);
+  }
+  return TMAT_OK;
+}
+
+}  // namespace
+
+bool dwpw_supported(int B, int S, int C, int N) {
+  DwpwPlan pl;
+  return plan_dwpw(B, S, C, N, &pl);
+}
+
+int dwpw_run(tmat_ctx* ctx, const bf16* in, int B, int S, int C, const float* dw, int relu_in, const bf16* wmat,
+             const float* shift, int N, int relu_out, bf16* out, cudaStream_t st) {
+  DwpwPlan pl;
+  TMAT_REQUIRE(plan_dwpw(B, S, C, N, &pl), "dwpw: shape (B=%d, S=%d, C=%d, N=%d) not supported", B, S, C, N);
+  const int TW = 1 << pl.tw_log, TH = 1 << pl.th_log, TN = 1 << pl.tn_log;
+  DwpwParams p;
+  memset(&p, 0, sizeof(p));
+  p.tw_log = pl.tw_log; p.th_log = pl.th_log; p.tn_log = pl.tn_log;
+  p.tiles_x = cdiv(S, TW); p.tiles_y = cdiv(S, TH); p.tiles_b = cdiv(B, TN); p.tiles_n = N / pl.BN;
+  int64_t total = (int64_t)p.tiles_x * p.tiles_y * p.tiles_b * p.tiles_n;
+  TMAT_REQUIRE(total < (1ll << 31), "dwpw: too many tiles");
+  p.total_tiles = (int)total;
+  p.nk = C / KSLAB; p.C = C; p.relu_in = relu_in;
+  p.raw_bytes = pl.raw_bytes; p.raw_tx = pl.raw_tx; p.n_raw = pl.n_raw; p.n_stage = pl.n_stage;
+  p.dw = dw;
+  memset(&p.e, 0, sizeof(p.e));
+  p.e.mode = EPI_STORE; p.e.relu = relu_out; p.e.B = B; p.e.H = S; p.e.W = S; p.e.Cout = N; p.e.ppg = 1;
+  p.e.shift = shift; p.e.out = out;
+  CUtensorMap mRaw, mB, mOut;
+  TMAT_TRY(tc_make_act_map(&mRaw, in, B, S, S, C, TW + 2, TH + 2, TN));
+  TMAT_TRY(tc_make_weight_map(&mB, wmat, N, C, pl.BN));
+  TMAT_TRY(tc_make_act_map(&mOut, out, B, S, S, N, TW, TH, TN));
+  switch (pl.BN) {
+    case 256: return launch_dwpw<256>(ctx, mRaw, mB, mOut, p, pl.smem, st);
+    case 128: return launch_dwpw<128>(ctx, mRaw, mB, mOut, p, pl.smem, st);
+    case 64: return launch_dwpw<64>(ctx, mRaw, mB, mOut, p, pl.smem, st);
+  }
+  return TMAT_ERR_INVALID;
+}

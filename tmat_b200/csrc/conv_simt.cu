@@ -7,7 +7,7 @@
 namespace {
 
 struct SimtParams {
-  const bf16* a0; int a0_C;
+  const bf16* a0; int a0_C; int a0_stride;
   const bf16* a1; int a1_C;
   int ngroups, ntaps, npad;
   int8_t dy[CONV_MAX_GROUPS][9], dx[CONV_MAX_GROUPS][9];
@@ -60,7 +60,8 @@ __global__ void __launch_bounds__(128) conv_simt_kernel(SimtParams p) {
   for (int t = 0; t < p.ntaps; ++t) {
     int yy = y + p.dy[g][t], xx = x + p.dx[g][t];
     if (yy < 0 || yy >= e.H || xx < 0 || xx >= e.W) continue;
-    const bf16* a = p.a0 + (((int64_t)b * e.H + yy) * e.W + xx) * p.a0_C;
+    const int sa = p.a0_stride;
+    const bf16* a = p.a0 + (((int64_t)b * e.H * sa + yy * sa) * e.W * sa + xx * sa) * p.a0_C;
     const bf16* wt = wrow + t * p.a0_C;
     for (int c = 0; c < p.a0_C; c += 2) {
       float2 av = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(a + c));
@@ -89,7 +90,8 @@ int conv_run_simt(tmat_ctx* ctx, const ConvOp& op, cudaStream_t st) {
   TMAT_REQUIRE(op.ngroups >= 1 && op.ngroups <= CONV_MAX_GROUPS && (op.ngroups == 1 || !op.a1),
                "conv_simt(%s): bad group configuration", op.name);
   SimtParams p;
-  p.a0 = op.a0; p.a0_C = op.a0_C; p.a1 = op.a1; p.a1_C = op.a1_C;
+  p.a0 = op.a0; p.a0_C = op.a0_C; p.a0_stride = op.a0_stride; p.a1 = op.a1; p.a1_C = op.a1_C;
+  TMAT_REQUIRE(op.a0_stride == 1 || (op.ntaps == 1 && op.ngroups == 1), "conv_simt(%s): strided a0 needs a single tap", op.name);
   p.ngroups = op.ngroups; p.ntaps = op.ntaps; p.npad = op.Npad;
   memcpy(p.dy, op.dy, sizeof(p.dy));
   memcpy(p.dx, op.dx, sizeof(p.dx));

@@ -22,18 +22,15 @@
 //                                   with the next tile's MMAs.  The TMA store clips partial tiles and
 //                                   writes full 128-byte lines, so the epilogue issues no per-thread
 //                                   global stores (the head, 4 floats per pixel, stores directly).
-#include "unet.cuh"
-#include <cuda.h>
+#include "tc_ptx.cuh"
 #include <algorithm>
+
+using namespace tcptx;
 
 namespace {
 
-constexpr int TILE_M = 128;
-constexpr int KSLAB = 64;                          // bf16 elements per k-step = 128 bytes = swizzle span
-constexpr int A_STAGE_BYTES = TILE_M * KSLAB * 2;  // 16 KiB
 constexpr int MAX_KSTEPS = 160;                    // over all groups
 constexpr int TC_THREADS = 192;
-constexpr int STG_BYTES = TILE_M * 128;            // one staging tile: 128 pixels x 64 bf16 channels
 constexpr int N_STG = 2;
 
 struct TcParams {
@@ -50,139 +47,6 @@ struct TcOutMaps {
   CUtensorMap m[4];
   CUtensorMap m2;
 };
-
-// ---- PTX wrappers ----------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-      "selp.b32 %0, 1, 0, p;\n\t}"
-      : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
-  return ok != 0;
-}
-// Bounded wait: a protocol bug traps (reported as a launch failure) instead of hanging the GPU.
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  uint32_t spins = 0;
-  while (!mbar_try_wait(bar, parity)) {
-    if (++spins > (1u << 26)) __trap();
-  }
-}
-__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-
-__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1,
-                                            int c2, int c3) {
-  asm volatile(
-      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
-      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
-}
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
-}
-// smem tile -> global tensor (bulk async group of the issuing thread)
-__device__ __forceinline__ void tma_store_4d(const CUtensorMap* map, uint32_t src, int c0, int c1, int c2, int c3) {
-  asm volatile(
-      "cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
-      ::"l"(map), "r"(src), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
-}
-__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void tma_store_wait_read() {
-  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
-}
-__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
-// named barrier among the 128 epilogue threads (barrier 0 is __syncthreads)
-__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
-__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint4 v) {
-  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
-}
-__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
-  asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
-}
-
-template <int COLS>
-__device__ __forceinline__ void tmem_alloc(uint32_t smem_dst) {
-  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_dst), "n"(COLS) : "memory");
-  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-}
-template <int COLS>
-__device__ __forceinline__ void tmem_dealloc(uint32_t taddr) {
-  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(COLS) : "memory");
-}
-
-// D[tmem] (+)= A[smem desc] * B[smem desc], kind::f16 (bf16 inputs, fp32 accumulate)
-__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
-                                          uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
-}
-// arrive on an mbarrier when all previously issued tcgen05.mma of this thread have completed
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-
-// shared-memory matrix descriptor: K-major, 128-byte swizzle, 8-row groups 1024 bytes apart
-__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
-  uint64_t d = 0;
-  d |= (uint64_t)((saddr & 0x3FFFF) >> 4);   // start address  [0,14)
-  d |= (uint64_t)1 << 16;                    // leading byte offset (ignored for swizzled K-major)
-  d |= (uint64_t)(1024 >> 4) << 32;          // stride byte offset [32,46)
-  d |= (uint64_t)1 << 46;                    // descriptor version (Blackwell)
-  d |= (uint64_t)2 << 61;                    // SWIZZLE_128B
-  return d;
-}
-
-// instruction descriptor: c=f32, a=b=bf16, both K-major, M=128, N=BN
-template <int BN>
-__device__ __forceinline__ constexpr uint32_t umma_idesc() {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TILE_M >> 4) << 24);
-}
-
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
-        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
-        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-      : "r"(taddr) : "memory");
-}
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-      : "r"(taddr) : "memory");
-}
-__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-
-__device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
-  __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
-  return *reinterpret_cast<uint32_t*>(&h);
-}
-__device__ __forceinline__ float sigmoid_f(float v) { return 1.f / (1.f + __expf(-v)); }
 
 // ---- the kernel -------------------------------------------------------------------------------
 template <int BN, int STAGES>
@@ -446,8 +310,8 @@ static EncodeTiledFn get_encode_fn() {
 // NHWC activation tensor (B, H, W, C) bf16 -> 4-D map, box = (64 ch, TW, TH, TN), 128B swizzle, zero OOB fill
 // (sx, sy = pixel strides in units of pixels of the underlying dense tensor of row length Wfull, height Hfull:
 //  the parity views of EPI_PAR use sx = sy = 2)
-static int make_act_map(CUtensorMap* m, const bf16* base, int B, int H, int W, int C, int TW, int TH, int TN,
-                        int sx = 1, int sy = 1) {
+int tc_make_act_map(CUtensorMap* m, const bf16* base, int B, int H, int W, int C, int TW, int TH, int TN,
+                    int sx, int sy) {
   EncodeTiledFn enc = get_encode_fn();
   if (!enc) { tmat_set_error("conv_tc: cuTensorMapEncodeTiled unavailable"); return TMAT_ERR_CUDA; }
   const cuuint64_t Wfull = (cuuint64_t)W * sx, Hfull = (cuuint64_t)H * sy;
@@ -466,7 +330,7 @@ static int make_act_map(CUtensorMap* m, const bf16* base, int B, int H, int W, i
   return TMAT_OK;
 }
 
-static int make_weight_map(CUtensorMap* m, const bf16* base, int Npad, int K, int BN) {
+int tc_make_weight_map(CUtensorMap* m, const bf16* base, int Npad, int K, int BN) {
   EncodeTiledFn enc = get_encode_fn();
   if (!enc) { tmat_set_error("conv_tc: cuTensorMapEncodeTiled unavailable"); return TMAT_ERR_CUDA; }
   cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)Npad};
@@ -484,7 +348,7 @@ static int make_weight_map(CUtensorMap* m, const bf16* base, int Npad, int K, in
 }
 
 // pick the 128-pixel tile (2^a x 2^b pixels x 2^c images) that covers (B, H, W) with the fewest tiles
-static void choose_tile(int B, int H, int W, int* tw_log, int* th_log, int* tn_log) {
+void tc_choose_tile(int B, int H, int W, int* tw_log, int* th_log, int* tn_log) {
   int64_t best = -1;
   for (int a = 7; a >= 0; --a)
     for (int b = 7 - a; b >= 0; --b) {
@@ -498,6 +362,7 @@ static void choose_tile(int B, int H, int W, int* tw_log, int* th_log, int* tn_l
 bool conv_tc_supported(const ConvOp& op) {
   if (op.a0_C % KSLAB != 0 || (op.a1 && op.a1_C % KSLAB != 0)) return false;
   if (op.ngroups < 1 || op.ngroups > CONV_MAX_GROUPS || (op.ngroups > 1 && op.a1)) return false;
+  if (op.a0_stride != 1 && (op.ntaps != 1 || op.ngroups != 1 || op.dy[0][0] != 0 || op.dx[0][0] != 0)) return false;
   int nk = op.ntaps * (op.a0_C / KSLAB) + (op.a1 ? op.a1_C / KSLAB : 0);
   if (nk * op.ngroups > MAX_KSTEPS) return false;
   if (op.epi == EPI_HEAD) return op.Npad == 16 && op.ngroups == 1;
@@ -538,7 +403,7 @@ int conv_run_tc(tmat_ctx* ctx, const ConvOp& op, cudaStream_t st) {
   TMAT_REQUIRE(conv_tc_supported(op), "conv_tc(%s): shape not supported by the tcgen05 path", op.name);
   TcParams p;
   memset(&p, 0, sizeof(p));
-  choose_tile(op.B, op.H, op.W, &p.tw_log, &p.th_log, &p.tn_log);
+  tc_choose_tile(op.B, op.H, op.W, &p.tw_log, &p.th_log, &p.tn_log);
   const int TW = 1 << p.tw_log, TH = 1 << p.th_log, TN = 1 << p.tn_log;
   int BN = op.epi == EPI_HEAD ? 16 : (op.Npad % 256 == 0 ? 256 : (op.Npad % 128 == 0 ? 128 : 64));
   p.tiles_x = cdiv(op.W, TW);
@@ -566,19 +431,19 @@ int conv_run_tc(tmat_ctx* ctx, const ConvOp& op, cudaStream_t st) {
 
   CUtensorMap mA0, mA1, mB;
   TcOutMaps om;
-  TMAT_TRY(make_act_map(&mA0, op.a0, op.B, op.H, op.W, op.a0_C, TW, TH, TN));
-  if (op.a1) TMAT_TRY(make_act_map(&mA1, op.a1, op.B, op.H, op.W, op.a1_C, TW, TH, TN));
+  TMAT_TRY(tc_make_act_map(&mA0, op.a0, op.B, op.H, op.W, op.a0_C, TW, TH, TN, op.a0_stride, op.a0_stride));
+  if (op.a1) TMAT_TRY(tc_make_act_map(&mA1, op.a1, op.B, op.H, op.W, op.a1_C, TW, TH, TN));
   else mA1 = mA0;
-  TMAT_TRY(make_weight_map(&mB, op.wmat, op.ngroups * op.Npad, op.K, BN));
+  TMAT_TRY(tc_make_weight_map(&mB, op.wmat, op.ngroups * op.Npad, op.K, BN));
   if (op.epi == EPI_STORE) {
-    TMAT_TRY(make_act_map(&om.m[0], op.out, op.B, op.H, op.W, op.Cout, TW, TH, TN));
+    TMAT_TRY(tc_make_act_map(&om.m[0], op.out, op.B, op.H, op.W, op.Cout, TW, TH, TN));
     om.m[1] = om.m[2] = om.m[3] = om.m[0];
-    if (op.out2) TMAT_TRY(make_act_map(&om.m2, op.out2, op.B, op.H, op.W, op.Cout, TW, TH, TN));
+    if (op.out2) TMAT_TRY(tc_make_act_map(&om.m2, op.out2, op.B, op.H, op.W, op.Cout, TW, TH, TN));
     else om.m2 = om.m[0];
   } else if (op.epi == EPI_PAR) {
     for (int q = 0; q < 4; ++q) {
       const bf16* base = op.out + ((int64_t)(q >> 1) * 2 * op.W + (q & 1)) * op.Cout;
-      TMAT_TRY(make_act_map(&om.m[q], base, op.B, op.H, op.W, op.Cout, TW, TH, TN, 2, 2));
+      TMAT_TRY(tc_make_act_map(&om.m[q], base, op.B, op.H, op.W, op.Cout, TW, TH, TN, 2, 2));
     }
     om.m2 = om.m[0];
   } else {

@@ -30,6 +30,7 @@ struct tmat_unet {
   int fc[4];
   int device = 0;
   bool use_tc = false;
+  bool fuse_dw = true;     // SeparableConv2D as one tcgen05 kernel (TMAT_NO_FUSE_DW=1 runs depthwise separately)
   std::vector<void*> allocs;
   float* stem_w = nullptr; float* stem_shift = nullptr;
   struct Down { int cin, f; float *dw1, *dw2; bf16 *pw1, *pw2, *res; float *sh1, *sh2, *shres; } down[3];
@@ -345,34 +346,42 @@ int unet_forward(tmat_ctx* ctx, tmat_unet* net, const StemSrc& src, int B, float
   for (int i = 0; i < 3; ++i) {
     auto& D = net->down[i];
     size_t px = (size_t)B * S * S;
-    bf16 *d1, *xs, *a1, *d2, *b2, *pooled, *out, *outr = nullptr;
-    TMAT_TRY(arena_get(ctx, px * D.cin, &d1));
-    TMAT_TRY(arena_get(ctx, px / 4 * D.cin, &xs));
+    bf16 *d1 = nullptr, *a1, *d2 = nullptr, *b2, *pooled, *out, *outr = nullptr;
+    const bool fused = net->use_tc && net->fuse_dw && dwpw_supported(B, S, D.cin, D.f) && dwpw_supported(B, S, D.f, D.f);
+    if (!fused) {
+      TMAT_TRY(arena_get(ctx, px * D.cin, &d1));
+      TMAT_TRY(arena_get(ctx, px * D.f, &d2));
+    }
     TMAT_TRY(arena_get(ctx, px * D.f, &a1));
-    TMAT_TRY(arena_get(ctx, px * D.f, &d2));
     TMAT_TRY(arena_get(ctx, px * D.f, &b2));
     TMAT_TRY(arena_get(ctx, px / 4 * D.f, &pooled));
     TMAT_TRY(arena_get(ctx, px / 4 * D.f, &out));
     if (i == 2) TMAT_TRY(arena_get(ctx, px / 4 * D.f, &outr));
-    // [ReLU] -> depthwise 3x3 ; also the stride-2 sample of the block input for the residual conv
-    TMAT_TRY(dwconv_run(ctx, P, B, S, D.cin, D.dw1, i != 0, d1, xs, st));
-    ConvOp op;
-    op.name = "down.pw1"; op.a0 = d1; op.a0_C = D.cin; op.B = B; op.H = S; op.W = S; set_tap1x1(op);
-    op.wmat = D.pw1; op.K = D.cin; op.shift = D.sh1; op.Cout = op.Npad = D.f; op.epi = EPI_STORE; op.relu = 1;
-    op.out = a1;
-    TMAT_TRY(run_op(ctx, net, op, st));
+    if (fused) {
+      // SeparableConv2D as one kernel each: [ReLU] -> depthwise -> pointwise + BN [+ ReLU]
+      TMAT_TRY(dwpw_run(ctx, P, B, S, D.cin, D.dw1, i != 0, D.pw1, D.sh1, D.f, 1, a1, st));
+      TMAT_TRY(dwpw_run(ctx, a1, B, S, D.f, D.dw2, 0, D.pw2, D.sh2, D.f, 0, b2, st));
+    } else {
+      TMAT_TRY(dwconv_run(ctx, P, B, S, D.cin, D.dw1, i != 0, d1, nullptr, st));
+      ConvOp op;
+      op.name = "down.pw1"; op.a0 = d1; op.a0_C = D.cin; op.B = B; op.H = S; op.W = S; set_tap1x1(op);
+      op.wmat = D.pw1; op.K = D.cin; op.shift = D.sh1; op.Cout = op.Npad = D.f; op.epi = EPI_STORE; op.relu = 1;
+      op.out = a1;
+      TMAT_TRY(run_op(ctx, net, op, st));
+      TMAT_TRY(dwconv_run(ctx, a1, B, S, D.f, D.dw2, 0, d2, nullptr, st));
+      ConvOp op2;
+      op2.name = "down.pw2"; op2.a0 = d2; op2.a0_C = D.f; op2.B = B; op2.H = S; op2.W = S; set_tap1x1(op2);
+      op2.wmat = D.pw2; op2.K = D.f; op2.shift = D.sh2; op2.Cout = op2.Npad = D.f; op2.epi = EPI_STORE; op2.relu = 0;
+      op2.out = b2;
+      TMAT_TRY(run_op(ctx, net, op2, st));
+    }
     record(net, (std::string("down") + std::to_string(i) + ".r1").c_str(), a1, B, S, S, D.f);
-    TMAT_TRY(dwconv_run(ctx, a1, B, S, D.f, D.dw2, 0, d2, nullptr, st));
-    ConvOp op2;
-    op2.name = "down.pw2"; op2.a0 = d2; op2.a0_C = D.f; op2.B = B; op2.H = S; op2.W = S; set_tap1x1(op2);
-    op2.wmat = D.pw2; op2.K = D.f; op2.shift = D.sh2; op2.Cout = op2.Npad = D.f; op2.epi = EPI_STORE; op2.relu = 0;
-    op2.out = b2;
-    TMAT_TRY(run_op(ctx, net, op2, st));
     record(net, (std::string("down") + std::to_string(i) + ".b2").c_str(), b2, B, S, S, D.f);
     // MaxPool(3, 2, same)(b2) + residual 1x1 stride-2 conv of the block input
     TMAT_TRY(maxpool_run(ctx, b2, B, S, D.f, pooled, st));
     ConvOp op3;
-    op3.name = "down.res"; op3.a0 = xs; op3.a0_C = D.cin; op3.B = B; op3.H = S / 2; op3.W = S / 2; set_tap1x1(op3);
+    op3.name = "down.res"; op3.a0 = P; op3.a0_C = D.cin; op3.a0_stride = 2; op3.B = B; op3.H = S / 2; op3.W = S / 2;
+    set_tap1x1(op3);
     op3.wmat = D.res; op3.K = D.cin; op3.shift = D.shres; op3.Cout = op3.Npad = D.f; op3.epi = EPI_STORE;
     op3.relu = 0; op3.add_src = pooled; op3.add_shift = 0; op3.out = out; op3.out2 = outr;
     TMAT_TRY(run_op(ctx, net, op3, st));
@@ -492,6 +501,7 @@ extern "C" int tmat_unet_load(tmat_ctx* ctx, const tmat_unet_desc* desc, int n_a
   for (int i = 0; i < 4; ++i) net->fc[i] = desc->filter_counts[i];
   net->device = ctx->device;
   net->use_tc = (desc->impl == 2) || (desc->impl == 0 && mult64);
+  { const char* e = getenv("TMAT_NO_FUSE_DW"); net->fuse_dw = !(e && atoi(e) != 0); }
   WeightSet ws;
   for (int i = 0; i < n_arrays; ++i) ws.m[names[i]] = std::make_pair(arrays_host[i], sizes[i]);
   int r = pack_weights(net, ws);
@@ -797,6 +807,44 @@ extern "C" int tmat_debug_conv_selftest(tmat_ctx* ctx, int B, int H, int W, int 
     max_abs_diff_kernel<bf16><<<256, 256>>>(o1, o2, (int64_t)out_elems, stats);
     if (dual) max_abs_diff_kernel<bf16><<<256, 256>>>(r1, r2, (int64_t)out_elems, stats);
   }
+  float h[2];
+  CUDA_TRY(cudaMemcpy(h, stats, 8, cudaMemcpyDeviceToHost));
+  *max_abs_diff = h[0];
+  *max_abs_ref = h[1];
+  return TMAT_OK;
+}
+
+// Fused depthwise+pointwise kernel vs the unfused pair (dwconv_kernel + CUDA-core GEMM) on random data.
+extern "C" int tmat_debug_dwpw_selftest(tmat_ctx* ctx, int B, int S, int C, int N, int relu_in, int relu_out,
+                                        uint64_t seed, double* max_abs_diff, double* max_abs_ref) {
+  TMAT_REQUIRE(ctx && max_abs_diff && max_abs_ref, "tmat_debug_dwpw_selftest: NULL argument");
+  TMAT_REQUIRE(dwpw_supported(B, S, C, N), "tmat_debug_dwpw_selftest: shape not supported by the fused kernel");
+  TMAT_TRY(arena_reset(ctx));
+  size_t px = (size_t)B * S * S;
+  bf16 *in, *d1, *w, *o1, *o2;
+  float *dw, *shift, *stats;
+  TMAT_TRY(arena_get(ctx, px * C, &in));
+  TMAT_TRY(arena_get(ctx, px * C, &d1));
+  TMAT_TRY(arena_get(ctx, (size_t)N * C, &w));
+  TMAT_TRY(arena_get(ctx, px * N, &o1));
+  TMAT_TRY(arena_get(ctx, px * N, &o2));
+  TMAT_TRY(arena_get(ctx, (size_t)9 * C, &dw));
+  TMAT_TRY(arena_get(ctx, (size_t)N, &shift));
+  TMAT_TRY(arena_get(ctx, 2, &stats));
+  fill_random_bf16<<<(unsigned)cdiv64(px * C, 256), 256>>>(in, (int64_t)(px * C), seed + 1, 1.f);
+  fill_random_bf16<<<(unsigned)cdiv64((int64_t)N * C, 256), 256>>>(w, (int64_t)N * C, seed + 2, 1.f / sqrtf((float)C));
+  fill_random_f32<<<cdiv(9 * C, 256), 256>>>(dw, 9 * C, seed + 3, 0.5f);
+  fill_random_f32<<<cdiv(N, 256), 256>>>(shift, N, seed + 4, 0.5f);
+  CUDA_TRY(cudaMemsetAsync(stats, 0, 8, 0));
+  CUDA_TRY(cudaMemsetAsync(o1, 0xff, px * N * 2, 0));
+  CUDA_TRY(cudaMemsetAsync(o2, 0x7f, px * N * 2, 0));
+  TMAT_TRY(dwconv_run(ctx, in, B, S, C, dw, relu_in, d1, nullptr, 0));
+  ConvOp op;
+  op.name = "dwpw.ref"; op.a0 = d1; op.a0_C = C; op.B = B; op.H = S; op.W = S; set_tap1x1(op);
+  op.wmat = w; op.K = C; op.shift = shift; op.Cout = op.Npad = N; op.epi = EPI_STORE; op.relu = relu_out; op.out = o1;
+  TMAT_TRY(conv_run_simt(ctx, op, 0));
+  TMAT_TRY(dwpw_run(ctx, in, B, S, C, dw, relu_in, w, shift, N, relu_out, o2, 0));
+  max_abs_diff_kernel<bf16><<<256, 256>>>(o1, o2, (int64_t)(px * N), stats);
   float h[2];
   CUDA_TRY(cudaMemcpy(h, stats, 8, cudaMemcpyDeviceToHost));
   *max_abs_diff = h[0];

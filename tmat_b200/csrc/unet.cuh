@@ -25,6 +25,8 @@ struct ConvOp {
   // when ngroups == 1) one 1x1 view of a1
   const bf16* a0 = nullptr; int a0_C = 0;
   const bf16* a1 = nullptr; int a1_C = 0;
+  int a0_stride = 1;                // a0 is a dense (B, H*s, W*s, a0_C) tensor read at pixels (y*s, x*s): the
+                                    // stride-2 1x1 residual conv of the down blocks (1 tap only)
   int B = 0, H = 0, W = 0;          // pixel grid of the GEMM rows (= resolution of a0/a1)
   int ngroups = 1;                  // independent column groups with their own tap lists
   int ntaps = 1;                    // taps per group
@@ -94,3 +96,9 @@ int dwconv_run(tmat_ctx* ctx, const bf16* in, int B, int S, int C, const float* 
 // MaxPool2D(3, strides=2, padding="same") on an even size (pads 0 before / 1 after, padding excluded
 // from the max; models.py:139): in (B,S,S,C) bf16 -> out (B,S/2,S/2,C) bf16.
 int maxpool_run(tmat_ctx* ctx, const bf16* in, int B, int S, int C, bf16* out, cudaStream_t st);
+
+// Fused SeparableConv2D on the tcgen05 path (conv_dwpw.cu): out = [relu](BN(pointwise(depthwise([relu](in)))))
+bool dwpw_supported(int B, int S, int C, int N);
+int dwpw_run(tmat_ctx* ctx, const bf16* in, int B, int S, int C, const float* dw /*[9][C]*/, int relu_in,
+             const bf16* wmat /*[N][C], BN scale folded*/, const float* shift, int N, int relu_out, bf16* out,
+             cudaStream_t st);
