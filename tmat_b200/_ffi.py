@@ -63,6 +63,7 @@ SIGNATURES = {
     "tmat_unet_debug_tap": [_vp, _vp, C.c_char_p, _vp, _i64, C.POINTER(_i64)],
     "tmat_debug_conv_selftest": [_vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, C.c_uint64,
                                  C.POINTER(C.c_double), C.POINTER(C.c_double)],
+    "tmat_debug_set_halo_mode": [_i],
     "tmat_debug_dwpw_selftest": [_vp, _i, _i, _i, _i, _i, _i, C.c_uint64, C.POINTER(C.c_double),
                                  C.POINTER(C.c_double)],
     "tmat_unet_flops_per_patch": [C.POINTER(UnetDesc), C.POINTER(C.c_double)],

@@ -43,15 +43,36 @@ __device__ __forceinline__ uint2 ld_shared_v2(uint32_t addr) {
 __device__ __forceinline__ void st_shared_v2(uint32_t addr, uint2 v) {
   asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(addr), "r"(v.x), "r"(v.y) : "memory");
 }
-__device__ __forceinline__ void unpack4s(const uint2& v, bool relu, float (&f)[4]) {
-  __nv_bfloat162 h0 = *reinterpret_cast<const __nv_bfloat162*>(&v.x);
-  __nv_bfloat162 h1 = *reinterpret_cast<const __nv_bfloat162*>(&v.y);
+// packed fp32 pairs (Blackwell FFMA2): two channels per instruction
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+  f32x2 d;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "f"(lo), "f"(hi));
+  return d;
+}
+__device__ __forceinline__ f32x2 ffma2(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ f32x2 fmul2(f32x2 a, f32x2 b) {
+  f32x2 d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+// bf16x2 (channel c in the low half, c+1 in the high half) -> fp32 pair, optional ReLU
+__device__ __forceinline__ f32x2 bf2_to_f2(uint32_t x, bool relu) {
   if (relu) {
-    const __nv_bfloat162 z = __floats2bfloat162_rn(0.f, 0.f);
-    h0 = __hmax2(h0, z); h1 = __hmax2(h1, z);
+    __nv_bfloat162 h = *reinterpret_cast<__nv_bfloat162*>(&x);
+    h = __hmax2(h, __floats2bfloat162_rn(0.f, 0.f));
+    x = *reinterpret_cast<uint32_t*>(&h);
   }
-  float2 a = __bfloat1622float2(h0), b = __bfloat1622float2(h1);
-  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y;
+  return pack2(__uint_as_float(x << 16), __uint_as_float(x & 0xffff0000u));
+}
+__device__ __forceinline__ uint32_t f2_to_bf2(f32x2 v) {
+  float lo, hi;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+  return pack_bf16x2(lo, hi);
 }
 
 template <int BN>
@@ -231,40 +252,47 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
     int stage = 0, rs = 0; uint32_t phase = 0, rphase = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
       for (int ks = 0; ks < p.nk; ++ks) {
-        float wr[9][4];
+        f32x2 wr[9][2];
 #pragma unroll
         for (int tp = 0; tp < 9; ++tp) {
           float4 wv = __ldg(reinterpret_cast<const float4*>(p.dw + tp * p.C + ks * KSLAB + h * 4));
-          wr[tp][0] = wv.x; wr[tp][1] = wv.y; wr[tp][2] = wv.z; wr[tp][3] = wv.w;
+          wr[tp][0] = pack2(wv.x, wv.y); wr[tp][1] = pack2(wv.z, wv.w);
         }
         mbar_wait(rfull_bar(rs), rphase);
         mbar_wait(empty_bar(stage), phase ^ 1);
         const uint32_t rbase = raw_base + rs * p.raw_bytes;
         const uint32_t abase = smem_base + stage * STAGE_BYTES;
+        // swizzled address of this thread's 8 bytes of raw pixel rp / A row r
+        auto raw_addr = [&](uint32_t rp) { return rbase + rp * 128u + (((jch ^ (rp & 7u)) << 4) | sub); };
         for (int ci = cslot; ci < ncols; ci += 16) {
           const int n = ci >> p.tw_log, x = ci & (TW - 1);
-          float acc0[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f}, acc2[4];
+          f32x2 acc0[2] = {0ull, 0ull}, acc1[2] = {0ull, 0ull}, acc2[2];
           uint32_t rp = (uint32_t)((n * RH) * RW + x);          // raw pixel (n, yy = 0, xx = x)
           uint32_t ar = (uint32_t)((n * TH) * TW + x);          // A row of output (n, y = 0, x)
-          for (int yy = 0; yy < RH; ++yy, rp += RW) {
-            float fl[4], fc[4], fr[4];
-            unpack4s(ld_shared_v2(rbase + rp * 128u + (((jch ^ (rp & 7u)) << 4) | sub)), relu, fl);
-            unpack4s(ld_shared_v2(rbase + (rp + 1) * 128u + (((jch ^ ((rp + 1) & 7u)) << 4) | sub)), relu, fc);
-            unpack4s(ld_shared_v2(rbase + (rp + 2) * 128u + (((jch ^ ((rp + 2) & 7u)) << 4) | sub)), relu, fr);
+          uint2 nl = ld_shared_v2(raw_addr(rp)), nc = ld_shared_v2(raw_addr(rp + 1)), nr = ld_shared_v2(raw_addr(rp + 2));
+          for (int yy = 0; yy < RH; ++yy) {
+            const uint2 cl = nl, cc = nc, cr = nr;
+            rp += RW;
+            if (yy + 1 < RH) {                                  // prefetch the next raw row
+              nl = ld_shared_v2(raw_addr(rp)); nc = ld_shared_v2(raw_addr(rp + 1)); nr = ld_shared_v2(raw_addr(rp + 2));
+            }
+            const f32x2 fl[2] = {bf2_to_f2(cl.x, relu), bf2_to_f2(cl.y, relu)};
+            const f32x2 fc[2] = {bf2_to_f2(cc.x, relu), bf2_to_f2(cc.y, relu)};
+            const f32x2 fr[2] = {bf2_to_f2(cr.x, relu), bf2_to_f2(cr.y, relu)};
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
+            for (int c = 0; c < 2; ++c) {
               // raw row yy is tap row ky=2 of output yy-2, ky=1 of output yy-1, ky=0 of output yy
-              acc0[c] = fmaf(fl[c], wr[6][c], acc0[c]); acc0[c] = fmaf(fc[c], wr[7][c], acc0[c]); acc0[c] = fmaf(fr[c], wr[8][c], acc0[c]);
-              acc1[c] = fmaf(fl[c], wr[3][c], acc1[c]); acc1[c] = fmaf(fc[c], wr[4][c], acc1[c]); acc1[c] = fmaf(fr[c], wr[5][c], acc1[c]);
-              acc2[c] = fl[c] * wr[0][c];               acc2[c] = fmaf(fc[c], wr[1][c], acc2[c]); acc2[c] = fmaf(fr[c], wr[2][c], acc2[c]);
+              acc0[c] = ffma2(fl[c], wr[6][c], acc0[c]); acc0[c] = ffma2(fc[c], wr[7][c], acc0[c]); acc0[c] = ffma2(fr[c], wr[8][c], acc0[c]);
+              acc1[c] = ffma2(fl[c], wr[3][c], acc1[c]); acc1[c] = ffma2(fc[c], wr[4][c], acc1[c]); acc1[c] = ffma2(fr[c], wr[5][c], acc1[c]);
+              acc2[c] = fmul2(fl[c], wr[0][c]);          acc2[c] = ffma2(fc[c], wr[1][c], acc2[c]); acc2[c] = ffma2(fr[c], wr[2][c], acc2[c]);
             }
             if (yy >= 2) {
-              uint2 o = make_uint2(pack_bf16x2(acc0[0], acc0[1]), pack_bf16x2(acc0[2], acc0[3]));
-              st_shared_v2(abase + ar * 128u + (((jch ^ (ar & 7u)) << 4) | sub), o);
+              st_shared_v2(abase + ar * 128u + (((jch ^ (ar & 7u)) << 4) | sub),
+                           make_uint2(f2_to_bf2(acc0[0]), f2_to_bf2(acc0[1])));
               ar += TW;
             }
 #pragma unroll
-            for (int c = 0; c < 4; ++c) { acc0[c] = acc1[c]; acc1[c] = acc2[c]; }
+            for (int c = 0; c < 2; ++c) { acc0[c] = acc1[c]; acc1[c] = acc2[c]; }
           }
         }
         fence_proxy_async();

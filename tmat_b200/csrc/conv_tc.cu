@@ -31,7 +31,6 @@ namespace {
 
 constexpr int MAX_KSTEPS = 160;                    // over all groups
 constexpr int TC_THREADS = 192;
-constexpr int N_STG = 2;
 
 struct TcParams {
   int tw_log, th_log, tn_log;   // tile = 2^tw x 2^th pixels x 2^tn images (product 128)
@@ -40,12 +39,6 @@ struct TcParams {
   int npad;                     // GEMM columns per group
   uint16_t kstep[MAX_KSTEPS];   // [group][nk]: bit0 src | bits1-2 dy+1 | bits3-4 dx+1 | bits5.. c0/64
   EpiParams e;
-};
-
-// tensor maps of the output: m[q] = view of parity q (EPI_STORE: m[0] = the tensor), m2 = ReLU'd copy
-struct TcOutMaps {
-  CUtensorMap m[4];
-  CUtensorMap m2;
 };
 
 // ---- the kernel -------------------------------------------------------------------------------
@@ -185,100 +178,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
       mbar_wait(tfull_bar(as), aphase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
-      if constexpr (BN >= 64) {
-        const bool dual = (e.out2 != nullptr);
-        const bf16* addp = nullptr;
-        if (e.add_src != nullptr && valid) {
-          const int s = e.add_shift;
-          const int Ha = (e.H + (1 << s) - 1) >> s, Wa = (e.W + (1 << s) - 1) >> s;
-          addp = e.add_src + (((int64_t)b * Ha + (y >> s)) * Wa + (x >> s)) * e.Cout;
-        }
-#pragma unroll 1
-        for (int c64 = 0; c64 < BN; c64 += 64) {
-          const int col = nt * BN + c64;                        // column within the group
-          int par = 0, ch0 = col;
-          if (e.mode == EPI_PAR) { par = g * e.ppg + col / e.Cout; ch0 = col % e.Cout; }
-          // the staging buffer(s) about to be written must have been read out by their last store
-          if (leader) { if (dual) tma_store_wait_read<0>(); else tma_store_wait_read<1>(); }
-          epi_bar_sync();
-          const uint32_t buf0 = stg_base + (dual ? 0 : sbuf * STG_BYTES) + stg_row;
-          const uint32_t buf1 = stg_base + STG_BYTES + stg_row;
-#pragma unroll
-          for (int half = 0; half < 2; ++half) {
-            uint32_t rr[32];
-            tmem_ld32(taddr + c64 + half * 32, rr);
-            tmem_ld_wait();
-            float v[32];
-#pragma unroll
-            for (int i = 0; i < 32; i += 4) {
-              float4 s = __ldg(reinterpret_cast<const float4*>(e.shift + ch0 + half * 32 + i));
-              v[i] = __uint_as_float(rr[i]) + s.x; v[i + 1] = __uint_as_float(rr[i + 1]) + s.y;
-              v[i + 2] = __uint_as_float(rr[i + 2]) + s.z; v[i + 3] = __uint_as_float(rr[i + 3]) + s.w;
-            }
-            if (addp != nullptr) {
-              const uint4* ap = reinterpret_cast<const uint4*>(addp + ch0 + half * 32);
-#pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                uint4 u = __ldg(ap + j);
-                const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                  float2 t = __bfloat1622float2(h[i]);
-                  v[8 * j + 2 * i] += t.x; v[8 * j + 2 * i + 1] += t.y;
-                }
-              }
-            }
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const uint32_t off = (((uint32_t)(half * 4 + j)) ^ sw) << 4;   // 128-byte swizzle: chunk ^= row % 8
-              float f[8];
-#pragma unroll
-              for (int i = 0; i < 8; ++i) f[i] = e.relu ? fmaxf(v[8 * j + i], 0.f) : v[8 * j + i];
-              uint4 o;
-              o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]);
-              o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
-              st_shared_v4(buf0 + off, o);
-              if (dual) {
-                o.x = pack_bf16x2(fmaxf(v[8 * j], 0.f), fmaxf(v[8 * j + 1], 0.f));
-                o.y = pack_bf16x2(fmaxf(v[8 * j + 2], 0.f), fmaxf(v[8 * j + 3], 0.f));
-                o.z = pack_bf16x2(fmaxf(v[8 * j + 4], 0.f), fmaxf(v[8 * j + 5], 0.f));
-                o.w = pack_bf16x2(fmaxf(v[8 * j + 6], 0.f), fmaxf(v[8 * j + 7], 0.f));
-                st_shared_v4(buf1 + off, o);
-              }
-            }
-          }
-          if (c64 + 64 >= BN) {                  // accumulator fully read: hand the TMEM buffer back
-            tc_fence_before();
-            mbar_arrive(tempty_bar(as));
-          }
-          fence_proxy_async();                   // generic-proxy smem writes -> visible to the TMA unit
-          epi_bar_sync();
-          if (leader) {
-            tma_store_4d(&om.m[par], buf0 - stg_row, ch0, x0, y0, b0);
-            if (dual) tma_store_4d(&om.m2, buf1 - stg_row, ch0, x0, y0, b0);
-            tma_store_commit();
-          }
-          if (!dual) sbuf ^= 1;
-        }
-      } else {
-        // head: 4 output-pixel parities in columns 0..3
-        uint32_t rr[16];
-        tmem_ld16(taddr, rr);
-        tmem_ld_wait();
-        tc_fence_before();
-        mbar_arrive(tempty_bar(as));
-        if (valid) {
-          float o[4];
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            float v = __uint_as_float(rr[i]) + __ldg(e.shift + i);
-            o[i] = e.logits ? v : sigmoid_f(v);
-          }
-          float* dst = e.out_f32 + ((int64_t)b * 2 * e.H + 2 * y) * (2 * e.W) + 2 * x;
-          *reinterpret_cast<float2*>(dst) = make_float2(o[0], o[1]);
-          *reinterpret_cast<float2*>(dst + 2 * e.W) = make_float2(o[2], o[3]);
-        }
-      }
+      tc_epilogue_tile<BN>(e, om, taddr, g, nt, x0, y0, b0, x, y, b, valid, stg_base, stg_row, sw, leader, sbuf,
+                           tempty_bar(as));
     }
     if (leader) tma_store_wait_all();            // smem must outlive the last store's read
   }
@@ -400,6 +301,7 @@ static int launch_tc(tmat_ctx* ctx, const CUtensorMap& a0, const CUtensorMap& a1
 }
 
 int conv_run_tc(tmat_ctx* ctx, const ConvOp& op, cudaStream_t st) {
+  if (conv_halo_supported(op)) return conv_run_halo(ctx, op, conv_halo_mode(), st);
   TMAT_REQUIRE(conv_tc_supported(op), "conv_tc(%s): shape not supported by the tcgen05 path", op.name);
   TcParams p;
   memset(&p, 0, sizeof(p));

@@ -102,3 +102,9 @@ bool dwpw_supported(int B, int S, int C, int N);
 int dwpw_run(tmat_ctx* ctx, const bf16* in, int B, int S, int C, const float* dw /*[9][C]*/, int relu_in,
              const bf16* wmat /*[N][C], BN scale folded*/, const float* shift, int N, int relu_out, bf16* out,
              cudaStream_t st);
+
+// 3x3 convolution with the haloed A tile loaded once per tile (conv_halo.cu); conv_run_tc dispatches to it
+// for single-group 3x3 ops with N <= 128 (and the head) when conv_halo_supported().
+bool conv_halo_supported(const ConvOp& op);
+int conv_halo_mode();
+int conv_run_halo(tmat_ctx* ctx, const ConvOp& op, int mode, cudaStream_t st);
