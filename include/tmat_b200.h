@@ -142,8 +142,7 @@ int tmat_unet_debug_tap(tmat_ctx* ctx, tmat_unet* net, const char* name, float* 
 int tmat_debug_conv_selftest(tmat_ctx* ctx, int B, int H, int W, int C0, int C1, int Cout, int ntaps,
                              int epi, int relu, int dual, int addend, uint64_t seed,
                              double* max_abs_diff, double* max_abs_ref);
-/* Debug switch of the haloed-tile 3x3 kernel (conv_halo.cu): 0 off, 1 raw row pitch 10 pixels,
- * 2 pitch 10 + descriptor base offset, 3 pitch 16, 4 pitch 16 + base offset.  Default: env TMAT_HALO or 1. */
+/* Debug switch of the haloed-tile 3x3 kernel (conv_halo.cu): 0 off, 1 on.  Default: env TMAT_HALO or 1. */
 int tmat_debug_set_halo_mode(int mode);
 /* Self-test hook: the fused SeparableConv2D kernel (depthwise 3x3 computed into the tcgen05 A operand)
  * vs the unfused pair (depthwise kernel, CUDA-core GEMM) on random data. */

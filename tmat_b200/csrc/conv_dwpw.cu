@@ -60,19 +60,52 @@ __device__ __forceinline__ f32x2 fmul2(f32x2 a, f32x2 b) {
   asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
   return d;
 }
-// bf16x2 (channel c in the low half, c+1 in the high half) -> fp32 pair, optional ReLU
-__device__ __forceinline__ f32x2 bf2_to_f2(uint32_t x, bool relu) {
-  if (relu) {
-    __nv_bfloat162 h = *reinterpret_cast<__nv_bfloat162*>(&x);
-    h = __hmax2(h, __floats2bfloat162_rn(0.f, 0.f));
-    x = *reinterpret_cast<uint32_t*>(&h);
-  }
-  return pack2(__uint_as_float(x << 16), __uint_as_float(x & 0xffff0000u));
-}
 __device__ __forceinline__ uint32_t f2_to_bf2(f32x2 v) {
   float lo, hi;
   asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
   return pack_bf16x2(lo, hi);
+}
+// bf16x2 (channel c in the low half, c+1 in the high half) -> fp32 pair; `floor2` is bf16x2 (0, 0) for a
+// fused ReLU on the input and (-inf, -inf) otherwise, so the max is branch-free
+__device__ __forceinline__ f32x2 bf2_to_f2(uint32_t x, uint32_t floor2) {
+  __nv_bfloat162 h = __hmax2(*reinterpret_cast<__nv_bfloat162*>(&x), *reinterpret_cast<__nv_bfloat162*>(&floor2));
+  x = *reinterpret_cast<uint32_t*>(&h);
+  return pack2(__uint_as_float(x << 16), __uint_as_float(x & 0xffff0000u));
+}
+
+// One tile column of the depthwise 3x3 for a thread's 4 channels, RH = TH_C + 2 raw rows, fully unrolled:
+// raw row yy is tap row ky of output row yy - ky; the three live accumulators rotate by compile-time index.
+template <int TH_C>
+__device__ __forceinline__ void dw_column(uint32_t rbase_sub, uint32_t abase_sub, uint32_t rp0, uint32_t ar0,
+                                          uint32_t RW, uint32_t TW, uint32_t jch, uint32_t floor2,
+                                          const f32x2 (&wr)[9][2]) {
+  f32x2 acc[3][2];
+  auto raw_addr = [&](uint32_t rp) { return rbase_sub + (rp << 7) + ((jch ^ (rp & 7u)) << 4); };
+#pragma unroll
+  for (int yy = 0; yy < TH_C + 2; ++yy) {
+    const uint32_t rp = rp0 + (uint32_t)yy * RW;
+    const uint2 cl = ld_shared_v2(raw_addr(rp)), cc = ld_shared_v2(raw_addr(rp + 1)), cr = ld_shared_v2(raw_addr(rp + 2));
+    const f32x2 f[3][2] = {{bf2_to_f2(cl.x, floor2), bf2_to_f2(cl.y, floor2)},
+                           {bf2_to_f2(cc.x, floor2), bf2_to_f2(cc.y, floor2)},
+                           {bf2_to_f2(cr.x, floor2), bf2_to_f2(cr.y, floor2)}};
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky) {
+      const int o = yy - ky;                     // output row this raw row feeds through tap row ky
+      if (o < 0 || o >= TH_C) continue;
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        f32x2 a = (ky == 0) ? fmul2(f[0][c], wr[0][c]) : ffma2(f[0][c], wr[3 * ky][c], acc[o % 3][c]);
+        a = ffma2(f[1][c], wr[3 * ky + 1][c], a);
+        acc[o % 3][c] = ffma2(f[2][c], wr[3 * ky + 2][c], a);
+      }
+    }
+    if (yy >= 2) {
+      const int o = yy - 2;
+      const uint32_t ar = ar0 + (uint32_t)o * TW;
+      st_shared_v2(abase_sub + (ar << 7) + ((jch ^ (ar & 7u)) << 4),
+                   make_uint2(f2_to_bf2(acc[o % 3][0]), f2_to_bf2(acc[o % 3][1])));
+    }
+  }
 }
 
 template <int BN>
@@ -151,32 +184,33 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
       }
     }
   } else if (warp == 1) {
-    // ================= MMA issuer =================
-    constexpr uint32_t idesc = umma_idesc<BN>();
-    int stage = 0; uint32_t phase = 0;
-    int it = 0;
-    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
-      const int as = it & 1;
-      const uint32_t aphase = (it >> 1) & 1;
-      mbar_wait(tempty_bar(as), aphase ^ 1);
-      tc_fence_after();
-      const uint32_t tmem_d = tmem_base + as * BN;
-      for (int ks = 0; ks < p.nk; ++ks) {
-        mbar_wait(full_bar(stage), phase);
+    // ================= MMA issuer (one thread runs the whole loop) =================
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc<BN>();
+      int stage = 0; uint32_t phase = 0;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+        const int as = it & 1;
+        const uint32_t aphase = (it >> 1) & 1;
+        mbar_wait(tempty_bar(as), aphase ^ 1);
         tc_fence_after();
-        if (lane == 0) {
-          uint32_t sa = smem_base + stage * STAGE_BYTES;
-          uint64_t adesc = umma_desc_sw128(sa);
-          uint64_t bdesc = umma_desc_sw128(sa + A_STAGE_BYTES);
+        const uint32_t tmem_d = tmem_base + as * BN;
+        for (int ks = 0; ks < p.nk; ++ks) {
+          mbar_wait(full_bar(stage), phase);
+          tc_fence_after();
+          const uint32_t sa = smem_base + stage * STAGE_BYTES;
+          const uint64_t adesc = umma_desc_sw128(sa);
+          const uint64_t bdesc = umma_desc_sw128(sa + A_STAGE_BYTES);
+          umma_bf16(tmem_d, adesc, bdesc, idesc, ks != 0);
 #pragma unroll
-          for (int k = 0; k < KSLAB / 16; ++k) umma_bf16(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (ks | k) != 0);
+          for (int k = 1; k < KSLAB / 16; ++k) umma_bf16(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, 1u);
           umma_commit(empty_bar(stage));
           if (ks == p.nk - 1) umma_commit(tfull_bar(as));
+          if (++stage == p.n_stage) { stage = 0; phase ^= 1; }
         }
-        __syncwarp();
-        if (++stage == p.n_stage) { stage = 0; phase ^= 1; }
       }
     }
+    __syncwarp();
   } else if (warp < 6) {
     // ================= epilogue (warps 2..5) =================
     const int q = warp & 3;
@@ -248,7 +282,7 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
     const int cslot = t >> 4;               // column slot 0..15
     const int ncols = TW * TN;
     const int RW = TW + 2, RH = TH + 2;
-    const bool relu = p.relu_in != 0;
+    const uint32_t floor2 = p.relu_in ? 0u : 0xff80ff80u;   // bf16x2 (0, 0) or (-inf, -inf)
     int stage = 0, rs = 0; uint32_t phase = 0, rphase = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
       for (int ks = 0; ks < p.nk; ++ks) {
@@ -262,38 +296,15 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
         mbar_wait(empty_bar(stage), phase ^ 1);
         const uint32_t rbase = raw_base + rs * p.raw_bytes;
         const uint32_t abase = smem_base + stage * STAGE_BYTES;
-        // swizzled address of this thread's 8 bytes of raw pixel rp / A row r
-        auto raw_addr = [&](uint32_t rp) { return rbase + rp * 128u + (((jch ^ (rp & 7u)) << 4) | sub); };
         for (int ci = cslot; ci < ncols; ci += 16) {
           const int n = ci >> p.tw_log, x = ci & (TW - 1);
-          f32x2 acc0[2] = {0ull, 0ull}, acc1[2] = {0ull, 0ull}, acc2[2];
-          uint32_t rp = (uint32_t)((n * RH) * RW + x);          // raw pixel (n, yy = 0, xx = x)
-          uint32_t ar = (uint32_t)((n * TH) * TW + x);          // A row of output (n, y = 0, x)
-          uint2 nl = ld_shared_v2(raw_addr(rp)), nc = ld_shared_v2(raw_addr(rp + 1)), nr = ld_shared_v2(raw_addr(rp + 2));
-          for (int yy = 0; yy < RH; ++yy) {
-            const uint2 cl = nl, cc = nc, cr = nr;
-            rp += RW;
-            if (yy + 1 < RH) {                                  // prefetch the next raw row
-              nl = ld_shared_v2(raw_addr(rp)); nc = ld_shared_v2(raw_addr(rp + 1)); nr = ld_shared_v2(raw_addr(rp + 2));
-            }
-            const f32x2 fl[2] = {bf2_to_f2(cl.x, relu), bf2_to_f2(cl.y, relu)};
-            const f32x2 fc[2] = {bf2_to_f2(cc.x, relu), bf2_to_f2(cc.y, relu)};
-            const f32x2 fr[2] = {bf2_to_f2(cr.x, relu), bf2_to_f2(cr.y, relu)};
-#pragma unroll
-            for (int c = 0; c < 2; ++c) {
-              // raw row yy is tap row ky=2 of output yy-2, ky=1 of output yy-1, ky=0 of output yy
-              acc0[c] = ffma2(fl[c], wr[6][c], acc0[c]); acc0[c] = ffma2(fc[c], wr[7][c], acc0[c]); acc0[c] = ffma2(fr[c], wr[8][c], acc0[c]);
-              acc1[c] = ffma2(fl[c], wr[3][c], acc1[c]); acc1[c] = ffma2(fc[c], wr[4][c], acc1[c]); acc1[c] = ffma2(fr[c], wr[5][c], acc1[c]);
-              acc2[c] = fmul2(fl[c], wr[0][c]);          acc2[c] = ffma2(fc[c], wr[1][c], acc2[c]); acc2[c] = ffma2(fr[c], wr[2][c], acc2[c]);
-            }
-            if (yy >= 2) {
-              st_shared_v2(abase + ar * 128u + (((jch ^ (ar & 7u)) << 4) | sub),
-                           make_uint2(f2_to_bf2(acc0[0]), f2_to_bf2(acc0[1])));
-              ar += TW;
-            }
-#pragma unroll
-            for (int c = 0; c < 2; ++c) { acc0[c] = acc1[c]; acc1[c] = acc2[c]; }
-          }
+          const uint32_t rp0 = (uint32_t)((n * RH) * RW + x);   // raw pixel (n, yy = 0, xx = x)
+          const uint32_t ar0 = (uint32_t)((n * TH) * TW + x);   // A row of output (n, y = 0, x)
+          if (TH == 8) dw_column<8>(rbase + sub, abase + sub, rp0, ar0, RW, TW, jch, floor2, wr);
+          else if (TH == 4) dw_column<4>(rbase + sub, abase + sub, rp0, ar0, RW, TW, jch, floor2, wr);
+          else if (TH == 16) dw_column<16>(rbase + sub, abase + sub, rp0, ar0, RW, TW, jch, floor2, wr);
+          else if (TH == 2) dw_column<2>(rbase + sub, abase + sub, rp0, ar0, RW, TW, jch, floor2, wr);
+          else dw_column<1>(rbase + sub, abase + sub, rp0, ar0, RW, TW, jch, floor2, wr);
         }
         fence_proxy_async();
         __syncwarp();
@@ -319,8 +330,19 @@ struct DwpwPlan {
 bool plan_dwpw(int B, int S, int C, int N, DwpwPlan* pl) {
   if (C % KSLAB != 0 || N % 64 != 0 || C / KSLAB > 64) return false;
   tc_choose_tile(B, S, S, &pl->tw_log, &pl->th_log, &pl->tn_log);
+  {
+    // the depthwise warps re-read 2 halo rows per tile column: prefer 8-row tiles (16x8x1, 8x8x2, 4x8x4 ...)
+    // when they cover the image with at most 10 % more tiles than the best shape
+    int64_t best = (int64_t)cdiv(S, 1 << pl->tw_log) * cdiv(S, 1 << pl->th_log) * cdiv(B, 1 << pl->tn_log);
+    int64_t b8 = -1; int a8 = 0;
+    for (int a = 4; a >= 0; --a) {
+      int64_t n = (int64_t)cdiv(S, 1 << a) * cdiv(S, 8) * cdiv(B, 1 << (4 - a));
+      if (b8 < 0 || n < b8) { b8 = n; a8 = a; }
+    }
+    if (b8 * 10 <= best * 11) { pl->tw_log = a8; pl->th_log = 3; pl->tn_log = 4 - a8; }
+  }
   const int TW = 1 << pl->tw_log, TH = 1 << pl->th_log, TN = 1 << pl->tn_log;
-  if (TW * TN < 1 || TW + 2 > 256 || TH + 2 > 256) return false;
+  if (TH > 16 || TW + 2 > 256) return false;
   pl->BN = N % 256 == 0 ? 256 : (N % 128 == 0 ? 128 : 64);
   pl->raw_tx = (TW + 2) * (TH + 2) * TN * 128;
   pl->raw_bytes = (pl->raw_tx + 1023) / 1024 * 1024;

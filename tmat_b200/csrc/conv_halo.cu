@@ -25,14 +25,12 @@ constexpr int HALO_THREADS = 192;
 constexpr int HTW = 8, HTH = 16;                 // tile: 8 x 16 pixels of one image
 constexpr int MAX_STAGES = 8;
 constexpr int MAX_RAW = 4;
+constexpr int PITCH = HTW + 2;                    // raw row pitch in pixels = box width of the raw load
 
 struct HaloParams {
   int tiles_x, tiles_y, tiles_b, tiles_n, total_tiles;
   int nslab, Cin;
-  int pitch;           // raw row pitch in pixels (box width of the raw load)
-  int use_base_off;    // put (start address >> 7) & 7 into the descriptor's base-offset field
   int raw_bytes, raw_tx, n_raw, n_stage;
-  int b_resident;      // all 9 * nslab weight tiles live in shared memory for the whole kernel
   EpiParams e;
 };
 
@@ -47,7 +45,7 @@ __device__ __forceinline__ uint64_t umma_desc_sw128_ex(uint32_t saddr, uint32_t 
   return d;
 }
 
-template <int BN>
+template <int BN, bool BRES>
 __global__ void __launch_bounds__(HALO_THREADS, 1)
 conv_halo_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ TcOutMaps om, const __grid_constant__ HaloParams p) {
@@ -55,7 +53,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
   constexpr int TMEM_COLS = (2 * BN <= 32) ? 32 : 2 * BN;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const int n_btiles = p.b_resident ? 9 * p.nslab : p.n_stage;
+  const int n_btiles = BRES ? 9 * p.nslab : p.n_stage;
   const uint32_t b_base = smem_base;
   const uint32_t raw_base = (b_base + n_btiles * B_TILE_BYTES + 1023u) & ~1023u;
   const uint32_t stg_base = raw_base + p.n_raw * p.raw_bytes;
@@ -104,7 +102,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
 
   if (warp == 0) {
     // ================= TMA producer =================
-    if (p.b_resident && my_tiles > 0) {
+    if (BRES && my_tiles > 0) {
       if (lane == 0) {
         mbar_expect_tx(bres_bar, 9 * p.nslab * B_TILE_BYTES);
         for (int c = 0; c < p.nslab; ++c)
@@ -119,7 +117,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
     // Raw tiles run ahead of the B loads.  With streamed B the look-ahead is n_raw - 2 items, so the slot
     // a raw load waits for was released two items ago and the wait never delays this item's B loads;
     // with resident B the producer has nothing else to do and simply keeps the ring full.
-    const int look = p.b_resident ? items : (p.n_raw >= 2 ? p.n_raw - 2 : 0);
+    const int look = BRES ? items : (p.n_raw >= 2 ? p.n_raw - 2 : 0);
     for (int item = 0; item < items; ++item) {
       while (ri < items && ri <= item + look) {
         mbar_wait(rempty_bar(rs), rphase ^ 1);
@@ -134,7 +132,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
         ++ri;
         if (++rs == p.n_raw) { rs = 0; rphase ^= 1; }
       }
-      if (!p.b_resident) {
+      if (!BRES) {
         int k = item / p.nslab, c = item - k * p.nslab;
         int nt, x0, y0, b0;
         decode((int)blockIdx.x + k * (int)gridDim.x, nt, x0, y0, b0);
@@ -150,50 +148,53 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
       }
     }
   } else if (warp == 1) {
-    // ================= MMA issuer =================
-    constexpr uint32_t idesc = umma_idesc<BN>();
-    const uint32_t sbo = (uint32_t)p.pitch * 128u;
-    int stage = 0; uint32_t phase = 0;
-    int rs = 0; uint32_t rphase = 0;
-    if (p.b_resident && my_tiles > 0) mbar_wait(bres_bar, 0);
-    for (int it = 0; it < my_tiles; ++it) {
-      const int as = it & 1;
-      const uint32_t aphase = (it >> 1) & 1;
-      mbar_wait(tempty_bar(as), aphase ^ 1);
-      tc_fence_after();
-      const uint32_t tmem_d = tmem_base + as * BN;
-      for (int c = 0; c < p.nslab; ++c) {
-        mbar_wait(rfull_bar(rs), rphase);
+    // ================= MMA issuer (one thread runs the whole loop; taps fully unrolled) =================
+    if (lane == 0 && my_tiles > 0) {
+      constexpr uint32_t idesc = umma_idesc<BN>();
+      // descriptor bits that do not change: SBO = PITCH rows of 128 bytes (A), 1024 bytes (B)
+      const uint64_t a_hi = umma_desc_sw128_ex(0, PITCH * 128u, 0);
+      const uint64_t b_hi = umma_desc_sw128(0);
+      int stage = 0; uint32_t phase = 0;
+      int rs = 0; uint32_t rphase = 0;
+      if (BRES) mbar_wait(bres_bar, 0);
+      for (int it = 0; it < my_tiles; ++it) {
+        const int as = it & 1;
+        const uint32_t aphase = (it >> 1) & 1;
+        mbar_wait(tempty_bar(as), aphase ^ 1);
         tc_fence_after();
-        const uint32_t rbase = raw_base + rs * p.raw_bytes;
-        for (int t = 0; t < 9; ++t) {
-          uint32_t sb;
-          if (p.b_resident) sb = b_base + (c * 9 + t) * B_TILE_BYTES;
-          else {
-            mbar_wait(full_bar(stage), phase);
-            tc_fence_after();
-            sb = b_base + stage * B_TILE_BYTES;
-          }
-          if (lane == 0) {
-            const int ky = t / 3, kx = t - 3 * ky;
-            const uint32_t sa = rbase + (uint32_t)(ky * p.pitch + kx) * 128u;
-            const uint64_t adesc = umma_desc_sw128_ex(sa, sbo, p.use_base_off ? (sa >> 7) : 0u);
-            const uint64_t bdesc = umma_desc_sw128(sb);
+        const uint32_t tmem_d = tmem_base + as * BN;
+        for (int c = 0; c < p.nslab; ++c) {
+          mbar_wait(rfull_bar(rs), rphase);
+          tc_fence_after();
+          const uint64_t a0 = a_hi | (uint64_t)((raw_base + rs * p.raw_bytes) >> 4);
+          const uint64_t bres0 = b_hi | (uint64_t)((b_base + c * 9 * B_TILE_BYTES) >> 4);
 #pragma unroll
-            for (int k = 0; k < KSLAB / 16; ++k)
-              umma_bf16(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (c | t | k) != 0);
-            if (!p.b_resident) umma_commit(empty_bar(stage));
-            if (t == 8) {
-              umma_commit(rempty_bar(rs));
-              if (c == p.nslab - 1) umma_commit(tfull_bar(as));
+          for (int t = 0; t < 9; ++t) {
+            uint64_t bdesc;
+            if (BRES) bdesc = bres0 + (uint64_t)((t * B_TILE_BYTES) >> 4);
+            else {
+              mbar_wait(full_bar(stage), phase);
+              tc_fence_after();
+              bdesc = b_hi | (uint64_t)((b_base + stage * B_TILE_BYTES) >> 4);
+            }
+            // tap (ky, kx) = (t / 3, t % 3): the A tile starts (ky * PITCH + kx) 128-byte rows further on
+            const uint64_t adesc = a0 + (uint64_t)((((t / 3) * PITCH + (t % 3)) * 128) >> 4);
+            if (t == 0) umma_bf16(tmem_d, adesc, bdesc, idesc, c != 0);
+            else umma_bf16(tmem_d, adesc, bdesc, idesc, 1u);
+#pragma unroll
+            for (int k = 1; k < KSLAB / 16; ++k) umma_bf16(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, 1u);
+            if (!BRES) {
+              umma_commit(empty_bar(stage));
+              if (++stage == p.n_stage) { stage = 0; phase ^= 1; }
             }
           }
-          __syncwarp();
-          if (!p.b_resident) { if (++stage == p.n_stage) { stage = 0; phase ^= 1; } }
+          umma_commit(rempty_bar(rs));
+          if (c == p.nslab - 1) umma_commit(tfull_bar(as));
+          if (++rs == p.n_raw) { rs = 0; rphase ^= 1; }
         }
-        if (++rs == p.n_raw) { rs = 0; rphase ^= 1; }
       }
     }
+    __syncwarp();
   } else {
     // ================= epilogue (warps 2..5) =================
     const int q = warp & 3;
@@ -225,10 +226,10 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
   if (warp == 1) tmem_dealloc<TMEM_COLS>(tmem_base);
 }
 
-struct HaloPlan { int BN, pitch, use_base_off, n_raw, n_stage, raw_bytes, raw_tx, b_resident, smem; };
+struct HaloPlan { int BN, n_raw, n_stage, raw_bytes, raw_tx, b_resident, smem; };
 
 int g_halo_mode = -1;
-int halo_mode() {   // 0 off, 1 pitch 10, 2 pitch 10 + base offset, 3 pitch 16, 4 pitch 16 + base offset
+int halo_mode() {   // 0 off, 1 on (env TMAT_HALO)
   if (g_halo_mode < 0) {
     const char* e = getenv("TMAT_HALO");
     g_halo_mode = e ? atoi(e) : 1;
@@ -237,7 +238,7 @@ int halo_mode() {   // 0 off, 1 pitch 10, 2 pitch 10 + base offset, 3 pitch 16, 
 }
 
 bool plan_halo(const ConvOp& op, int mode, HaloPlan* pl) {
-  if (mode <= 0 || mode > 4) return false;
+  if (mode != 1) return false;
   if (op.ngroups != 1 || op.ntaps != 9 || op.a1 || op.a0_stride != 1 || op.a0_C % KSLAB != 0) return false;
   for (int t = 0; t < 9; ++t)
     if (op.dy[0][t] != t / 3 - 1 || op.dx[0][t] != t % 3 - 1) return false;
@@ -249,9 +250,7 @@ bool plan_halo(const ConvOp& op, int mode, HaloPlan* pl) {
   // tile efficiency: the fixed 8 x 16 tile must not waste much of the image
   double eff = (double)op.W * op.H / ((double)cdiv(op.W, HTW) * HTW * cdiv(op.H, HTH) * HTH);
   if (eff < 0.8) return false;
-  pl->pitch = (mode >= 3) ? 16 : 10;
-  pl->use_base_off = (mode == 2 || mode == 4);
-  pl->raw_tx = pl->pitch * (HTH + 2) * 128;
+  pl->raw_tx = PITCH * (HTH + 2) * 128;
   pl->raw_bytes = (pl->raw_tx + 1023) / 1024 * 1024;
   const int nslab = op.a0_C / KSLAB;
   const int btile = pl->BN * KSLAB * 2;
@@ -270,12 +269,12 @@ bool plan_halo(const ConvOp& op, int mode, HaloPlan* pl) {
   return false;
 }
 
-template <int BN>
+template <int BN, bool BRES>
 int launch_halo(tmat_ctx* ctx, const CUtensorMap& raw, const CUtensorMap& b, const TcOutMaps& om, const HaloParams& p,
                 int smem, cudaStream_t st) {
   static bool configured = false;
   if (!configured) {
-    CUDA_TRY(cudaFuncSetAttribute(conv_halo_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    CUDA_TRY(cudaFuncSetAttribute(conv_halo_kernel<BN, BRES>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     configured = true;
   }
   int grid = std::min(p.total_tiles, ctx->sm_count);
@@ -288,7 +287,7 @@ int launch_halo(tmat_ctx* ctx, const CUtensorMap& raw, const CUtensorMap& b, con
     rec.flops = 2.0 * p.e.B * p.e.H * p.e.W * (double)(p.tiles_n * BN) * (double)(9 * p.Cin);
     CUDA_TRY(cudaEventRecord(rec.a, st));
   }
-  conv_halo_kernel<BN><<<grid, HALO_THREADS, smem, st>>>(raw, b, om, p);
+  conv_halo_kernel<BN, BRES><<<grid, HALO_THREADS, smem, st>>>(raw, b, om, p);
   KERNEL_CHECK(ctx);
   if (ctx->profiling) {
     CUDA_TRY(cudaEventRecord(rec.b, st));
@@ -322,13 +321,11 @@ int conv_run_halo(tmat_ctx* ctx, const ConvOp& op, int mode, cudaStream_t st) {
   TMAT_REQUIRE(total < (1ll << 31), "conv_halo(%s): too many tiles", op.name);
   p.total_tiles = (int)total;
   p.nslab = op.a0_C / KSLAB; p.Cin = op.a0_C;
-  p.pitch = pl.pitch; p.use_base_off = pl.use_base_off;
   p.raw_bytes = pl.raw_bytes; p.raw_tx = pl.raw_tx; p.n_raw = pl.n_raw; p.n_stage = pl.n_stage;
-  p.b_resident = pl.b_resident;
   p.e = epi_of(op);
   CUtensorMap mRaw, mB;
   TcOutMaps om;
-  TMAT_TRY(tc_make_act_map(&mRaw, op.a0, op.B, op.H, op.W, op.a0_C, pl.pitch, HTH + 2, 1));
+  TMAT_TRY(tc_make_act_map(&mRaw, op.a0, op.B, op.H, op.W, op.a0_C, PITCH, HTH + 2, 1));
   TMAT_TRY(tc_make_weight_map(&mB, op.wmat, op.Npad, op.K, pl.BN));
   if (op.epi == EPI_STORE) {
     TMAT_TRY(tc_make_act_map(&om.m[0], op.out, op.B, op.H, op.W, op.Cout, HTW, HTH, 1));
@@ -338,10 +335,14 @@ int conv_run_halo(tmat_ctx* ctx, const ConvOp& op, int mode, cudaStream_t st) {
   } else {
     om.m[0] = om.m[1] = om.m[2] = om.m[3] = om.m2 = mRaw;
   }
-  switch (pl.BN) {
-    case 128: return launch_halo<128>(ctx, mRaw, mB, om, p, pl.smem, st);
-    case 64: return launch_halo<64>(ctx, mRaw, mB, om, p, pl.smem, st);
-    case 16: return launch_halo<16>(ctx, mRaw, mB, om, p, pl.smem, st);
+  const int key = pl.BN * 2 + (pl.b_resident ? 1 : 0);
+  switch (key) {
+    case 128 * 2 + 0: return launch_halo<128, false>(ctx, mRaw, mB, om, p, pl.smem, st);
+    case 128 * 2 + 1: return launch_halo<128, true>(ctx, mRaw, mB, om, p, pl.smem, st);
+    case 64 * 2 + 0: return launch_halo<64, false>(ctx, mRaw, mB, om, p, pl.smem, st);
+    case 64 * 2 + 1: return launch_halo<64, true>(ctx, mRaw, mB, om, p, pl.smem, st);
+    case 16 * 2 + 0: return launch_halo<16, false>(ctx, mRaw, mB, om, p, pl.smem, st);
+    case 16 * 2 + 1: return launch_halo<16, true>(ctx, mRaw, mB, om, p, pl.smem, st);
   }
   return TMAT_ERR_INVALID;
 }

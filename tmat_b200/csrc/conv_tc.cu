@@ -125,35 +125,34 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
       }
     }
   } else if (warp == 1) {
-    // ================= MMA issuer =================
-    constexpr uint32_t idesc = umma_idesc<BN>();
-    int stage = 0; uint32_t phase = 0;
-    int it = 0;
-    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
-      const int as = it & 1;
-      const uint32_t aphase = (it >> 1) & 1;
-      mbar_wait(tempty_bar(as), aphase ^ 1);
-      tc_fence_after();
-      const uint32_t tmem_d = tmem_base + as * BN;
-      for (int ks = 0; ks < p.nk; ++ks) {
-        mbar_wait(full_bar(stage), phase);
+    // ================= MMA issuer (one thread runs the whole loop) =================
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc<BN>();
+      int stage = 0; uint32_t phase = 0;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+        const int as = it & 1;
+        const uint32_t aphase = (it >> 1) & 1;
+        mbar_wait(tempty_bar(as), aphase ^ 1);
         tc_fence_after();
-        if (lane == 0) {
-          uint32_t sa = smem_base + stage * L::STAGE_BYTES;
-          uint64_t adesc = umma_desc_sw128(sa);
-          uint64_t bdesc = umma_desc_sw128(sa + A_STAGE_BYTES);
+        const uint32_t tmem_d = tmem_base + as * BN;
+        for (int ks = 0; ks < p.nk; ++ks) {
+          mbar_wait(full_bar(stage), phase);
+          tc_fence_after();
+          const uint32_t sa = smem_base + stage * L::STAGE_BYTES;
+          const uint64_t adesc = umma_desc_sw128(sa);
+          const uint64_t bdesc = umma_desc_sw128(sa + A_STAGE_BYTES);
+          // advance 16 bf16 = 32 bytes along K inside the swizzle atom: +2 in the (>>4) address field
+          umma_bf16(tmem_d, adesc, bdesc, idesc, ks != 0);
 #pragma unroll
-          for (int k = 0; k < KSLAB / 16; ++k) {
-            // advance 16 bf16 = 32 bytes along K inside the swizzle atom: +2 in the (>>4) address field
-            umma_bf16(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (ks | k) != 0);
-          }
+          for (int k = 1; k < KSLAB / 16; ++k) umma_bf16(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, 1u);
           umma_commit(empty_bar(stage));                     // stage reusable once these MMAs retire
           if (ks == p.nk - 1) umma_commit(tfull_bar(as));    // accumulator complete
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
-        __syncwarp();
-        if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
     }
+    __syncwarp();
   } else {
     // ================= epilogue (warps 2..5) =================
     const int q = warp & 3;                   // TMEM lane quarter this warp may access

@@ -92,23 +92,6 @@ __global__ void __launch_bounds__(256) stem_kernel(StemSrc src, int B, int ws, c
 }
 
 // ---- depthwise 3x3 ---------------------------------------------------------------------------
-__device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
-  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    float2 t = __bfloat1622float2(h[i]);
-    f[2 * i] = t.x; f[2 * i + 1] = t.y;
-  }
-}
-__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
-  uint4 o;
-  __nv_bfloat162 h;
-  h = __floats2bfloat162_rn(f[0], f[1]); o.x = *reinterpret_cast<uint32_t*>(&h);
-  h = __floats2bfloat162_rn(f[2], f[3]); o.y = *reinterpret_cast<uint32_t*>(&h);
-  h = __floats2bfloat162_rn(f[4], f[5]); o.z = *reinterpret_cast<uint32_t*>(&h);
-  h = __floats2bfloat162_rn(f[6], f[7]); o.w = *reinterpret_cast<uint32_t*>(&h);
-  return o;
-}
 __device__ __forceinline__ void unpack4(const uint2& v, bool relu, float (&f)[4]) {
   __nv_bfloat162 h0 = *reinterpret_cast<const __nv_bfloat162*>(&v.x);
   __nv_bfloat162 h1 = *reinterpret_cast<const __nv_bfloat162*>(&v.y);
