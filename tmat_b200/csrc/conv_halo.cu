@@ -212,11 +212,9 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
       decode((int)blockIdx.x + it * (int)gridDim.x, nt, x0, y0, b0);
       const int x = x0 + tx_in, y = y0 + ty_in, b = b0;
       const bool valid = (x < e.W) && (y < e.H);
-      mbar_wait(tfull_bar(as), aphase);
-      tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
       tc_epilogue_tile<BN>(e, om, taddr, 0, nt, x0, y0, b0, x, y, b, valid, stg_base, stg_row, sw, leader, sbuf,
-                           tempty_bar(as));
+                           tempty_bar(as), tfull_bar(as), aphase);
     }
     if (leader) tma_store_wait_all();
   }

@@ -174,11 +174,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
       decode(tile, g, nt, x0, y0, b0);
       const int x = x0 + tx_in, y = y0 + ty_in, b = b0 + tb_in;
       const bool valid = (x < e.W) && (y < e.H) && (b < e.B);
-      mbar_wait(tfull_bar(as), aphase);
-      tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
       tc_epilogue_tile<BN>(e, om, taddr, g, nt, x0, y0, b0, x, y, b, valid, stg_base, stg_row, sw, leader, sbuf,
-                           tempty_bar(as));
+                           tempty_bar(as), tfull_bar(as), aphase);
     }
     if (leader) tma_store_wait_all();            // smem must outlive the last store's read
   }

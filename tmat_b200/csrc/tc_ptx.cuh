@@ -163,12 +163,13 @@ constexpr int N_STG = 2;   // staging tiles of STG_BYTES each at stg_base
 // Epilogue of one output tile, executed by the 128 epilogue threads (thread = GEMM row = TMEM lane):
 // accumulator columns [0, BN) at taddr -> +shift (+addend) (ReLU) -> bf16 -> swizzled staging tile -> one
 // TMA tensor store per 64 channels (the head, BN = 16, stores its 4 floats per pixel directly).  `tempty`
-// is arrived on as soon as the accumulator has been read.
+// is arrived on as soon as the accumulator has been read; the wait for the accumulator (`tfull`, `tphase`)
+// happens inside, after the first addend loads have been issued.
 template <int BN>
 __device__ __forceinline__ void tc_epilogue_tile(const EpiParams& e, const TcOutMaps& om, uint32_t taddr, int g, int nt,
                                                  int x0, int y0, int b0, int x, int y, int b, bool valid,
                                                  uint32_t stg_base, uint32_t stg_row, uint32_t sw, bool leader,
-                                                 int& sbuf, uint32_t tempty) {
+                                                 int& sbuf, uint32_t tempty, uint32_t tfull, uint32_t tphase) {
       if constexpr (BN >= 64) {
         const bool dual = (e.out2 != nullptr);
         const bf16* addp = nullptr;
@@ -182,6 +183,18 @@ __device__ __forceinline__ void tc_epilogue_tile(const EpiParams& e, const TcOut
           const int col = nt * BN + c64;                        // column within the group
           int par = 0, ch0 = col;
           if (e.mode == EPI_PAR) { par = g * e.ppg + col / e.Cout; ch0 = col % e.Cout; }
+          // the addend (8 x 16 bytes per thread) is fetched before anything that waits: its L2 latency hides
+          // behind the accumulator wait / the staging hand-over
+          uint4 av[8];
+          if (addp != nullptr) {
+            const uint4* ap = reinterpret_cast<const uint4*>(addp + ch0);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) av[j] = __ldg(ap + j);
+          }
+          if (c64 == 0) {
+            mbar_wait(tfull, tphase);
+            tc_fence_after();
+          }
           // the staging buffer(s) about to be written must have been read out by their last store
           if (leader) { if (dual) tma_store_wait_read<0>(); else tma_store_wait_read<1>(); }
           epi_bar_sync();
@@ -200,10 +213,9 @@ __device__ __forceinline__ void tc_epilogue_tile(const EpiParams& e, const TcOut
               v[i + 2] = __uint_as_float(rr[i + 2]) + s.z; v[i + 3] = __uint_as_float(rr[i + 3]) + s.w;
             }
             if (addp != nullptr) {
-              const uint4* ap = reinterpret_cast<const uint4*>(addp + ch0 + half * 32);
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
-                uint4 u = __ldg(ap + j);
+                const uint4 u = av[half * 4 + j];
                 const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
@@ -246,6 +258,8 @@ __device__ __forceinline__ void tc_epilogue_tile(const EpiParams& e, const TcOut
         }
       } else {
         // head: 4 output-pixel parities in columns 0..3
+        mbar_wait(tfull, tphase);
+        tc_fence_after();
         uint32_t rr[16];
         tmem_ld16(taddr, rr);
         tmem_ld_wait();

@@ -525,10 +525,11 @@ extern "C" int tmat_unet_free(tmat_unet* net) {
 static int chunk_size(const tmat_unet* net) {
   const char* e = getenv("TMAT_CHUNK");
   if (e && atoi(e) > 0) return atoi(e);
-  // ~45 MB of bf16 activations per 320x320 patch; 64 patches keep every GEMM launch >= 1 wave
+  // ~40 MB of bf16 activations per 320x320 patch; 256 patches per chunk (10 GB) keep the persistent GEMM
+  // kernels at >= 20 tiles per SM even at the 20x20 bottleneck (measured: 64 -> 65.8, 128 -> 61.9, 256 -> 60.4 ms)
   int64_t px = (int64_t)net->desc.patch * net->desc.patch;
-  int c = (int)(64 * 102400 / px);
-  return c < 8 ? 8 : (c > 512 ? 512 : c);
+  int c = (int)(256 * 102400 / px);
+  return c < 8 ? 8 : (c > 2048 ? 2048 : c);
 }
 
 extern "C" int tmat_unet_forward_dev(tmat_ctx* ctx, tmat_unet* net, const float* patches_dev, int n,

@@ -10,6 +10,29 @@
 
 typedef __nv_bfloat16 bf16;
 
+#ifdef __CUDACC__
+// packed fp32 pairs (Blackwell FFMA2 / FMUL2): two channels per instruction
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+  f32x2 d;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "f"(lo), "f"(hi));
+  return d;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 ffma2(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ f32x2 fmul2(f32x2 a, f32x2 b) {
+  f32x2 d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+#endif
+
 enum EpiMode {
   EPI_STORE = 0,    // out[b,y,x,:] (same resolution), optional addend and ReLU'd second copy
   EPI_PAR = 1,      // parity store: GEMM column block q = (py,px) -> out[b,2y+py,2x+px,:]; this is a

@@ -40,12 +40,23 @@ __global__ void __launch_bounds__(256) stem_kernel(StemSrc src, int B, int ws, c
     } else {
       pp = src.patches + (int64_t)b * ws * ws;
     }
+    // the D4 tile map is affine in (i, j): three probes give its coefficients for the whole block
+    int r00 = 0, c00 = 0, dri = 0, dci = 0, drj = 0, dcj = 0;
+    if (src.use_geom) {
+      const StpGeom& G = src.geom;
+      int r10, c10, r01, c01;
+      d4_rot_to_orig(g, ti * G.step, tj * G.step, G.PM, G.PN, &r00, &c00);
+      d4_rot_to_orig(g, ti * G.step + 1, tj * G.step, G.PM, G.PN, &r10, &c10);
+      d4_rot_to_orig(g, ti * G.step, tj * G.step + 1, G.PM, G.PN, &r01, &c01);
+      dri = r10 - r00; dci = c10 - c00; drj = r01 - r00; dcj = c01 - c00;
+    }
     for (int idx = threadIdx.x; idx < IR * IC; idx += blockDim.x) {
       int r = idx / IC, c = idx - r * IC;
       int i = 2 * y0 + r, j = 2 * x0 + c;
       float v = 0.f;
       if (i < ws && j < ws)
-        v = src.use_geom ? stp_tile_pixel(src.img, src.geom, g, ti, tj, i, j, minval) : __ldg(pp + (int64_t)i * ws + j);
+        v = src.use_geom ? stp_padded_value(src.img, src.geom, r00 + i * dri + j * drj, c00 + i * dci + j * dcj, minval)
+                         : __ldg(pp + (int64_t)i * ws + j);
       tile[r][c] = v;
     }
   }
@@ -53,39 +64,44 @@ __global__ void __launch_bounds__(256) stem_kernel(StemSrc src, int B, int ws, c
   const int groups = C0 >> 3;                  // 8 when C0 == 64
   const int px_per_pass = blockDim.x / groups;
   const int cg = threadIdx.x % groups;
-  float wr[9][8], sh[8];
+  f32x2 wr[9][4], sh[4];
 #pragma unroll
   for (int t = 0; t < 9; ++t) {
     const float4* wp = reinterpret_cast<const float4*>(w + t * C0 + cg * 8);
     float4 w0 = __ldg(wp), w1 = __ldg(wp + 1);
-    wr[t][0] = w0.x; wr[t][1] = w0.y; wr[t][2] = w0.z; wr[t][3] = w0.w;
-    wr[t][4] = w1.x; wr[t][5] = w1.y; wr[t][6] = w1.z; wr[t][7] = w1.w;
+    wr[t][0] = pack2(w0.x, w0.y); wr[t][1] = pack2(w0.z, w0.w);
+    wr[t][2] = pack2(w1.x, w1.y); wr[t][3] = pack2(w1.z, w1.w);
   }
 #pragma unroll
-  for (int c = 0; c < 8; ++c) sh[c] = __ldg(shift + cg * 8 + c);
+  for (int c = 0; c < 4; ++c) sh[c] = pack2(__ldg(shift + cg * 8 + 2 * c), __ldg(shift + cg * 8 + 2 * c + 1));
   for (int xl = threadIdx.x / groups; xl < STEM_COLS; xl += px_per_pass) {
     const int x = x0 + xl;
     if (x >= S) break;
+#pragma unroll
     for (int r = 0; r < STEM_ROWS; ++r) {
       const int y = y0 + r;
       if (y >= S) break;
-      float acc[8];
+      f32x2 acc[4];
 #pragma unroll
-      for (int c = 0; c < 8; ++c) acc[c] = sh[c];
+      for (int c = 0; c < 4; ++c) acc[c] = sh[c];
 #pragma unroll
       for (int ky = 0; ky < 3; ++ky)
 #pragma unroll
         for (int kx = 0; kx < 3; ++kx) {
-          float v = tile[2 * r + ky][2 * xl + kx];
+          const float v = tile[2 * r + ky][2 * xl + kx];
+          const f32x2 vv = pack2(v, v);
 #pragma unroll
-          for (int c = 0; c < 8; ++c) acc[c] = fmaf(v, wr[ky * 3 + kx][c], acc[c]);
+          for (int c = 0; c < 4; ++c) acc[c] = ffma2(vv, wr[ky * 3 + kx][c], acc[c]);
         }
       uint4 o;
-      __nv_bfloat162 h;
-      h = __floats2bfloat162_rn(fmaxf(acc[0], 0.f), fmaxf(acc[1], 0.f)); o.x = *reinterpret_cast<uint32_t*>(&h);
-      h = __floats2bfloat162_rn(fmaxf(acc[2], 0.f), fmaxf(acc[3], 0.f)); o.y = *reinterpret_cast<uint32_t*>(&h);
-      h = __floats2bfloat162_rn(fmaxf(acc[4], 0.f), fmaxf(acc[5], 0.f)); o.z = *reinterpret_cast<uint32_t*>(&h);
-      h = __floats2bfloat162_rn(fmaxf(acc[6], 0.f), fmaxf(acc[7], 0.f)); o.w = *reinterpret_cast<uint32_t*>(&h);
+      uint32_t* ow = reinterpret_cast<uint32_t*>(&o);
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        float lo, hi;
+        unpack2(acc[c], lo, hi);
+        __nv_bfloat162 h = __floats2bfloat162_rn(fmaxf(lo, 0.f), fmaxf(hi, 0.f));
+        ow[c] = *reinterpret_cast<uint32_t*>(&h);
+      }
       *reinterpret_cast<uint4*>(out + (((int64_t)b * S + y) * S + x) * C0 + cg * 8) = o;
     }
   }
