@@ -252,12 +252,13 @@ def main():
             "config": {"workload": f"C4 per-image unit: one {size}x{size} float32 projection per rank per step -> "
                                    f"{patches} patches of 320x320 (ws 320, subdiv 2, 8x D4) through the random-init "
                                    "binary_segmentation UNet (64/128/256/512) + spline blend",
-                       "l2": "working set per step (554 MB of patch probabilities + ~3 GB of activations per chunk) "
-                             "exceeds the 126 MB L2; no explicit flush",
+                       "l2": "working set per step (554 MB of patch probabilities + ~10 GB of activations per "
+                             "256-patch chunk) exceeds the 126 MB L2; no explicit flush",
                        "parallelism": f"image-sharded x{world}"},
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": pk["bf16_sustained"], "unit": "TFLOP/s",
                          "frac": achieved / pk["bf16_sustained"], "traffic": None,
-                         "kernel": "conv_tc_kernel (tcgen05 implicit-GEMM convolution, all UNet GEMM layers)",
+                         "kernel": "the tcgen05 GEMM kernels of the UNet: conv_tc_kernel (implicit-GEMM convolution), "
+                                   "conv_dwpw_kernel (fused SeparableConv2D), conv_halo_kernel (3x3, haloed tile)",
                          "algorithmic_flops_per_step": algo_flops_step, "executed_flops_per_step": tc_flops / args.steps,
                          "kernel_ms_per_step": tc_ms_step, "launches_per_step": tc_launches / args.steps,
                          "kernel_share_of_step": tc_ms_step / ms_step, "peak_source": pk["source"] + " (sustained bf16)"},

@@ -48,29 +48,30 @@ __device__ __forceinline__ uint32_t f2_to_bf2(f32x2 v) {
   asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
   return pack_bf16x2(lo, hi);
 }
-// bf16x2 (channel c in the low half, c+1 in the high half) -> fp32 pair; `floor2` is bf16x2 (0, 0) for a
-// fused ReLU on the input and (-inf, -inf) otherwise, so the max is branch-free
-__device__ __forceinline__ f32x2 bf2_to_f2(uint32_t x, uint32_t floor2) {
-  __nv_bfloat162 h = __hmax2(*reinterpret_cast<__nv_bfloat162*>(&x), *reinterpret_cast<__nv_bfloat162*>(&floor2));
-  x = *reinterpret_cast<uint32_t*>(&h);
+// bf16x2 (channel c in the low half, c+1 in the high half) -> fp32 pair, with the block's input ReLU fused
+template <bool RELU>
+__device__ __forceinline__ f32x2 bf2_to_f2(uint32_t x) {
+  if (RELU) {
+    __nv_bfloat162 h = __hmax2(*reinterpret_cast<__nv_bfloat162*>(&x), __floats2bfloat162_rn(0.f, 0.f));
+    x = *reinterpret_cast<uint32_t*>(&h);
+  }
   return pack2(__uint_as_float(x << 16), __uint_as_float(x & 0xffff0000u));
 }
 
 // One tile column of the depthwise 3x3 for a thread's 4 channels, RH = TH_C + 2 raw rows, fully unrolled:
 // raw row yy is tap row ky of output row yy - ky; the three live accumulators rotate by compile-time index.
-template <int TH_C>
+template <int TH_C, bool RELU>
 __device__ __forceinline__ void dw_column(uint32_t rbase_sub, uint32_t abase_sub, uint32_t rp0, uint32_t ar0,
-                                          uint32_t RW, uint32_t TW, uint32_t jch, uint32_t floor2,
-                                          const f32x2 (&wr)[9][2]) {
+                                          uint32_t RW, uint32_t TW, uint32_t jch, const f32x2 (&wr)[9][2]) {
   f32x2 acc[3][2];
   auto raw_addr = [&](uint32_t rp) { return rbase_sub + (rp << 7) + ((jch ^ (rp & 7u)) << 4); };
 #pragma unroll
   for (int yy = 0; yy < TH_C + 2; ++yy) {
     const uint32_t rp = rp0 + (uint32_t)yy * RW;
     const uint2 cl = ld_shared_v2(raw_addr(rp)), cc = ld_shared_v2(raw_addr(rp + 1)), cr = ld_shared_v2(raw_addr(rp + 2));
-    const f32x2 f[3][2] = {{bf2_to_f2(cl.x, floor2), bf2_to_f2(cl.y, floor2)},
-                           {bf2_to_f2(cc.x, floor2), bf2_to_f2(cc.y, floor2)},
-                           {bf2_to_f2(cr.x, floor2), bf2_to_f2(cr.y, floor2)}};
+    const f32x2 f[3][2] = {{bf2_to_f2<RELU>(cl.x), bf2_to_f2<RELU>(cl.y)},
+                           {bf2_to_f2<RELU>(cc.x), bf2_to_f2<RELU>(cc.y)},
+                           {bf2_to_f2<RELU>(cr.x), bf2_to_f2<RELU>(cr.y)}};
 #pragma unroll
     for (int ky = 0; ky < 3; ++ky) {
       const int o = yy - ky;                     // output row this raw row feeds through tap row ky
@@ -265,7 +266,7 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
     const int cslot = t >> 4;               // column slot 0..15
     const int ncols = TW * TN;
     const int RW = TW + 2, RH = TH + 2;
-    const uint32_t floor2 = p.relu_in ? 0u : 0xff80ff80u;   // bf16x2 (0, 0) or (-inf, -inf)
+    const bool relu = p.relu_in != 0;
     int stage = 0, rs = 0; uint32_t phase = 0, rphase = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
       for (int ks = 0; ks < p.nk; ++ks) {
@@ -283,11 +284,19 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
           const int n = ci >> p.tw_log, x = ci & (TW - 1);
           const uint32_t rp0 = (uint32_t)((n * RH) * RW + x);   // raw pixel (n, yy = 0, xx = x)
           const uint32_t ar0 = (uint32_t)((n * TH) * TW + x);   // A row of output (n, y = 0, x)
-          if (TH == 8) dw_column<8>(rbase + sub, abase + sub, rp0, ar0, RW, TW, jch, floor2, wr);
-          else if (TH == 4) dw_column<4>(rbase + sub, abase + sub, rp0, ar0, RW, TW, jch, floor2, wr);
-          else if (TH == 16) dw_column<16>(rbase + sub, abase + sub, rp0, ar0, RW, TW, jch, floor2, wr);
-          else if (TH == 2) dw_column<2>(rbase + sub, abase + sub, rp0, ar0, RW, TW, jch, floor2, wr);
-          else dw_column<1>(rbase + sub, abase + sub, rp0, ar0, RW, TW, jch, floor2, wr);
+          if (!relu) {
+            if (TH == 8) dw_column<8, false>(rbase + sub, abase + sub, rp0, ar0, RW, TW, jch, wr);
+            else if (TH == 4) dw_column<4, false>(rbase + sub, abase + sub, rp0, ar0, RW, TW, jch, wr);
+            else if (TH == 16) dw_column<16, false>(rbase + sub, abase + sub, rp0, ar0, RW, TW, jch, wr);
+            else if (TH == 2) dw_column<2, false>(rbase + sub, abase + sub, rp0, ar0, RW, TW, jch, wr);
+            else dw_column<1, false>(rbase + sub, abase + sub, rp0, ar0, RW, TW, jch, wr);
+          } else {
+            if (TH == 8) dw_column<8, true>(rbase + sub, abase + sub, rp0, ar0, RW, TW, jch, wr);
+            else if (TH == 4) dw_column<4, true>(rbase + sub, abase + sub, rp0, ar0, RW, TW, jch, wr);
+            else if (TH == 16) dw_column<16, true>(rbase + sub, abase + sub, rp0, ar0, RW, TW, jch, wr);
+            else if (TH == 2) dw_column<2, true>(rbase + sub, abase + sub, rp0, ar0, RW, TW, jch, wr);
+            else dw_column<1, true>(rbase + sub, abase + sub, rp0, ar0, RW, TW, jch, wr);
+          }
         }
         fence_proxy_async();
         __syncwarp();
