@@ -129,6 +129,18 @@ int tmat_stp_predict_dev(tmat_ctx* ctx, tmat_unet* net, const float* img_dev, in
                          int subdiv, double* out_dev, void* stream);
 int tmat_stp_predict_host(tmat_ctx* ctx, tmat_unet* net, const float* img_host, int H, int W,
                           int subdiv, double* out_host);
+/* Row-strip form of the fused path: output rows [row0, row1) only (out: (row1-row0) x W float64).  The UNet
+ * runs on the patches whose window touches those rows, so N GPUs that each take H/N rows of ONE large image
+ * (BASELINE config "large-well tiles", SURVEY 8(e) owner-computes row strips) need no cross-GPU reduction;
+ * the strips are bit-identical to the rows of tmat_stp_predict_*.  n_patches (optional): patches evaluated. */
+int tmat_stp_predict_rows_dev(tmat_ctx* ctx, tmat_unet* net, const float* img_dev, int H, int W, int subdiv,
+                              int row0, int row1, double* out_rows_dev, int* n_patches, void* stream);
+int tmat_stp_predict_rows_host(tmat_ctx* ctx, tmat_unet* net, const float* img_host, int H, int W, int subdiv,
+                               int row0, int row1, double* out_rows_host, int* n_patches);
+/* Host geometry of the row-strip form: ids (orientation * tiles_per_orientation + tile index in the rotated
+ * frame) of the patches whose window touches output rows [row0, row1).  list may be NULL to query the count. */
+int tmat_stp_rows_patches(int H, int W, int ws, int subdiv, int row0, int row1, int* list, int capacity,
+                          int* n_out);
 /* debug / test hook: copy a named intermediate activation of the last forward (float32 NHWC)
  * to the host; returns TMAT_ERR_INVALID when the tap does not exist. */
 int tmat_unet_debug_tap(tmat_ctx* ctx, tmat_unet* net, const char* name, float* out_host,
@@ -165,6 +177,27 @@ int tmat_gaussian_dev(tmat_ctx* ctx, const void* img_dev, int dtype, int H, int 
                       void* out_dev, void* stream);
 int tmat_gaussian_host(tmat_ctx* ctx, const void* img_host, int dtype, int H, int W, double sigma,
                        void* out_host);
+/* preprocessing.py:44-93 exec_threshold: the statistics of GaussianMixture(n_components=2).fit on the
+ * selected pixels (float32 vector x, n >= 2).  rand3: the three uniform [0,1) draws scikit-learn's k-means++
+ * seeding takes from the caller's RandomState (random_sample() for the first centre, uniform(size=2) for the
+ * candidate trials), made by the caller so its stream advances as in the reference.
+ * result10: [0] threshold = min(255, mu_fg + sd_coef * sd_fg), [1,2] weights, [3,4] means, [5,6] variances,
+ * [7] EM iterations (negative: not converged in 100), [8] k-means iterations, [9] mean log-likelihood. */
+int tmat_gmm2_threshold_dev(tmat_ctx* ctx, const float* x_dev, int64_t n, double sd_coef,
+                            const double* rand3_host, double* result10_host, void* stream);
+int tmat_gmm2_threshold_host(tmat_ctx* ctx, const float* x_host, int64_t n, double sd_coef,
+                             const double* rand3_host, double* result10_host);
+/* preprocessing.py:91 np.where(masked <= thr, 0, masked), float32 */
+int tmat_threshold_le_zero_f32_host(tmat_ctx* ctx, const float* img_host, int64_t n, double thr,
+                                    float* out_host);
+/* preprocessing.py:165-183 blur(img, blur_itr, k_size, gs): blur_itr x cv2.GaussianBlur((k,k), 0)
+ * (fixed kernels for k = 3, 5, 7, BORDER_REFLECT_101), then the reference's final rounding.
+ * dtype U8: exact fixed point (8-bit weights, (S + 32768) >> 16), out uint8, final_op ignored.
+ * dtype F32: final_op 0 = raw float32, 1 = np.round -> float32 (gs=False), 2 = np.round -> uint8 (gs=True). */
+int tmat_blur_dev(tmat_ctx* ctx, const void* img_dev, int dtype, int H, int W, int ksize, int iters,
+                  int final_op, void* out_dev, void* stream);
+int tmat_blur_host(tmat_ctx* ctx, const void* img_host, int dtype, int H, int W, int ksize, int iters,
+                   int final_op, void* out_host);
 /* well_mask_generation.py:236-277 auto_threshold_well: gaussian(sigma=1) -> rescale to uint8
  * -> corner medians -> optional invert -> Otsu -> '>=' -> binary_erosion(disk(5)).
  * mask: uint8 0/1.  info (optional, 4 ints): [0]=inverted [1]=otsu threshold [2]=u8 min [3]=u8 max */

@@ -54,3 +54,24 @@ def test_stp_partition_of_unity_interior():
     out = predict_img_with_smooth_windowing(
         img, 32, 2, lambda b, verbose=0: np.ones(b.shape + (1,), np.float32))
     assert np.abs(out - 1).max() < 1e-12
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_row_strips_are_bit_identical_to_the_full_prediction(world):
+    """Owner-computes row strips (one large image sharded over GPUs): concatenated strips == full image."""
+    from oracle import unet as ou
+    from tmat_b200 import models
+    from tmat_b200.smooth_tiled_predictions import (predict_img_with_smooth_windowing, strip_rows,
+                                                    predict_rows_with_smooth_windowing, patches_for_rows)
+    fc, ws = (64, 64, 128, 128), 64
+    net = models.CudaUNet(ou.make_weights(fc, seed=2, randomize_affine=True, head_gain=4.0), ws, fc, impl="tc")
+    img = helpers.synth_projection(200, 150, 77)
+    full = predict_img_with_smooth_windowing(img, ws, 2, net.predict)
+    parts, n_eval = [], 0
+    for r in range(world):
+        row0, row1 = strip_rows(200, r, world)
+        parts.append(predict_rows_with_smooth_windowing(img, ws, 2, net.predict, row0, row1))
+        n_eval += len(patches_for_rows(200, 150, ws, 2, row0, row1))
+    assert np.array_equal(np.concatenate(parts), full)
+    n_total = len(patches_for_rows(200, 150, ws, 2, 0, 200))
+    assert n_total < n_eval < 2 * n_total

@@ -60,6 +60,9 @@ SIGNATURES = {
     "tmat_unet_forward_host": [_vp, _vp, _vp, _i, _vp, _i],
     "tmat_stp_predict_dev": [_vp, _vp, _vp, _i, _i, _i, _vp, _vp],
     "tmat_stp_predict_host": [_vp, _vp, _vp, _i, _i, _i, _vp],
+    "tmat_stp_predict_rows_dev": [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, C.POINTER(_i), _vp],
+    "tmat_stp_predict_rows_host": [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, C.POINTER(_i)],
+    "tmat_stp_rows_patches": [_i, _i, _i, _i, _i, _i, _vp, _i, C.POINTER(_i)],
     "tmat_unet_debug_tap": [_vp, _vp, C.c_char_p, _vp, _i64, C.POINTER(_i64)],
     "tmat_debug_conv_selftest": [_vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, C.c_uint64,
                                  C.POINTER(C.c_double), C.POINTER(C.c_double)],
@@ -67,6 +70,11 @@ SIGNATURES = {
     "tmat_debug_dwpw_selftest": [_vp, _i, _i, _i, _i, _i, _i, C.c_uint64, C.POINTER(C.c_double),
                                  C.POINTER(C.c_double)],
     "tmat_unet_flops_per_patch": [C.POINTER(UnetDesc), C.POINTER(C.c_double)],
+    "tmat_gmm2_threshold_dev": [_vp, _vp, _i64, C.c_double, _vp, _vp, _vp],
+    "tmat_gmm2_threshold_host": [_vp, _vp, _i64, C.c_double, _vp, _vp],
+    "tmat_threshold_le_zero_f32_host": [_vp, _vp, _i64, C.c_double, _vp],
+    "tmat_blur_dev": [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp],
+    "tmat_blur_host": [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp],
     "tmat_threshold_gt_f64_dev": [_vp, _vp, _i64, C.c_double, _vp, _vp],
     "tmat_apply_mask_f32_dev": [_vp, _vp, _vp, _i64, _vp, _vp],
     "tmat_gaussian_dev": [_vp, _vp, _i, _i, _i, C.c_double, _vp, _vp],

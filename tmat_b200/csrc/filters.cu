@@ -8,6 +8,7 @@
 #include "common.cuh"
 #include <math.h>
 #include <algorithm>
+#include <type_traits>
 
 int erode_disk(tmat_ctx* ctx, const uint8_t* in, int H, int W, int r, int border_value, uint8_t* out, cudaStream_t st);
 
@@ -362,6 +363,158 @@ extern "C" int tmat_auto_threshold_well_host(tmat_ctx* ctx, const void* img_host
   CUDA_TRY(cudaMemcpyAsync(d_in, img_host, n * es, cudaMemcpyHostToDevice, 0));
   TMAT_TRY(auto_threshold_impl(ctx, d_in, dtype, H, W, d_mask, info, 0));
   CUDA_TRY(cudaMemcpyAsync(mask_host, d_mask, n, cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaStreamSynchronize(0));
+  return TMAT_OK;
+}
+
+// ---- preprocessing.blur (preprocessing.py:165-183): blur_itr x cv2.GaussianBlur((k,k), 0), then round ----------
+// cv2.GaussianBlur with sigma = 0 and k <= 7 uses the fixed kernels [1,2,1]/4, [1,4,6,4,1]/16,
+// [0.03125, 0.109375, 0.21875, 0.28125, ...], BORDER_REFLECT_101.  Verified against cv2 4.13 in the build
+// container (oracle/blur.py):  uint8  -> exact fixed point, 8-bit weights w = round(256 g), separable,
+//                                        one rounding: (S + 32768) >> 16;
+//                              float32 -> separable, per pass  acc = g[c] x[c]; acc = fma(g[c+j], x[c-j] + x[c+j], acc)
+//                                        (bit-identical for k = 3, within 2 ulp of the image range for k = 5, 7).
+namespace {
+
+constexpr int BL_TW = 32, BL_TH = 16, BL_MAXR = 3;
+
+__device__ __forceinline__ int reflect101(int i, int n) {
+  if (n == 1) return 0;
+  while (i < 0 || i >= n) i = (i < 0) ? -i : 2 * (n - 1) - i;
+  return i;
+}
+
+// final: 0 keep, 1 rint (float32 only), 2 rint -> uint8 (float32 only; written to out_u8)
+template <typename T>
+__global__ void __launch_bounds__(BL_TW * BL_TH) blur_kernel(const T* __restrict__ in, int H, int W, int r,
+                                                              const float* __restrict__ gk, T* __restrict__ out,
+                                                              uint8_t* __restrict__ out_u8, int final_op) {
+  using A = typename std::conditional<std::is_same<T, uint8_t>::value, int, float>::type;
+  __shared__ A tile[BL_TH + 2 * BL_MAXR][BL_TW + 2 * BL_MAXR];
+  __shared__ A tmp[BL_TH + 2 * BL_MAXR][BL_TW];
+  __shared__ A wk[2 * BL_MAXR + 1];
+  const int x0 = blockIdx.x * BL_TW, y0 = blockIdx.y * BL_TH;
+  const int tid = threadIdx.y * BL_TW + threadIdx.x;
+  const int k = 2 * r + 1;
+  if (tid < k) {
+    if (std::is_same<T, uint8_t>::value) wk[tid] = (A)__float2int_rn(gk[tid] * 256.f);
+    else wk[tid] = (A)gk[tid];
+  }
+  const int th = BL_TH + 2 * r, tw = BL_TW + 2 * r;
+  for (int i = tid; i < th * tw; i += BL_TW * BL_TH) {
+    int ty = i / tw, tx = i - ty * tw;
+    int yy = reflect101(y0 + ty - r, H), xx = reflect101(x0 + tx - r, W);
+    tile[ty][tx] = (A)in[(int64_t)yy * W + xx];
+  }
+  __syncthreads();
+  // horizontal pass over th rows
+  for (int i = tid; i < th * BL_TW; i += BL_TW * BL_TH) {
+    int ty = i / BL_TW, tx = i - ty * BL_TW;
+    A acc;
+    if (std::is_same<T, uint8_t>::value) {
+      acc = wk[r] * tile[ty][tx + r];
+      for (int j = 1; j <= r; ++j) acc += wk[r + j] * (tile[ty][tx + r - j] + tile[ty][tx + r + j]);
+    } else {
+      acc = (A)__fmul_rn((float)wk[r], (float)tile[ty][tx + r]);
+      for (int j = 1; j <= r; ++j)
+        acc = (A)__fmaf_rn((float)wk[r + j], __fadd_rn((float)tile[ty][tx + r - j], (float)tile[ty][tx + r + j]), (float)acc);
+    }
+    tmp[ty][tx] = acc;
+  }
+  __syncthreads();
+  const int x = x0 + threadIdx.x, y = y0 + threadIdx.y;
+  if (x >= W || y >= H) return;
+  const int ty = threadIdx.y, tx = threadIdx.x;
+  if (std::is_same<T, uint8_t>::value) {
+    int acc = (int)wk[r] * (int)tmp[ty + r][tx];
+    for (int j = 1; j <= r; ++j) acc += (int)wk[r + j] * ((int)tmp[ty + r - j][tx] + (int)tmp[ty + r + j][tx]);
+    out[(int64_t)y * W + x] = (T)((acc + 32768) >> 16);
+  } else {
+    float acc = __fmul_rn((float)wk[r], (float)tmp[ty + r][tx]);
+    for (int j = 1; j <= r; ++j)
+      acc = __fmaf_rn((float)wk[r + j], __fadd_rn((float)tmp[ty + r - j][tx], (float)tmp[ty + r + j][tx]), acc);
+    if (final_op >= 1) acc = rintf(acc);          // np.round: half to even
+    if (final_op == 2) out_u8[(int64_t)y * W + x] = (uint8_t)(int)acc;
+    else out[(int64_t)y * W + x] = (T)acc;
+  }
+}
+
+__global__ void round_f32_kernel(const float* in, int64_t n, float* out, uint8_t* out_u8) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float v = rintf(in[i]);
+  if (out_u8) out_u8[i] = (uint8_t)(int)v; else out[i] = v;
+}
+
+// cv2.getGaussianKernel(k, 0) for k = 3, 5, 7 (fixed small kernels)
+const float BLUR_K3[3] = {0.25f, 0.5f, 0.25f};
+const float BLUR_K5[5] = {0.0625f, 0.25f, 0.375f, 0.25f, 0.0625f};
+const float BLUR_K7[7] = {0.03125f, 0.109375f, 0.21875f, 0.28125f, 0.21875f, 0.109375f, 0.03125f};
+
+int blur_impl(tmat_ctx* ctx, const void* in, int dtype, int H, int W, int ksize, int iters, int final_op, void* out,
+              cudaStream_t st) {
+  TMAT_REQUIRE(dtype == TMAT_U8 || dtype == TMAT_F32, "tmat_blur: dtype must be uint8 or float32");
+  TMAT_REQUIRE(ksize == 3 || ksize == 5 || ksize == 7, "tmat_blur: k_size %d not supported (3, 5, 7)", ksize);
+  TMAT_REQUIRE(iters >= 0 && final_op >= 0 && final_op <= 2, "tmat_blur: bad argument");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  const int64_t n = (int64_t)H * W;
+  const size_t es = dtype_size(dtype);
+  const float* hk = ksize == 3 ? BLUR_K3 : (ksize == 5 ? BLUR_K5 : BLUR_K7);
+  float* gk;
+  TMAT_TRY(arena_get(ctx, 8, &gk));
+  CUDA_TRY(cudaMemcpyAsync(gk, hk, ksize * sizeof(float), cudaMemcpyHostToDevice, st));
+  void *b0, *b1;
+  TMAT_TRY(arena_alloc(ctx, n * es, &b0));
+  TMAT_TRY(arena_alloc(ctx, n * es, &b1));
+  dim3 grid(cdiv(W, BL_TW), cdiv(H, BL_TH)), block(BL_TW, BL_TH);
+  const void* src = in;
+  for (int it = 0; it < iters; ++it) {
+    const bool last = (it == iters - 1);
+    void* dst;
+    uint8_t* dst_u8 = nullptr;
+    if (!last) dst = (src == b0) ? b1 : b0;
+    else if (dtype == TMAT_F32 && final_op == 2) { dst = (src == b0) ? b1 : b0; dst_u8 = (uint8_t*)out; }
+    else dst = out;
+    if (dtype == TMAT_U8)
+      blur_kernel<uint8_t><<<grid, block, 0, st>>>((const uint8_t*)src, H, W, ksize / 2, gk, (uint8_t*)dst, nullptr, 0);
+    else
+      blur_kernel<float><<<grid, block, 0, st>>>((const float*)src, H, W, ksize / 2, gk, (float*)dst, dst_u8,
+                                                 last ? final_op : 0);
+    KERNEL_CHECK(ctx);
+    src = dst;
+  }
+  if (iters == 0) {   // no blur: copy (+ round for float32)
+    if (dtype == TMAT_U8 || final_op == 0) CUDA_TRY(cudaMemcpyAsync(out, in, n * es, cudaMemcpyDeviceToDevice, st));
+    else {
+      round_f32_kernel<<<(unsigned)cdiv64(n, 256), 256, 0, st>>>((const float*)in, n, (float*)out,
+                                                                  final_op == 2 ? (uint8_t*)out : nullptr);
+      KERNEL_CHECK(ctx);
+    }
+  }
+  return TMAT_OK;
+}
+
+}  // namespace
+
+extern "C" int tmat_blur_dev(tmat_ctx* ctx, const void* img_dev, int dtype, int H, int W, int ksize, int iters,
+                             int final_op, void* out_dev, void* stream) {
+  TMAT_REQUIRE(ctx && img_dev && out_dev && H >= 1 && W >= 1, "tmat_blur: bad argument");
+  TMAT_TRY(arena_reset(ctx));
+  return blur_impl(ctx, img_dev, dtype, H, W, ksize, iters, final_op, out_dev, as_stream(stream));
+}
+
+extern "C" int tmat_blur_host(tmat_ctx* ctx, const void* img_host, int dtype, int H, int W, int ksize, int iters,
+                              int final_op, void* out_host) {
+  TMAT_REQUIRE(ctx && img_host && out_host && H >= 1 && W >= 1, "tmat_blur_host: bad argument");
+  TMAT_REQUIRE(dtype == TMAT_U8 || dtype == TMAT_F32, "tmat_blur_host: dtype must be uint8 or float32");
+  TMAT_TRY(arena_reset(ctx));
+  size_t n = (size_t)H * W, es = dtype_size(dtype), os = (dtype == TMAT_F32 && final_op == 2) ? 1 : es;
+  void *d_in, *d_out;
+  TMAT_TRY(arena_alloc(ctx, n * es, &d_in));
+  TMAT_TRY(arena_alloc(ctx, n * es, &d_out));
+  CUDA_TRY(cudaMemcpyAsync(d_in, img_host, n * es, cudaMemcpyHostToDevice, 0));
+  TMAT_TRY(blur_impl(ctx, d_in, dtype, H, W, ksize, iters, final_op, d_out, 0));
+  CUDA_TRY(cudaMemcpyAsync(out_host, d_out, n * os, cudaMemcpyDeviceToHost, 0));
   CUDA_TRY(cudaStreamSynchronize(0));
   return TMAT_OK;
 }

@@ -140,13 +140,14 @@ __global__ void __launch_bounds__(256) stp_gather_kernel(const float* __restrict
 // the 8 results are added left to right and divided by 8 (np.mean over the list, :133).
 __global__ void __launch_bounds__(256) stp_blend_kernel(const float* __restrict__ preds, StpGeom G,
                                                         const double* __restrict__ w1d,
+                                                        const int* __restrict__ slot_of_patch, int row0, int row1,
                                                         double* __restrict__ out) {
   int x = blockIdx.x * blockDim.x + threadIdx.x;
-  int y = blockIdx.y;
-  if (x >= G.W || y >= G.H) return;
+  int y = row0 + blockIdx.y;
+  if (x >= G.W || y >= row1) return;
   const int r = y + G.aug, c = x + G.aug;
   const int ws = G.ws, step = G.step;
-  const int64_t per_orient = (int64_t)G.tiles_per_orient() * ws * ws;
+  const int per_orient = G.tiles_per_orient();
   const double inv_div = (double)(G.subdiv * G.subdiv);
   double total = 0.0;
 #pragma unroll 1
@@ -161,21 +162,22 @@ __global__ void __launch_bounds__(256) stp_blend_kernel(const float* __restrict_
     tj0 = tj0 <= 0 ? 0 : (tj0 + step - 1) / step;
     int tj1 = min(rj / step, b - 1);
     double s = 0.0;
-    const float* pg = preds + g * per_orient;
     for (int ti = ti0; ti <= ti1; ++ti) {
       int i = ri - ti * step;
       double wi = w1d[i];
       for (int tj = tj0; tj <= tj1; ++tj) {
         int j = rj - tj * step;
         double w2 = __dmul_rn(wi, w1d[j]);
-        double p = (double)__ldg(pg + ((int64_t)(ti * b + tj) * ws + i) * ws + j);
+        int pid = g * per_orient + ti * b + tj;
+        if (slot_of_patch) pid = __ldg(slot_of_patch + pid);
+        double p = (double)__ldg(preds + ((int64_t)pid * ws + i) * ws + j);
         s = __dadd_rn(s, __dmul_rn(p, w2));
       }
     }
     s = __ddiv_rn(s, inv_div);
     total = (g == 0) ? s : __dadd_rn(total, s);
   }
-  out[(int64_t)y * G.W + x] = __ddiv_rn(total, 8.0);
+  out[(int64_t)(y - row0) * G.W + x] = __ddiv_rn(total, 8.0);
 }
 
 }  // namespace
@@ -208,8 +210,52 @@ int stp_upload_window(tmat_ctx* ctx, int ws, const double* window1d_host, double
 int stp_blend(tmat_ctx* ctx, const StpGeom& G, const float* preds_dev, const double* w1d_dev, double* out_dev,
               cudaStream_t st) {
   dim3 grid(cdiv(G.W, 256), G.H);
-  stp_blend_kernel<<<grid, 256, 0, st>>>(preds_dev, G, w1d_dev, out_dev);
+  stp_blend_kernel<<<grid, 256, 0, st>>>(preds_dev, G, w1d_dev, nullptr, 0, G.H, out_dev);
   KERNEL_CHECK(ctx);
+  return TMAT_OK;
+}
+
+int stp_blend_rows(tmat_ctx* ctx, const StpGeom& G, const float* preds_dev, const int* slot_of_patch_dev,
+                   const double* w1d_dev, int row0, int row1, double* out_rows_dev, cudaStream_t st) {
+  TMAT_REQUIRE(row0 >= 0 && row0 < row1 && row1 <= G.H, "stp: bad row range [%d, %d) for H=%d", row0, row1, G.H);
+  dim3 grid(cdiv(G.W, 256), row1 - row0);
+  stp_blend_kernel<<<grid, 256, 0, st>>>(preds_dev, G, w1d_dev, slot_of_patch_dev, row0, row1, out_rows_dev);
+  KERNEL_CHECK(ctx);
+  return TMAT_OK;
+}
+
+void stp_patches_for_rows(const StpGeom& G, int row0, int row1, std::vector<int>* list) {
+  list->clear();
+  const int lo = row0 + G.aug, hi = row1 + G.aug;     // padded rows [lo, hi) of the ORIGINAL frame
+  const int per = G.tiles_per_orient();
+  for (int g = 0; g < 8; ++g) {
+    const int a = G.tile_rows(g), b = G.tile_cols(g);
+    for (int ti = 0; ti < a; ++ti)
+      for (int tj = 0; tj < b; ++tj) {
+        // the window is an axis-aligned square in both frames: map two opposite corners
+        int r0, c0, r1, c1;
+        d4_rot_to_orig(g, ti * G.step, tj * G.step, G.PM, G.PN, &r0, &c0);
+        d4_rot_to_orig(g, ti * G.step + G.ws - 1, tj * G.step + G.ws - 1, G.PM, G.PN, &r1, &c1);
+        const int rmin = r0 < r1 ? r0 : r1, rmax = r0 < r1 ? r1 : r0;
+        if (rmax >= lo && rmin < hi) list->push_back(g * per + ti * b + tj);
+      }
+  }
+}
+
+// host geometry: which patches a row strip needs (for sharding one large image across GPUs by row strips)
+extern "C" int tmat_stp_rows_patches(int H, int W, int ws, int subdiv, int row0, int row1, int* list, int capacity,
+                                     int* n_out) {
+  TMAT_REQUIRE(n_out, "tmat_stp_rows_patches: NULL output");
+  StpGeom G;
+  TMAT_TRY(stp_make_geom(H, W, ws, subdiv, &G));
+  TMAT_REQUIRE(row0 >= 0 && row0 < row1 && row1 <= H, "tmat_stp_rows_patches: bad row range [%d, %d)", row0, row1);
+  std::vector<int> v;
+  stp_patches_for_rows(G, row0, row1, &v);
+  *n_out = (int)v.size();
+  if (list) {
+    TMAT_REQUIRE(capacity >= (int)v.size(), "tmat_stp_rows_patches: capacity %d < %d", capacity, (int)v.size());
+    memcpy(list, v.data(), v.size() * sizeof(int));
+  }
   return TMAT_OK;
 }
 

@@ -64,5 +64,12 @@ __device__ __forceinline__ float stp_tile_pixel(const float* __restrict__ img, c
 int stp_image_min(tmat_ctx* ctx, const float* img_dev, int64_t n, float* minmax_dev /*[2]*/, cudaStream_t st);
 int stp_blend(tmat_ctx* ctx, const StpGeom& G, const float* preds_dev, const double* w1d_dev, double* out_dev,
               cudaStream_t st);
+// Blend of output rows [row0, row1) only; preds_dev holds the patches of a row strip in list order and
+// slot_of_patch (device, one int per patch of the image, -1 = not computed) maps patch id -> slot.
+int stp_blend_rows(tmat_ctx* ctx, const StpGeom& G, const float* preds_dev, const int* slot_of_patch_dev,
+                   const double* w1d_dev, int row0, int row1, double* out_rows_dev, cudaStream_t st);
+// Patches (id = orientation * tiles_per_orient + tile index in the rotated frame) whose window touches
+// output rows [row0, row1), in id order.  Host geometry only.
+void stp_patches_for_rows(const StpGeom& G, int row0, int row1, std::vector<int>* list);
 int stp_upload_window(tmat_ctx* ctx, int ws, const double* window1d_host, double** w1d_dev, cudaStream_t st);
 void spline_window_host(int ws, double* out);

@@ -616,6 +616,73 @@ int stp_predict_impl(tmat_ctx* ctx, tmat_unet* net, const float* img_dev, int H,
   return stp_blend(ctx, G, probs, w1d, out_dev, st);
 }
 
+// Output rows [row0, row1) of predict_img_with_smooth_windowing only: the UNet runs on the patches whose window
+// touches those rows (owner-computes row strips: sharding ONE large image over GPUs with no reduction)
+int stp_predict_rows_impl(tmat_ctx* ctx, tmat_unet* net, const float* img_dev, int H, int W, int subdiv, int row0,
+                          int row1, double* out_rows_dev, int* n_patches, cudaStream_t st) {
+  StpGeom G;
+  const int ws = net->desc.patch;
+  TMAT_TRY(stp_make_geom(H, W, ws, subdiv, &G));
+  TMAT_REQUIRE(row0 >= 0 && row0 < row1 && row1 <= H, "tmat_stp_predict_rows: bad row range [%d, %d) for H=%d", row0,
+               row1, H);
+  std::vector<int> list;
+  stp_patches_for_rows(G, row0, row1, &list);
+  const int n_total = 8 * G.tiles_per_orient();
+  const int n_sel = (int)list.size();
+  if (n_patches) *n_patches = n_sel;
+  std::vector<int> slot(n_total, -1);
+  for (int i = 0; i < n_sel; ++i) slot[list[i]] = i;
+  const int CH = std::min(n_sel, chunk_size(net));
+  TMAT_TRY(arena_reserve(ctx, (size_t)n_sel * ws * ws * 4 + forward_scratch_bytes(net, CH) + (size_t)n_total * 8 + (4 << 20)));
+  float *minmax, *probs;
+  double* w1d;
+  int *d_list, *d_slot;
+  TMAT_TRY(arena_get(ctx, 2, &minmax));
+  TMAT_TRY(arena_get(ctx, (size_t)n_sel * ws * ws, &probs));
+  TMAT_TRY(arena_get(ctx, (size_t)n_sel, &d_list));
+  TMAT_TRY(arena_get(ctx, (size_t)n_total, &d_slot));
+  CUDA_TRY(cudaMemcpyAsync(d_list, list.data(), (size_t)n_sel * 4, cudaMemcpyHostToDevice, st));
+  CUDA_TRY(cudaMemcpyAsync(d_slot, slot.data(), (size_t)n_total * 4, cudaMemcpyHostToDevice, st));
+  CUDA_TRY(cudaStreamSynchronize(st));        // the host vectors die with this frame
+  TMAT_TRY(stp_upload_window(ctx, ws, nullptr, &w1d, st));
+  TMAT_TRY(stp_image_min(ctx, img_dev, (int64_t)H * W, minmax, st));
+  net->keep_taps = false;
+  for (int p0 = 0; p0 < n_sel; p0 += CH) {
+    int B = std::min(CH, n_sel - p0);
+    size_t mark = arena_mark(ctx);
+    StemSrc src;
+    memset(&src, 0, sizeof(src));
+    src.img = img_dev; src.minmax = minmax; src.geom = G; src.first_patch = p0; src.use_geom = 1;
+    src.patch_list = d_list;
+    TMAT_TRY(unet_forward(ctx, net, src, B, probs + (size_t)p0 * ws * ws, 0, st));
+    arena_release(ctx, mark);
+  }
+  return stp_blend_rows(ctx, G, probs, d_slot, w1d, row0, row1, out_rows_dev, st);
+}
+
+extern "C" int tmat_stp_predict_rows_dev(tmat_ctx* ctx, tmat_unet* net, const float* img_dev, int H, int W, int subdiv,
+                                         int row0, int row1, double* out_rows_dev, int* n_patches, void* stream) {
+  TMAT_REQUIRE(ctx && net && img_dev && out_rows_dev, "tmat_stp_predict_rows: NULL argument");
+  TMAT_TRY(arena_reset(ctx));
+  return stp_predict_rows_impl(ctx, net, img_dev, H, W, subdiv, row0, row1, out_rows_dev, n_patches, as_stream(stream));
+}
+
+extern "C" int tmat_stp_predict_rows_host(tmat_ctx* ctx, tmat_unet* net, const float* img_host, int H, int W,
+                                          int subdiv, int row0, int row1, double* out_rows_host, int* n_patches) {
+  TMAT_REQUIRE(ctx && net && img_host && out_rows_host, "tmat_stp_predict_rows_host: NULL argument");
+  TMAT_REQUIRE(H >= 1 && W >= 1 && row0 >= 0 && row0 < row1 && row1 <= H, "tmat_stp_predict_rows_host: bad shape / rows");
+  TMAT_TRY(arena_reset(ctx));
+  float* d_img;
+  double* d_out;
+  TMAT_TRY(arena_get(ctx, (size_t)H * W, &d_img));
+  TMAT_TRY(arena_get(ctx, (size_t)(row1 - row0) * W, &d_out));
+  CUDA_TRY(cudaMemcpyAsync(d_img, img_host, (size_t)H * W * 4, cudaMemcpyHostToDevice, 0));
+  TMAT_TRY(stp_predict_rows_impl(ctx, net, d_img, H, W, subdiv, row0, row1, d_out, n_patches, 0));
+  CUDA_TRY(cudaMemcpyAsync(out_rows_host, d_out, (size_t)(row1 - row0) * W * 8, cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaStreamSynchronize(0));
+  return TMAT_OK;
+}
+
 extern "C" int tmat_stp_predict_dev(tmat_ctx* ctx, tmat_unet* net, const float* img_dev, int H, int W, int subdiv,
                                     double* out_dev, void* stream) {
   TMAT_REQUIRE(ctx && net && img_dev && out_dev, "tmat_stp_predict: NULL argument");

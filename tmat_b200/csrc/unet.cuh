@@ -109,6 +109,7 @@ struct StemSrc {
   StpGeom geom;
   int first_patch;
   int use_geom;
+  const int* patch_list;  // optional (device): patch id = patch_list[first_patch + b] (row-strip prediction)
 };
 int stem_run(tmat_ctx* ctx, const StemSrc& src, int B, int ws, const float* w /*[9][C0] scale folded*/,
              const float* shift, int C0, bf16* out, cudaStream_t st);

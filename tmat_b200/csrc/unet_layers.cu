@@ -31,6 +31,7 @@ __global__ void __launch_bounds__(256) stem_kernel(StemSrc src, int B, int ws, c
     if (src.use_geom) {
       const StpGeom& G = src.geom;
       int p = src.first_patch + b;
+      if (src.patch_list) p = __ldg(src.patch_list + p);
       int per = G.tiles_per_orient();
       g = p / per;
       int t = p - g * per;
@@ -50,14 +51,24 @@ __global__ void __launch_bounds__(256) stem_kernel(StemSrc src, int B, int ws, c
       d4_rot_to_orig(g, ti * G.step, tj * G.step + 1, G.PM, G.PN, &r01, &c01);
       dri = r10 - r00; dci = c10 - c00; drj = r01 - r00; dcj = c01 - c00;
     }
-    for (int idx = threadIdx.x; idx < IR * IC; idx += blockDim.x) {
-      int r = idx / IC, c = idx - r * IC;
-      int i = 2 * y0 + r, j = 2 * x0 + c;
+    // all global loads of the fill are issued before the first shared-memory store (latency overlap)
+    constexpr int FILL = (IR * IC + 255) / 256;
+    float vals[FILL];
+#pragma unroll
+    for (int k = 0; k < FILL; ++k) {
+      const int idx = threadIdx.x + k * 256;
+      const int r = idx / IC, c = idx - r * IC;
+      const int i = 2 * y0 + r, j = 2 * x0 + c;
       float v = 0.f;
-      if (i < ws && j < ws)
+      if (idx < IR * IC && i < ws && j < ws)
         v = src.use_geom ? stp_padded_value(src.img, src.geom, r00 + i * dri + j * drj, c00 + i * dci + j * dcj, minval)
                          : __ldg(pp + (int64_t)i * ws + j);
-      tile[r][c] = v;
+      vals[k] = v;
+    }
+#pragma unroll
+    for (int k = 0; k < FILL; ++k) {
+      const int idx = threadIdx.x + k * 256;
+      if (idx < IR * IC) tile[idx / IC][idx % IC] = vals[k];
     }
   }
   __syncthreads();

@@ -30,3 +30,54 @@ def apply_mask(img, mask):
 def bin_thresh(img, img_max, threshold=0):
     """preprocessing.py:26-41."""
     return np.where(np.copy(img) > threshold, img_max, 0)
+
+
+def blur(img, blur_itr, k_size=3, gs=True):
+    """preprocessing.py:165-183 on the GPU: ``blur_itr`` x ``cv2.GaussianBlur((k, k), 0)`` then ``.round()``
+    (``.astype(uint8)`` when ``gs``).  uint8 input is bit-exact (fixed-point kernels); float32 input is
+    bit-exact for ``k_size=3`` and within 2 ulp of the image range for 5 and 7."""
+    a = np.ascontiguousarray(img)
+    if a.ndim != 2 or a.dtype not in (np.dtype(np.uint8), np.dtype(np.float32)):
+        raise TypeError("blur: a 2-D uint8 or float32 image is required on the GPU path")
+    if k_size not in (3, 5, 7):
+        raise ValueError("blur: k_size must be 3, 5 or 7 (cv2's fixed sigma=0 kernels)")
+    is_f = a.dtype == np.float32
+    final_op = (2 if gs else 1) if is_f else 0
+    out = np.empty(a.shape, np.uint8 if (gs or not is_f) else np.float32)
+    _ffi.check(_ffi.lib().tmat_blur_host(_ffi.default_context().handle, _ffi.ptr(a), _ffi.DTYPES[a.dtype], a.shape[0],
+                                         a.shape[1], int(k_size), int(blur_itr), final_op, _ffi.ptr(out)))
+    return out
+
+
+def gmm_foreground_threshold(pixels, sd_coef, rand_state, return_params=False):
+    """The scalar of preprocessing.py:75-87: 2-component GMM on ``pixels`` (1-D), threshold =
+    ``min(255, mean_fg + sd_coef * sd_fg)``.  The three uniform draws scikit-learn's k-means++ seeding would
+    take from ``rand_state`` are taken here in the same order; everything that touches the samples runs on
+    the GPU (csrc/gmm.cu)."""
+    x = np.ascontiguousarray(np.asarray(pixels).reshape(-1), dtype=np.float32)
+    rnd = np.empty(3, np.float64)
+    rnd[0] = rand_state.random_sample()          # random_state.choice(n_samples, p=uniform)
+    rnd[1:] = rand_state.uniform(size=2)         # the two local seeding trials
+    res = np.empty(10, np.float64)
+    _ffi.check(_ffi.lib().tmat_gmm2_threshold_host(_ffi.default_context().handle, _ffi.ptr(x), x.size, float(sd_coef),
+                                                   _ffi.ptr(rnd), _ffi.ptr(res)))
+    if return_params:
+        return res[0], {"weights": res[1:3].copy(), "means": res[3:5].copy(), "variances": res[5:7].copy(),
+                        "n_iter": int(res[7]), "kmeans_iter": int(res[8]), "lower_bound": res[9]}
+    return res[0]
+
+
+def exec_threshold(masked, mask_idx, sd_coef, rand_state):
+    """preprocessing.py:44-93.  ``masked``: 2-D image (the reference passes float32 in [0, 1]); ``mask_idx``:
+    index tuple of the pixels inside the mask, or None for all pixels.  Returns a copy with background pixels
+    (``<=`` threshold) set to 0."""
+    a = np.asarray(masked)
+    pixels = a[mask_idx] if mask_idx is not None else a.reshape(-1)
+    thr = gmm_foreground_threshold(pixels, sd_coef, rand_state)
+    if a.dtype != np.float32:
+        return np.where(np.copy(a) <= thr, 0, a)
+    src = np.ascontiguousarray(a)
+    out = np.empty_like(src)
+    _ffi.check(_ffi.lib().tmat_threshold_le_zero_f32_host(_ffi.default_context().handle, _ffi.ptr(src), src.size,
+                                                          float(thr), _ffi.ptr(out)))
+    return out

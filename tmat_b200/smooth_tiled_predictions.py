@@ -92,3 +92,68 @@ def predict_img_with_smooth_windowing(input_img, window_size, subdivisions, pred
     _ffi.check(L.tmat_stp_blend_host(ctx.handle, _ffi.ptr(preds), h, w, window_size, subdivisions,
                                      _ffi.ptr(w1d), _ffi.ptr(out)))
     return out
+
+
+# ---- one large image sharded over ranks by row strips (BASELINE "large-well tiles"; no reduction) ----------
+def strip_rows(h, rank, world):
+    """Output rows [row0, row1) owned by ``rank``: contiguous strips, sizes differ by at most one row."""
+    base, extra = divmod(h, world)
+    row0 = rank * base + min(rank, extra)
+    return row0, row0 + base + (1 if rank < extra else 0)
+
+
+def patches_for_rows(h, w, window_size, subdivisions, row0, row1):
+    """Ids of the (orientation, tile) patches whose window touches output rows [row0, row1) (host geometry)."""
+    n = _ffi.C.c_int()
+    _ffi.check(_ffi.lib().tmat_stp_rows_patches(h, w, window_size, subdivisions, row0, row1, None, 0, _ffi.C.byref(n)))
+    ids = np.empty(n.value, np.int32)
+    _ffi.check(_ffi.lib().tmat_stp_rows_patches(h, w, window_size, subdivisions, row0, row1, _ffi.ptr(ids), n.value,
+                                                _ffi.C.byref(n)))
+    return ids
+
+
+def predict_rows_with_smooth_windowing(input_img, window_size, subdivisions, pred_func, row0, row1):
+    """Rows [row0, row1) of ``predict_img_with_smooth_windowing`` (bit-identical to those rows of the full
+    result), evaluating only the patches that touch them.  ``pred_func`` must be ``CudaUNet.predict``."""
+    img = _ffi.as_c(np.asarray(input_img), np.float32)
+    if img.ndim != 2:
+        raise ValueError(f"input_img must be 2-D, got shape {img.shape}")
+    owner = getattr(pred_func, "__self__", None)
+    net = getattr(owner, "_tmat_handle", None)
+    if net is None:
+        raise TypeError("predict_rows_with_smooth_windowing needs the CUDA UNet's predict method")
+    if owner.patch != window_size:
+        raise ValueError(f"window_size {window_size} != UNet patch size {owner.patch}")
+    h, w = img.shape
+    out = np.empty((row1 - row0, w), dtype=np.float64)
+    _ffi.check(_ffi.lib().tmat_stp_predict_rows_host(_ffi.default_context().handle, net, _ffi.ptr(img), h, w,
+                                                     subdivisions, row0, row1, _ffi.ptr(out), None))
+    return out
+
+
+def predict_img_row_sharded(input_img, window_size, subdivisions, pred_func, rank=None, world=None):
+    """``predict_img_with_smooth_windowing`` of ONE image over ``world`` ranks: rank r computes its row strip
+    (owner computes; ~(ws/2) rows of overlap work per strip boundary, no data-path reduction) and the strips
+    are all-gathered over the default process group (NCCL on GPUs) so every rank returns the full image."""
+    import torch
+    import torch.distributed as dist
+    if world is None:
+        world = dist.get_world_size() if dist.is_initialized() else 1
+    if rank is None:
+        rank = dist.get_rank() if dist.is_initialized() else 0
+    h, w = np.asarray(input_img).shape
+    row0, row1 = strip_rows(h, rank, world)
+    mine = predict_rows_with_smooth_windowing(input_img, window_size, subdivisions, pred_func, row0, row1)
+    if world == 1:
+        return mine
+    rows_max = -(-h // world)
+    dev = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend() == "nccl" else torch.device("cpu")
+    buf = torch.zeros((rows_max, w), dtype=torch.float64, device=dev)
+    buf[: row1 - row0] = torch.from_numpy(mine).to(dev)
+    parts = [torch.empty_like(buf) for _ in range(world)]
+    dist.all_gather(parts, buf)
+    out = np.empty((h, w), np.float64)
+    for r in range(world):
+        a, b = strip_rows(h, r, world)
+        out[a:b] = parts[r][: b - a].cpu().numpy()
+    return out
