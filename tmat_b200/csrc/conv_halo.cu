@@ -148,8 +148,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
       }
     }
   } else if (warp == 1) {
-    // ================= MMA issuer (one thread runs the whole loop; taps fully unrolled) =================
-    if (lane == 0 && my_tiles > 0) {
+    // ================= MMA issuer (warp-convergent loop, one elected lane issues; taps fully unrolled) =====
+    if (my_tiles > 0) {
       constexpr uint32_t idesc = umma_idesc<BN>();
       // descriptor bits that do not change: SBO = PITCH rows of 128 bytes (A), 1024 bytes (B)
       const uint64_t a_hi = umma_desc_sw128_ex(0, PITCH * 128u, 0);
@@ -179,17 +179,14 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
             }
             // tap (ky, kx) = (t / 3, t % 3): the A tile starts (ky * PITCH + kx) 128-byte rows further on
             const uint64_t adesc = a0 + (uint64_t)((((t / 3) * PITCH + (t % 3)) * 128) >> 4);
-            if (t == 0) umma_bf16(tmem_d, adesc, bdesc, idesc, c != 0);
-            else umma_bf16(tmem_d, adesc, bdesc, idesc, 1u);
-#pragma unroll
-            for (int k = 1; k < KSLAB / 16; ++k) umma_bf16(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, 1u);
+            umma_k64_elect(tmem_d, adesc, bdesc, idesc, (t == 0) ? (uint32_t)(c != 0) : 1u);
             if (!BRES) {
-              umma_commit(empty_bar(stage));
+              umma_commit_elect(empty_bar(stage));
               if (++stage == p.n_stage) { stage = 0; phase ^= 1; }
             }
           }
-          umma_commit(rempty_bar(rs));
-          if (c == p.nslab - 1) umma_commit(tfull_bar(as));
+          umma_commit_elect(rempty_bar(rs));
+          if (c == p.nslab - 1) umma_commit_elect(tfull_bar(as));
           if (++rs == p.n_raw) { rs = 0; rphase ^= 1; }
         }
       }

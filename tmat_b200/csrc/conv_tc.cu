@@ -125,8 +125,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
       }
     }
   } else if (warp == 1) {
-    // ================= MMA issuer (one thread runs the whole loop) =================
-    if (lane == 0) {
+    // ================= MMA issuer (warp-convergent loop, one elected lane issues) =================
+    {
       constexpr uint32_t idesc = umma_idesc<BN>();
       int stage = 0; uint32_t phase = 0;
       int it = 0;
@@ -140,14 +140,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
           mbar_wait(full_bar(stage), phase);
           tc_fence_after();
           const uint32_t sa = smem_base + stage * L::STAGE_BYTES;
-          const uint64_t adesc = umma_desc_sw128(sa);
-          const uint64_t bdesc = umma_desc_sw128(sa + A_STAGE_BYTES);
-          // advance 16 bf16 = 32 bytes along K inside the swizzle atom: +2 in the (>>4) address field
-          umma_bf16(tmem_d, adesc, bdesc, idesc, ks != 0);
-#pragma unroll
-          for (int k = 1; k < KSLAB / 16; ++k) umma_bf16(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, 1u);
-          umma_commit(empty_bar(stage));                     // stage reusable once these MMAs retire
-          if (ks == p.nk - 1) umma_commit(tfull_bar(as));    // accumulator complete
+          // the four K = 16 MMAs of the stage: +32 bytes along K inside the swizzle atom per MMA
+          umma_k64_elect(tmem_d, umma_desc_sw128(sa), umma_desc_sw128(sa + A_STAGE_BYTES), idesc, (uint32_t)(ks != 0));
+          umma_commit_elect(empty_bar(stage));                     // stage reusable once these MMAs retire
+          if (ks == p.nk - 1) umma_commit_elect(tfull_bar(as));    // accumulator complete
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
