@@ -12,3 +12,12 @@ except Exception as e: print('fail', e)
 P
 TMAT_CHUNK=64 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file gpurun_out/launches_1024.csv python bench.py --size 1024 --steps 1 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/ncu_launch.log 2>&1
 echo "ncu exit $?"
+if [ -n "$QUICK_EXTRA_ENV" ]; then
+  env $QUICK_EXTRA_ENV timeout 300 python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/bench_q2.log 2>&1
+  python - <<P
+import json
+try:
+    d=json.loads(open('gpurun_out/bench_q2.log').read().strip().splitlines()[-1]); print('bench[extra env]', d['value'], d['ms_per_step'], d['roofline']['kernel_ms_per_step'])
+except Exception as e: print('fail', e)
+P
+fi

@@ -19,6 +19,7 @@ namespace {
 
 constexpr int DW_THREADS = 448;
 constexpr int DW_WARPS = 8;          // depthwise warps (6..13)
+constexpr int DW_GROUP_WARPS = 4;    // two groups of four warps, each owning every other (tile, slab) item
 constexpr int MAX_STAGES = 8;
 constexpr int MAX_RAW = 4;
 
@@ -92,6 +93,48 @@ __device__ __forceinline__ void dw_column(uint32_t rbase_sub, uint32_t abase_sub
   }
 }
 
+// Two adjacent tile columns (x even, x + 1) per thread: the four raw pixels x .. x+3 of a row are loaded and
+// unpacked once and feed both columns, so the per-output cost of ld.shared + bf16 unpack drops from 3 to 2.
+template <int TH_C, bool RELU>
+__device__ __forceinline__ void dw_column2(uint32_t rbase_sub, uint32_t abase_sub, uint32_t rp0, uint32_t ar0,
+                                           uint32_t RW, uint32_t TW, uint32_t jch, const f32x2 (&wr)[9][2]) {
+  f32x2 acc[3][2][2];   // [live output row][column][channel pair]
+  auto raw_addr = [&](uint32_t rp) { return rbase_sub + (rp << 7) + ((jch ^ (rp & 7u)) << 4); };
+#pragma unroll
+  for (int yy = 0; yy < TH_C + 2; ++yy) {
+    const uint32_t rp = rp0 + (uint32_t)yy * RW;
+    uint2 q[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) q[k] = ld_shared_v2(raw_addr(rp + k));
+    f32x2 f[4][2];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { f[k][0] = bf2_to_f2<RELU>(q[k].x); f[k][1] = bf2_to_f2<RELU>(q[k].y); }
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky) {
+      const int o = yy - ky;
+      if (o < 0 || o >= TH_C) continue;
+#pragma unroll
+      for (int col = 0; col < 2; ++col) {
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          f32x2 a = (ky == 0) ? fmul2(f[col][c], wr[0][c]) : ffma2(f[col][c], wr[3 * ky][c], acc[o % 3][col][c]);
+          a = ffma2(f[col + 1][c], wr[3 * ky + 1][c], a);
+          acc[o % 3][col][c] = ffma2(f[col + 2][c], wr[3 * ky + 2][c], a);
+        }
+      }
+    }
+    if (yy >= 2) {
+      const int o = yy - 2;
+#pragma unroll
+      for (int col = 0; col < 2; ++col) {
+        const uint32_t ar = ar0 + (uint32_t)o * TW + col;
+        st_shared_v2(abase_sub + (ar << 7) + ((jch ^ (ar & 7u)) << 4),
+                     make_uint2(f2_to_bf2(acc[o % 3][col][0]), f2_to_bf2(acc[o % 3][col][1])));
+      }
+    }
+  }
+}
+
 template <int BN>
 __global__ void __launch_bounds__(DW_THREADS, 1)
 conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constant__ CUtensorMap tmB,
@@ -120,8 +163,8 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
   const int lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < p.n_stage; ++s) { mbar_init(full_bar(s), 1 + DW_WARPS); mbar_init(empty_bar(s), 1); }
-    for (int s = 0; s < p.n_raw; ++s) { mbar_init(rfull_bar(s), 1); mbar_init(rempty_bar(s), DW_WARPS); }
+    for (int s = 0; s < p.n_stage; ++s) { mbar_init(full_bar(s), 1 + DW_GROUP_WARPS); mbar_init(empty_bar(s), 1); }
+    for (int s = 0; s < p.n_raw; ++s) { mbar_init(rfull_bar(s), 1); mbar_init(rempty_bar(s), DW_GROUP_WARPS); }
     for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 128); }
     fence_barrier_init();
     fence_proxy_async();
@@ -257,16 +300,21 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
   } else {
     // ================= depthwise (warps 6..13) =================
     const int t = threadIdx.x - 192;        // 0..255
-    const int h = t & 15;                   // 4-channel group within the 64-channel slab
+    const int grp = t >> 7;                 // group 0 takes even items, group 1 odd items
+    const int tg = t & 127;
+    const int h = tg & 15;                  // 4-channel group within the 64-channel slab
     const uint32_t jch = (uint32_t)(h >> 1);            // 16-byte chunk
     const uint32_t sub = (uint32_t)(h & 1) << 3;        // 8-byte half of the chunk
-    const int cslot = t >> 4;               // column slot 0..15
+    const int cslot = tg >> 4;              // column(-pair) slot 0..7
     const int ncols = TW * TN;
     const int RW = TW + 2, RH = TH + 2;
     const bool relu = p.relu_in != 0;
-    int stage = 0, rs = 0; uint32_t phase = 0, rphase = 0;
+    int item = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
-      for (int ks = 0; ks < p.nk; ++ks) {
+      for (int ks = 0; ks < p.nk; ++ks, ++item) {
+        if ((item & 1) != grp) continue;
+        const int stage = item % p.n_stage, rs = item % p.n_raw;
+        const uint32_t phase = (uint32_t)(item / p.n_stage) & 1u, rphase = (uint32_t)(item / p.n_raw) & 1u;
         f32x2 wr[9][2];
 #pragma unroll
         for (int tp = 0; tp < 9; ++tp) {
@@ -275,24 +323,26 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
         }
         mbar_wait(rfull_bar(rs), rphase);
         mbar_wait(empty_bar(stage), phase ^ 1);
-        const uint32_t rbase = raw_base + rs * p.raw_bytes;
-        const uint32_t abase = smem_base + stage * STAGE_BYTES;
-        for (int ci = cslot; ci < ncols; ci += 16) {
-          const int n = ci >> p.tw_log, x = ci & (TW - 1);
-          const uint32_t rp0 = (uint32_t)((n * RH) * RW + x);   // raw pixel (n, yy = 0, xx = x)
-          const uint32_t ar0 = (uint32_t)((n * TH) * TW + x);   // A row of output (n, y = 0, x)
-          if (!relu) {
-            if (TH == 8) dw_column<8, false>(rbase + sub, abase + sub, rp0, ar0, RW, TW, jch, wr);
-            else if (TH == 4) dw_column<4, false>(rbase + sub, abase + sub, rp0, ar0, RW, TW, jch, wr);
-            else if (TH == 16) dw_column<16, false>(rbase + sub, abase + sub, rp0, ar0, RW, TW, jch, wr);
-            else if (TH == 2) dw_column<2, false>(rbase + sub, abase + sub, rp0, ar0, RW, TW, jch, wr);
-            else dw_column<1, false>(rbase + sub, abase + sub, rp0, ar0, RW, TW, jch, wr);
-          } else {
-            if (TH == 8) dw_column<8, true>(rbase + sub, abase + sub, rp0, ar0, RW, TW, jch, wr);
-            else if (TH == 4) dw_column<4, true>(rbase + sub, abase + sub, rp0, ar0, RW, TW, jch, wr);
-            else if (TH == 16) dw_column<16, true>(rbase + sub, abase + sub, rp0, ar0, RW, TW, jch, wr);
-            else if (TH == 2) dw_column<2, true>(rbase + sub, abase + sub, rp0, ar0, RW, TW, jch, wr);
-            else dw_column<1, true>(rbase + sub, abase + sub, rp0, ar0, RW, TW, jch, wr);
+        const uint32_t rbase = raw_base + rs * p.raw_bytes + sub;
+        const uint32_t abase = smem_base + stage * STAGE_BYTES + sub;
+        {
+          for (int ci = 2 * cslot; ci < ncols; ci += 16) {
+            const int n = ci >> p.tw_log, x = ci & (TW - 1);
+            const uint32_t rp0 = (uint32_t)((n * RH) * RW + x);   // raw pixel (n, yy = 0, xx = x)
+            const uint32_t ar0 = (uint32_t)((n * TH) * TW + x);   // A row of output (n, y = 0, x)
+            if (!relu) {
+              if (TH == 8) dw_column2<8, false>(rbase, abase, rp0, ar0, RW, TW, jch, wr);
+              else if (TH == 4) dw_column2<4, false>(rbase, abase, rp0, ar0, RW, TW, jch, wr);
+              else if (TH == 16) dw_column2<16, false>(rbase, abase, rp0, ar0, RW, TW, jch, wr);
+              else if (TH == 2) dw_column2<2, false>(rbase, abase, rp0, ar0, RW, TW, jch, wr);
+              else dw_column2<1, false>(rbase, abase, rp0, ar0, RW, TW, jch, wr);
+            } else {
+              if (TH == 8) dw_column2<8, true>(rbase, abase, rp0, ar0, RW, TW, jch, wr);
+              else if (TH == 4) dw_column2<4, true>(rbase, abase, rp0, ar0, RW, TW, jch, wr);
+              else if (TH == 16) dw_column2<16, true>(rbase, abase, rp0, ar0, RW, TW, jch, wr);
+              else if (TH == 2) dw_column2<2, true>(rbase, abase, rp0, ar0, RW, TW, jch, wr);
+              else dw_column2<1, true>(rbase, abase, rp0, ar0, RW, TW, jch, wr);
+            }
           }
         }
         fence_proxy_async();
@@ -301,8 +351,6 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
           mbar_arrive(full_bar(stage));
           mbar_arrive(rempty_bar(rs));
         }
-        if (++stage == p.n_stage) { stage = 0; phase ^= 1; }
-        if (++rs == p.n_raw) { rs = 0; rphase ^= 1; }
       }
     }
   }
@@ -331,13 +379,14 @@ bool plan_dwpw(int B, int S, int C, int N, DwpwPlan* pl) {
     if (b8 * 10 <= best * 11) { pl->tw_log = a8; pl->th_log = 3; pl->tn_log = 4 - a8; }
   }
   const int TW = 1 << pl->tw_log, TH = 1 << pl->th_log, TN = 1 << pl->tn_log;
-  if (TH > 16 || TW + 2 > 256) return false;
+  if (TH > 16 || TW < 2 || TW + 2 > 256) return false;   // the depthwise warps work on column pairs
   pl->BN = N % 256 == 0 ? 256 : (N % 128 == 0 ? 128 : 64);
   pl->raw_tx = (TW + 2) * (TH + 2) * TN * 128;
   pl->raw_bytes = (pl->raw_tx + 1023) / 1024 * 1024;
   const int stage_bytes = A_STAGE_BYTES + pl->BN * KSLAB * 2;
   const int budget = 227 * 1024 - 2048 - 2 * STG_BYTES;
-  for (int n_raw = 3; n_raw >= 2; --n_raw) {
+  static const int raw_max = [] { const char* v = getenv("TMAT_DW_RAW"); int r = v ? atoi(v) : 3; return r < 2 ? 2 : (r > MAX_RAW ? MAX_RAW : r); }();
+  for (int n_raw = raw_max; n_raw >= 2; --n_raw) {
     int left = budget - n_raw * pl->raw_bytes;
     int n_stage = left / stage_bytes;
     if (n_stage > 4) n_stage = 4;
