@@ -17,11 +17,14 @@ using namespace tcptx;
 
 namespace {
 
-constexpr int DW_THREADS = 448;
-constexpr int DW_WARPS = 8;          // depthwise warps (6..13)
-constexpr int DW_GROUP_WARPS = 4;    // two groups of four warps, each owning every other (tile, slab) item
-constexpr int MAX_STAGES = 8;
-constexpr int MAX_RAW = 4;
+constexpr int DW_THREADS = 480;     // 15 warps
+constexpr int DW_GROUP_WARPS = 4;    // depthwise warps 6..13: two groups of four, each owning every other (tile, slab) item
+constexpr int MAX_A = 4;             // A (depthwise output) ring
+constexpr int MAX_B = 8;             // pointwise-weight slabs: ring entries, or all nk slabs when resident
+constexpr int MAX_RAW = 8;           // raw haloed input tiles
+constexpr int BAR_BYTES = 1024;      // barrier block
+constexpr int MAX_N = 1024;          // shift vector staged in shared memory
+constexpr int TAIL_BYTES = BAR_BYTES + MAX_N * 4 + 1024;   // barriers + shift + alignment slack
 
 struct DwpwParams {
   int tw_log, th_log, tn_log;
@@ -31,7 +34,8 @@ struct DwpwParams {
   int relu_in;
   int raw_bytes;     // one raw ring slot (1024-aligned)
   int raw_tx;        // bytes one raw TMA load delivers
-  int n_raw, n_stage;
+  int n_raw, n_a, n_b, n_stg;
+  int b_resident;    // all nk weight slabs stay in smem for the whole kernel (n_b == nk, tiles_n == 1)
   const float* dw;   // [9][C]
   EpiParams e;
 };
@@ -135,42 +139,84 @@ __device__ __forceinline__ void dw_column2(uint32_t rbase_sub, uint32_t abase_su
   }
 }
 
+// One 64-column chunk of a thread's accumulator row: TMEM -> + shift (from shared memory) -> [ReLU] -> bf16 ->
+// swizzled staging row.  Packed fp32 pairs: one FADD2 per two columns, ReLU folded into the bf16 convert.
+__device__ __forceinline__ void ld_shared_v4f(uint32_t addr, f32x2& a, f32x2& b) {
+  asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "r"(addr));
+}
+template <bool RELU>
+__device__ __forceinline__ void dwpw_epi_chunk(uint32_t taddr, uint32_t shift_addr, uint32_t buf_row, uint32_t sw) {
+#pragma unroll
+  for (int half = 0; half < 2; ++half) {
+    uint32_t rr[32];
+    tmem_ld32(taddr + half * 32, rr);
+    f32x2 sh[16];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) ld_shared_v4f(shift_addr + (uint32_t)(half * 32 + 4 * i) * 4u, sh[2 * i], sh[2 * i + 1]);
+    tmem_ld_wait();
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      uint4 o;
+      o.x = cvt_bf16x2<RELU>(fadd2(pack2(__uint_as_float(rr[8 * j]), __uint_as_float(rr[8 * j + 1])), sh[4 * j]));
+      o.y = cvt_bf16x2<RELU>(fadd2(pack2(__uint_as_float(rr[8 * j + 2]), __uint_as_float(rr[8 * j + 3])), sh[4 * j + 1]));
+      o.z = cvt_bf16x2<RELU>(fadd2(pack2(__uint_as_float(rr[8 * j + 4]), __uint_as_float(rr[8 * j + 5])), sh[4 * j + 2]));
+      o.w = cvt_bf16x2<RELU>(fadd2(pack2(__uint_as_float(rr[8 * j + 6]), __uint_as_float(rr[8 * j + 7])), sh[4 * j + 3]));
+      st_shared_v4(buf_row + ((((uint32_t)(half * 4 + j)) ^ sw) << 4), o);
+    }
+  }
+}
+
 template <int BN>
 __global__ void __launch_bounds__(DW_THREADS, 1)
 conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ DwpwParams p) {
-  constexpr int B_STAGE_BYTES = BN * KSLAB * 2;
-  constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+  constexpr int B_BYTES = BN * KSLAB * 2;
   constexpr int TMEM_COLS = 2 * BN;
   extern __shared__ uint8_t smem_raw[];
+  // [A ring | B ring or resident slabs | raw ring | store staging | barriers]
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t raw_base = smem_base + p.n_stage * STAGE_BYTES;
+  const uint32_t b_base = smem_base + p.n_a * A_STAGE_BYTES;
+  const uint32_t raw_base = b_base + p.n_b * B_BYTES;
   const uint32_t stg_base = raw_base + p.n_raw * p.raw_bytes;
-  const uint32_t bar_base = stg_base + 2 * STG_BYTES;
-  auto full_bar = [&](int s) { return bar_base + 8u * s; };
-  auto empty_bar = [&](int s) { return bar_base + 8u * (MAX_STAGES + s); };
-  auto rfull_bar = [&](int s) { return bar_base + 8u * (2 * MAX_STAGES + s); };
-  auto rempty_bar = [&](int s) { return bar_base + 8u * (2 * MAX_STAGES + MAX_RAW + s); };
-  auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * MAX_STAGES + 2 * MAX_RAW + s); };
-  auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * MAX_STAGES + 2 * MAX_RAW + 2 + s); };
-  constexpr int TMEM_SLOT = 8 * (2 * MAX_STAGES + 2 * MAX_RAW + 4);
+  const uint32_t bar_base = stg_base + p.n_stg * STG_BYTES;
+  auto afull_bar = [&](int s) { return bar_base + 8u * s; };
+  auto aempty_bar = [&](int s) { return bar_base + 8u * (MAX_A + s); };
+  auto bfull_bar = [&](int s) { return bar_base + 8u * (2 * MAX_A + s); };
+  auto bempty_bar = [&](int s) { return bar_base + 8u * (2 * MAX_A + MAX_B + s); };
+  auto rfull_bar = [&](int s) { return bar_base + 8u * (2 * MAX_A + 2 * MAX_B + s); };
+  auto rempty_bar = [&](int s) { return bar_base + 8u * (2 * MAX_A + 2 * MAX_B + MAX_RAW + s); };
+  auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * MAX_A + 2 * MAX_B + 2 * MAX_RAW + s); };
+  auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * MAX_A + 2 * MAX_B + 2 * MAX_RAW + 2 + s); };
+  constexpr int TMEM_SLOT = 8 * (2 * MAX_A + 2 * MAX_B + 2 * MAX_RAW + 4);
+  constexpr int ISSUED_SLOT = TMEM_SLOT + 8;
+  const uint32_t shift_base = bar_base + BAR_BYTES;      // the layer's N shift values (fp32), staged once
   const uint32_t tmem_slot = bar_base + TMEM_SLOT;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
   volatile uint32_t* tmem_slot_gen =
       reinterpret_cast<volatile uint32_t*>(smem_gen + (bar_base - smem_base) + TMEM_SLOT);
+  // number of raw tiles the producer has issued so far: a depthwise group only starts to wait on a slot's
+  // barrier once the load it wants has been issued (two groups share the ring, so a plain parity wait could
+  // be satisfied by the slot's previous use)
+  volatile int* issued = reinterpret_cast<volatile int*>(smem_gen + (bar_base - smem_base) + ISSUED_SLOT);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < p.n_stage; ++s) { mbar_init(full_bar(s), 1 + DW_GROUP_WARPS); mbar_init(empty_bar(s), 1); }
+    for (int s = 0; s < p.n_a; ++s) { mbar_init(afull_bar(s), DW_GROUP_WARPS); mbar_init(aempty_bar(s), 1); }
+    for (int s = 0; s < p.n_b; ++s) { mbar_init(bfull_bar(s), 1); mbar_init(bempty_bar(s), 1); }
     for (int s = 0; s < p.n_raw; ++s) { mbar_init(rfull_bar(s), 1); mbar_init(rempty_bar(s), DW_GROUP_WARPS); }
+    *issued = 0;
     for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 128); }
     fence_barrier_init();
     fence_proxy_async();
     tma_prefetch_desc(&tmRaw);
     tma_prefetch_desc(&tmB);
     tma_prefetch_desc(&tmOut);
+  }
+  {
+    float* shift_gen = reinterpret_cast<float*>(smem_gen + (bar_base - smem_base) + BAR_BYTES);
+    for (int i = threadIdx.x; i < p.e.Cout; i += DW_THREADS) shift_gen[i] = __ldg(p.e.shift + i);
   }
   if (warp == 1) tmem_alloc<TMEM_COLS>(tmem_slot);
   tc_fence_before();
@@ -189,8 +235,10 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
   };
 
   if (warp == 0) {
-    // ================= TMA producer =================
-    int stage = 0, rs = 0; uint32_t phase = 0, rphase = 0;
+    // ================= raw-tile producer =================
+    // Only the raw ring gates this warp (the weight slabs have their own producer), so it runs as far ahead of
+    // the depthwise groups as the ring allows: n_raw - 2 haloed tiles in flight while two are being worked on.
+    int rs = 0; uint32_t rphase = 0; int item = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
       int nt, x0, y0, b0;
       decode(tile, nt, x0, y0, b0);
@@ -199,23 +247,45 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
         if (lane == 0) {
           mbar_expect_tx(rfull_bar(rs), p.raw_tx);
           tma_load_4d(raw_base + rs * p.raw_bytes, &tmRaw, rfull_bar(rs), ks * KSLAB, x0 - 1, y0 - 1, b0);
-        }
-        mbar_wait(empty_bar(stage), phase ^ 1);
-        if (lane == 0) {
-          mbar_expect_tx(full_bar(stage), B_STAGE_BYTES);
-          tma_load_2d(smem_base + stage * STAGE_BYTES + A_STAGE_BYTES, &tmB, full_bar(stage), ks * KSLAB, nt * BN);
+          *issued = ++item;
         }
         __syncwarp();
-        if (++stage == p.n_stage) { stage = 0; phase ^= 1; }
         if (++rs == p.n_raw) { rs = 0; rphase ^= 1; }
+      }
+    }
+  } else if (warp == 14) {
+    // ================= pointwise-weight producer =================
+    if (p.b_resident) {
+      if (lane == 0) {
+        for (int ks = 0; ks < p.nk; ++ks) {
+          mbar_expect_tx(bfull_bar(ks), B_BYTES);
+          tma_load_2d(b_base + ks * B_BYTES, &tmB, bfull_bar(ks), ks * KSLAB, 0);
+        }
+      }
+    } else {
+      int sb = 0; uint32_t bphase = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+        const int nt = tile % p.tiles_n;
+        for (int ks = 0; ks < p.nk; ++ks) {
+          mbar_wait(bempty_bar(sb), bphase ^ 1);
+          if (lane == 0) {
+            mbar_expect_tx(bfull_bar(sb), B_BYTES);
+            tma_load_2d(b_base + sb * B_BYTES, &tmB, bfull_bar(sb), ks * KSLAB, nt * BN);
+          }
+          __syncwarp();
+          if (++sb == p.n_b) { sb = 0; bphase ^= 1; }
+        }
       }
     }
   } else if (warp == 1) {
     // ================= MMA issuer (warp-convergent loop, one elected lane issues) =================
     {
       constexpr uint32_t idesc = umma_idesc<BN>();
-      int stage = 0; uint32_t phase = 0;
+      int sa = 0, sb = 0; uint32_t pa = 0, pb = 0;
       int it = 0;
+      if (p.b_resident) {
+        for (int ks = 0; ks < p.nk; ++ks) mbar_wait(bfull_bar(ks), 0);
+      }
       for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
         const int as = it & 1;
         const uint32_t aphase = (it >> 1) & 1;
@@ -223,14 +293,20 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + as * BN;
         for (int ks = 0; ks < p.nk; ++ks) {
-          mbar_wait(full_bar(stage), phase);
+          if (!p.b_resident) mbar_wait(bfull_bar(sb), pb);
+          mbar_wait(afull_bar(sa), pa);
           tc_fence_after();
-          const uint32_t sa = smem_base + stage * STAGE_BYTES;
-          // the four K = 16 MMAs of the stage: +32 bytes along K inside the swizzle atom per MMA
-          umma_k64_elect(tmem_d, umma_desc_sw128(sa), umma_desc_sw128(sa + A_STAGE_BYTES), idesc, (uint32_t)(ks != 0));
-          umma_commit_elect(empty_bar(stage));                     // stage reusable once these MMAs retire
+          const uint32_t a_addr = smem_base + sa * A_STAGE_BYTES;
+          const uint32_t b_addr = b_base + (p.b_resident ? ks : sb) * B_BYTES;
+          // the four K = 16 MMAs of the slab: +32 bytes along K inside the swizzle atom per MMA
+          umma_k64_elect(tmem_d, umma_desc_sw128(a_addr), umma_desc_sw128(b_addr), idesc, (uint32_t)(ks != 0));
+          umma_commit_elect(aempty_bar(sa));                       // A stage reusable once these MMAs retire
+          if (!p.b_resident) {
+            umma_commit_elect(bempty_bar(sb));
+            if (++sb == p.n_b) { sb = 0; pb ^= 1; }
+          }
           if (ks == p.nk - 1) umma_commit_elect(tfull_bar(as));    // accumulator complete
-          if (++stage == p.n_stage) { stage = 0; phase ^= 1; }
+          if (++sa == p.n_a) { sa = 0; pa ^= 1; }
         }
       }
     }
@@ -256,33 +332,11 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
 #pragma unroll 1
       for (int c64 = 0; c64 < BN; c64 += 64) {
         const int ch0 = nt * BN + c64;
-        if (leader) tma_store_wait_read<1>();
+        if (leader) { if (p.n_stg == 2) tma_store_wait_read<1>(); else tma_store_wait_read<0>(); }
         epi_bar_sync();
         const uint32_t buf = stg_base + sbuf * STG_BYTES;
-#pragma unroll
-        for (int half = 0; half < 2; ++half) {
-          uint32_t rr[32];
-          tmem_ld32(taddr + c64 + half * 32, rr);
-          tmem_ld_wait();
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            float f[8];
-#pragma unroll
-            for (int i = 0; i < 8; i += 4) {
-              float4 s = __ldg(reinterpret_cast<const float4*>(e.shift + ch0 + half * 32 + 8 * j + i));
-              f[i] = __uint_as_float(rr[8 * j + i]) + s.x; f[i + 1] = __uint_as_float(rr[8 * j + i + 1]) + s.y;
-              f[i + 2] = __uint_as_float(rr[8 * j + i + 2]) + s.z; f[i + 3] = __uint_as_float(rr[8 * j + i + 3]) + s.w;
-            }
-            if (e.relu) {
-#pragma unroll
-              for (int i = 0; i < 8; ++i) f[i] = fmaxf(f[i], 0.f);
-            }
-            uint4 o;
-            o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]);
-            o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
-            st_shared_v4(buf + stg_row + ((((uint32_t)(half * 4 + j)) ^ sw) << 4), o);
-          }
-        }
+        if (e.relu) dwpw_epi_chunk<true>(taddr + c64, shift_base + (uint32_t)ch0 * 4u, buf + stg_row, sw);
+        else dwpw_epi_chunk<false>(taddr + c64, shift_base + (uint32_t)ch0 * 4u, buf + stg_row, sw);
         if (c64 + 64 >= BN) {
           tc_fence_before();
           mbar_arrive(tempty_bar(as));
@@ -293,7 +347,7 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
           tma_store_4d(&tmOut, buf, ch0, x0, y0, b0);
           tma_store_commit();
         }
-        sbuf ^= 1;
+        if (p.n_stg == 2) sbuf ^= 1;
       }
     }
     if (leader) tma_store_wait_all();
@@ -313,18 +367,19 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
       for (int ks = 0; ks < p.nk; ++ks, ++item) {
         if ((item & 1) != grp) continue;
-        const int stage = item % p.n_stage, rs = item % p.n_raw;
-        const uint32_t phase = (uint32_t)(item / p.n_stage) & 1u, rphase = (uint32_t)(item / p.n_raw) & 1u;
+        const int sa = item % p.n_a, rs = item % p.n_raw;
+        const uint32_t pa = (uint32_t)(item / p.n_a) & 1u, rphase = (uint32_t)(item / p.n_raw) & 1u;
         f32x2 wr[9][2];
 #pragma unroll
         for (int tp = 0; tp < 9; ++tp) {
           float4 wv = __ldg(reinterpret_cast<const float4*>(p.dw + tp * p.C + ks * KSLAB + h * 4));
           wr[tp][0] = pack2(wv.x, wv.y); wr[tp][1] = pack2(wv.z, wv.w);
         }
+        while (*issued <= item) { }
         mbar_wait(rfull_bar(rs), rphase);
-        mbar_wait(empty_bar(stage), phase ^ 1);
+        mbar_wait(aempty_bar(sa), pa ^ 1);
         const uint32_t rbase = raw_base + rs * p.raw_bytes + sub;
-        const uint32_t abase = smem_base + stage * STAGE_BYTES + sub;
+        const uint32_t abase = smem_base + sa * A_STAGE_BYTES + sub;
         {
           for (int ci = 2 * cslot; ci < ncols; ci += 16) {
             const int n = ci >> p.tw_log, x = ci & (TW - 1);
@@ -348,7 +403,7 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
         fence_proxy_async();
         __syncwarp();
         if (lane == 0) {
-          mbar_arrive(full_bar(stage));
+          mbar_arrive(afull_bar(sa));
           mbar_arrive(rempty_bar(rs));
         }
       }
@@ -361,11 +416,11 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
 }
 
 struct DwpwPlan {
-  int tw_log, th_log, tn_log, BN, n_raw, n_stage, raw_bytes, raw_tx, smem;
+  int tw_log, th_log, tn_log, BN, n_raw, n_a, n_b, n_stg, b_resident, raw_bytes, raw_tx, smem;
 };
 
 bool plan_dwpw(int B, int S, int C, int N, DwpwPlan* pl) {
-  if (C % KSLAB != 0 || N % 64 != 0 || C / KSLAB > 64) return false;
+  if (C % KSLAB != 0 || N % 64 != 0 || C / KSLAB > 64 || N > MAX_N) return false;
   tc_choose_tile(B, S, S, &pl->tw_log, &pl->th_log, &pl->tn_log);
   {
     // the depthwise warps re-read 2 halo rows per tile column: prefer 8-row tiles (16x8x1, 8x8x2, 4x8x4 ...)
@@ -383,20 +438,28 @@ bool plan_dwpw(int B, int S, int C, int N, DwpwPlan* pl) {
   pl->BN = N % 256 == 0 ? 256 : (N % 128 == 0 ? 128 : 64);
   pl->raw_tx = (TW + 2) * (TH + 2) * TN * 128;
   pl->raw_bytes = (pl->raw_tx + 1023) / 1024 * 1024;
-  const int stage_bytes = A_STAGE_BYTES + pl->BN * KSLAB * 2;
-  const int budget = 227 * 1024 - 2048 - 2 * STG_BYTES;
-  static const int raw_max = [] { const char* v = getenv("TMAT_DW_RAW"); int r = v ? atoi(v) : 3; return r < 2 ? 2 : (r > MAX_RAW ? MAX_RAW : r); }();
-  for (int n_raw = raw_max; n_raw >= 2; --n_raw) {
-    int left = budget - n_raw * pl->raw_bytes;
-    int n_stage = left / stage_bytes;
-    if (n_stage > 4) n_stage = 4;
-    if (n_stage >= 2) {
-      pl->n_raw = n_raw; pl->n_stage = n_stage;
-      pl->smem = n_stage * stage_bytes + n_raw * pl->raw_bytes + 2 * STG_BYTES + 2048;
-      return true;
-    }
+  // Shared memory goes to the raw ring first: the depthwise groups hold two slots and only the slots beyond
+  // those keep loads in flight.  Weights stay resident when all slabs fit in 64 KB, else a two-slab ring;
+  // the store staging drops to one buffer and the A ring to two stages when that buys another raw slot.
+  const int b_bytes = pl->BN * KSLAB * 2;
+  const int nk = C / KSLAB;
+  static const int raw_max = [] { const char* v = getenv("TMAT_DW_RAW"); int r = v ? atoi(v) : MAX_RAW; return r < 2 ? 2 : (r > MAX_RAW ? MAX_RAW : r); }();
+  static const int raw_want = [] { const char* v = getenv("TMAT_DW_RAW_WANT"); int r = v ? atoi(v) : 5; return r < 2 ? 2 : r; }();
+  pl->b_resident = (N == pl->BN && nk * b_bytes <= 64 * 1024 && nk <= MAX_B) ? 1 : 0;
+  pl->n_b = pl->b_resident ? nk : 2;
+  const int budget = 227 * 1024 - TAIL_BYTES - pl->n_b * b_bytes;
+  // first option (in order of preference) that reaches raw_want slots, else the one with the most slots
+  int best_raw = 0;
+  const int opts[4][2] = {{3, 2}, {3, 1}, {2, 2}, {2, 1}};     // {n_a, n_stg}
+  for (int o = 0; o < 4; ++o) {
+    int n_raw = (budget - opts[o][0] * A_STAGE_BYTES - opts[o][1] * STG_BYTES) / pl->raw_bytes;
+    n_raw = std::min(n_raw, std::min(raw_max, raw_want));
+    if (n_raw > best_raw) { best_raw = n_raw; pl->n_a = opts[o][0]; pl->n_stg = opts[o][1]; pl->n_raw = n_raw; }
+    if (best_raw >= raw_want) break;
   }
-  return false;
+  if (best_raw < 2) return false;
+  pl->smem = pl->n_a * A_STAGE_BYTES + pl->n_b * b_bytes + pl->n_raw * pl->raw_bytes + pl->n_stg * STG_BYTES + TAIL_BYTES;
+  return true;
 }
 
 template <int BN>
@@ -446,7 +509,8 @@ int dwpw_run(tmat_ctx* ctx, const bf16* in, int B, int S, int C, const float* dw
   TMAT_REQUIRE(total < (1ll << 31), "dwpw: too many tiles");
   p.total_tiles = (int)total;
   p.nk = C / KSLAB; p.C = C; p.relu_in = relu_in;
-  p.raw_bytes = pl.raw_bytes; p.raw_tx = pl.raw_tx; p.n_raw = pl.n_raw; p.n_stage = pl.n_stage;
+  p.raw_bytes = pl.raw_bytes; p.raw_tx = pl.raw_tx;
+  p.n_raw = pl.n_raw; p.n_a = pl.n_a; p.n_b = pl.n_b; p.n_stg = pl.n_stg; p.b_resident = pl.b_resident;
   p.dw = dw;
   memset(&p.e, 0, sizeof(p.e));
   p.e.mode = EPI_STORE; p.e.relu = relu_out; p.e.B = B; p.e.H = S; p.e.W = S; p.e.Cout = N; p.e.ppg = 1;

@@ -50,6 +50,11 @@ __device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map
       "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
       ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
 }
+// haloed/plain 4-D box -> L2 only (no smem, no barrier): lets a short smem ring keep many more bytes in flight
+__device__ __forceinline__ void tma_prefetch_l2_4d(const CUtensorMap* map, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.prefetch.tensor.4d.L2.global.tile [%0, {%1, %2, %3, %4}];"
+               ::"l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
   asm volatile(
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
@@ -171,6 +176,28 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
   __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&h);
 }
+__device__ __forceinline__ f32x2 fadd2(f32x2 a, f32x2 b) {
+  f32x2 d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+// fp32 pair -> bf16x2 (lo in the low half), round to nearest even; RELU clamps negatives to +0 inside the convert
+template <bool RELU>
+__device__ __forceinline__ uint32_t cvt_bf16x2(f32x2 v) {
+  float lo, hi;
+  unpack2(v, lo, hi);
+  uint32_t d;
+  if (RELU) asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+  else asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+  return d;
+}
+__device__ __forceinline__ uint32_t cvt_bf16x2(f32x2 v, bool relu) {
+  return relu ? cvt_bf16x2<true>(v) : cvt_bf16x2<false>(v);
+}
+// bf16x2 -> fp32 pair (exact)
+__device__ __forceinline__ f32x2 bf16x2_to_f32x2(uint32_t x) {
+  return pack2(__uint_as_float(x << 16), __uint_as_float(x & 0xffff0000u));
+}
 __device__ __forceinline__ float sigmoid_f(float v) { return 1.f / (1.f + __expf(-v)); }
 
 
@@ -231,40 +258,39 @@ __device__ __forceinline__ void tc_epilogue_tile(const EpiParams& e, const TcOut
             uint32_t rr[32];
             tmem_ld32(taddr + c64 + half * 32, rr);
             tmem_ld_wait();
-            float v[32];
+            // packed fp32 pairs: one FADD2 per two columns, ReLU folded into the bf16 convert
+            f32x2 v[16];
 #pragma unroll
             for (int i = 0; i < 32; i += 4) {
               float4 s = __ldg(reinterpret_cast<const float4*>(e.shift + ch0 + half * 32 + i));
-              v[i] = __uint_as_float(rr[i]) + s.x; v[i + 1] = __uint_as_float(rr[i + 1]) + s.y;
-              v[i + 2] = __uint_as_float(rr[i + 2]) + s.z; v[i + 3] = __uint_as_float(rr[i + 3]) + s.w;
+              v[i / 2] = fadd2(pack2(__uint_as_float(rr[i]), __uint_as_float(rr[i + 1])), pack2(s.x, s.y));
+              v[i / 2 + 1] = fadd2(pack2(__uint_as_float(rr[i + 2]), __uint_as_float(rr[i + 3])), pack2(s.z, s.w));
             }
             if (addp != nullptr) {
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
                 const uint4 u = av[half * 4 + j];
-                const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                  float2 t = __bfloat1622float2(h[i]);
-                  v[8 * j + 2 * i] += t.x; v[8 * j + 2 * i + 1] += t.y;
-                }
+                v[4 * j] = fadd2(v[4 * j], bf16x2_to_f32x2(u.x));
+                v[4 * j + 1] = fadd2(v[4 * j + 1], bf16x2_to_f32x2(u.y));
+                v[4 * j + 2] = fadd2(v[4 * j + 2], bf16x2_to_f32x2(u.z));
+                v[4 * j + 3] = fadd2(v[4 * j + 3], bf16x2_to_f32x2(u.w));
               }
             }
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
               const uint32_t off = (((uint32_t)(half * 4 + j)) ^ sw) << 4;   // 128-byte swizzle: chunk ^= row % 8
-              float f[8];
-#pragma unroll
-              for (int i = 0; i < 8; ++i) f[i] = e.relu ? fmaxf(v[8 * j + i], 0.f) : v[8 * j + i];
               uint4 o;
-              o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]);
-              o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
+              if (e.relu) {
+                o.x = cvt_bf16x2<true>(v[4 * j]); o.y = cvt_bf16x2<true>(v[4 * j + 1]);
+                o.z = cvt_bf16x2<true>(v[4 * j + 2]); o.w = cvt_bf16x2<true>(v[4 * j + 3]);
+              } else {
+                o.x = cvt_bf16x2<false>(v[4 * j]); o.y = cvt_bf16x2<false>(v[4 * j + 1]);
+                o.z = cvt_bf16x2<false>(v[4 * j + 2]); o.w = cvt_bf16x2<false>(v[4 * j + 3]);
+              }
               st_shared_v4(buf0 + off, o);
               if (dual) {
-                o.x = pack_bf16x2(fmaxf(v[8 * j], 0.f), fmaxf(v[8 * j + 1], 0.f));
-                o.y = pack_bf16x2(fmaxf(v[8 * j + 2], 0.f), fmaxf(v[8 * j + 3], 0.f));
-                o.z = pack_bf16x2(fmaxf(v[8 * j + 4], 0.f), fmaxf(v[8 * j + 5], 0.f));
-                o.w = pack_bf16x2(fmaxf(v[8 * j + 6], 0.f), fmaxf(v[8 * j + 7], 0.f));
+                o.x = cvt_bf16x2<true>(v[4 * j]); o.y = cvt_bf16x2<true>(v[4 * j + 1]);
+                o.z = cvt_bf16x2<true>(v[4 * j + 2]); o.w = cvt_bf16x2<true>(v[4 * j + 3]);
                 st_shared_v4(buf1 + off, o);
               }
             }
