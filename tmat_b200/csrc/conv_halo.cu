@@ -211,7 +211,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
       const bool valid = (x < e.W) && (y < e.H);
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
       tc_epilogue_tile<BN>(e, om, taddr, 0, nt, x0, y0, b0, x, y, b, valid, stg_base, stg_row, sw, leader, sbuf,
-                           tempty_bar(as), tfull_bar(as), aphase);
+                           tempty_bar(as), tfull_bar(as), aphase, bar_base + 512u);
     }
     if (leader) tma_store_wait_all();
   }

@@ -48,7 +48,8 @@ struct TcSmem {
   static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
   static constexpr int STG_OFFSET = STAGES * STAGE_BYTES;
   static constexpr int BAR_OFFSET = STG_OFFSET + N_STG * STG_BYTES;
-  static constexpr int BYTES = BAR_OFFSET + 256 + 1024;   // barriers + alignment slack
+  static constexpr int SHIFT_OFFSET = BAR_OFFSET + 256;     // BN fp32 shift values of the current tile
+  static constexpr int BYTES = SHIFT_OFFSET + (BN < 64 ? 64 : BN) * 4 + 1024;   // barriers + shift + alignment slack
   static_assert(BYTES <= 227 * 1024, "shared memory budget");
 };
 
@@ -172,7 +173,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
       const bool valid = (x < e.W) && (y < e.H) && (b < e.B);
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
       tc_epilogue_tile<BN>(e, om, taddr, g, nt, x0, y0, b0, x, y, b, valid, stg_base, stg_row, sw, leader, sbuf,
-                           tempty_bar(as), tfull_bar(as), aphase);
+                           tempty_bar(as), tfull_bar(as), aphase, smem_base + L::SHIFT_OFFSET);
     }
     if (leader) tma_store_wait_all();            // smem must outlive the last store's read
   }

@@ -1,6 +1,7 @@
 // PTX wrappers shared by the tcgen05 kernels (conv_tc.cu, conv_dwpw.cu): mbarrier, TMA load / store,
 // TMEM allocation, UMMA descriptors and issue, tcgen05.ld.
 #pragma once
+#include <type_traits>
 #include "unet.cuh"
 #include <cuda.h>
 
@@ -176,6 +177,12 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
   __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&h);
 }
+__device__ __forceinline__ void st_shared_f32(uint32_t addr, float v) {
+  asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ void ld_shared_2xf32x2(uint32_t addr, f32x2& a, f32x2& b) {
+  asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "r"(addr));
+}
 __device__ __forceinline__ f32x2 fadd2(f32x2 a, f32x2 b) {
   f32x2 d;
   asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
@@ -222,8 +229,15 @@ template <int BN>
 __device__ __forceinline__ void tc_epilogue_tile(const EpiParams& e, const TcOutMaps& om, uint32_t taddr, int g, int nt,
                                                  int x0, int y0, int b0, int x, int y, int b, bool valid,
                                                  uint32_t stg_base, uint32_t stg_row, uint32_t sw, bool leader,
-                                                 int& sbuf, uint32_t tempty, uint32_t tfull, uint32_t tphase) {
+                                                 int& sbuf, uint32_t tempty, uint32_t tfull, uint32_t tphase,
+                                                 uint32_t shift_smem) {
       if constexpr (BN >= 64) {
+        // this tile's BN shift values -> shared memory (read back as broadcast 16-byte loads below); the
+        // hand-over barrier of the first chunk orders the writes, the last barrier of the previous tile the reuse
+        for (int c = (int)(stg_row >> 7); c < BN; c += 128) {
+          const int col = nt * BN + c;
+          st_shared_f32(shift_smem + 4u * (uint32_t)c, __ldg(e.shift + (e.mode == EPI_PAR ? col % e.Cout : col)));
+        }
         const bool dual = (e.out2 != nullptr);
         const bf16* addp = nullptr;
         if (e.add_src != nullptr && valid) {
@@ -253,48 +267,47 @@ __device__ __forceinline__ void tc_epilogue_tile(const EpiParams& e, const TcOut
           epi_bar_sync();
           const uint32_t buf0 = stg_base + (dual ? 0 : sbuf * STG_BYTES) + stg_row;
           const uint32_t buf1 = stg_base + STG_BYTES + stg_row;
+          auto chunk = [&](auto relu_c) {
+            constexpr bool RELU = decltype(relu_c)::value;
 #pragma unroll
-          for (int half = 0; half < 2; ++half) {
-            uint32_t rr[32];
-            tmem_ld32(taddr + c64 + half * 32, rr);
-            tmem_ld_wait();
-            // packed fp32 pairs: one FADD2 per two columns, ReLU folded into the bf16 convert
-            f32x2 v[16];
+            for (int half = 0; half < 2; ++half) {
+              uint32_t rr[32];
+              tmem_ld32(taddr + c64 + half * 32, rr);
+              // packed fp32 pairs: one FADD2 per two columns, ReLU folded into the bf16 convert
+              f32x2 v[16];
 #pragma unroll
-            for (int i = 0; i < 32; i += 4) {
-              float4 s = __ldg(reinterpret_cast<const float4*>(e.shift + ch0 + half * 32 + i));
-              v[i / 2] = fadd2(pack2(__uint_as_float(rr[i]), __uint_as_float(rr[i + 1])), pack2(s.x, s.y));
-              v[i / 2 + 1] = fadd2(pack2(__uint_as_float(rr[i + 2]), __uint_as_float(rr[i + 3])), pack2(s.z, s.w));
-            }
-            if (addp != nullptr) {
+              for (int i = 0; i < 8; ++i)
+                ld_shared_2xf32x2(shift_smem + 4u * (uint32_t)(c64 + half * 32 + 4 * i), v[2 * i], v[2 * i + 1]);
+              tmem_ld_wait();
+#pragma unroll
+              for (int i = 0; i < 16; ++i)
+                v[i] = fadd2(pack2(__uint_as_float(rr[2 * i]), __uint_as_float(rr[2 * i + 1])), v[i]);
+              if (addp != nullptr) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  const uint4 u = av[half * 4 + j];
+                  v[4 * j] = fadd2(v[4 * j], bf16x2_to_f32x2(u.x));
+                  v[4 * j + 1] = fadd2(v[4 * j + 1], bf16x2_to_f32x2(u.y));
+                  v[4 * j + 2] = fadd2(v[4 * j + 2], bf16x2_to_f32x2(u.z));
+                  v[4 * j + 3] = fadd2(v[4 * j + 3], bf16x2_to_f32x2(u.w));
+                }
+              }
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
-                const uint4 u = av[half * 4 + j];
-                v[4 * j] = fadd2(v[4 * j], bf16x2_to_f32x2(u.x));
-                v[4 * j + 1] = fadd2(v[4 * j + 1], bf16x2_to_f32x2(u.y));
-                v[4 * j + 2] = fadd2(v[4 * j + 2], bf16x2_to_f32x2(u.z));
-                v[4 * j + 3] = fadd2(v[4 * j + 3], bf16x2_to_f32x2(u.w));
+                const uint32_t off = (((uint32_t)(half * 4 + j)) ^ sw) << 4;   // 128-byte swizzle: chunk ^= row % 8
+                uint4 o;
+                o.x = cvt_bf16x2<RELU>(v[4 * j]); o.y = cvt_bf16x2<RELU>(v[4 * j + 1]);
+                o.z = cvt_bf16x2<RELU>(v[4 * j + 2]); o.w = cvt_bf16x2<RELU>(v[4 * j + 3]);
+                st_shared_v4(buf0 + off, o);
+                if (dual) {
+                  o.x = cvt_bf16x2<true>(v[4 * j]); o.y = cvt_bf16x2<true>(v[4 * j + 1]);
+                  o.z = cvt_bf16x2<true>(v[4 * j + 2]); o.w = cvt_bf16x2<true>(v[4 * j + 3]);
+                  st_shared_v4(buf1 + off, o);
+                }
               }
             }
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const uint32_t off = (((uint32_t)(half * 4 + j)) ^ sw) << 4;   // 128-byte swizzle: chunk ^= row % 8
-              uint4 o;
-              if (e.relu) {
-                o.x = cvt_bf16x2<true>(v[4 * j]); o.y = cvt_bf16x2<true>(v[4 * j + 1]);
-                o.z = cvt_bf16x2<true>(v[4 * j + 2]); o.w = cvt_bf16x2<true>(v[4 * j + 3]);
-              } else {
-                o.x = cvt_bf16x2<false>(v[4 * j]); o.y = cvt_bf16x2<false>(v[4 * j + 1]);
-                o.z = cvt_bf16x2<false>(v[4 * j + 2]); o.w = cvt_bf16x2<false>(v[4 * j + 3]);
-              }
-              st_shared_v4(buf0 + off, o);
-              if (dual) {
-                o.x = cvt_bf16x2<true>(v[4 * j]); o.y = cvt_bf16x2<true>(v[4 * j + 1]);
-                o.z = cvt_bf16x2<true>(v[4 * j + 2]); o.w = cvt_bf16x2<true>(v[4 * j + 3]);
-                st_shared_v4(buf1 + off, o);
-              }
-            }
-          }
+          };
+          if (e.relu) chunk(std::true_type{}); else chunk(std::false_type{});
           if (c64 + 64 >= BN) {                  // accumulator fully read: hand the TMEM buffer back
             tc_fence_before();
             mbar_arrive(tempty);
