@@ -139,6 +139,52 @@ __device__ __forceinline__ void dw_column2(uint32_t rbase_sub, uint32_t abase_su
   }
 }
 
+// dw_column2 with the tile width known at compile time: pixel offsets become immediates and the 128-byte swizzle
+// term (pixel index mod 8) reduces to eight per-thread base registers for the loads and two for the stores, so
+// the row loop carries no address arithmetic at all.
+template <int TH_C, int TW_C, bool RELU>
+__device__ __forceinline__ void dw_column2_fixed(uint32_t rbase_sub, uint32_t abase_sub, uint32_t rp0, uint32_t ar0,
+                                                 uint32_t jch, const f32x2 (&wr)[9][2]) {
+  constexpr int RW = TW_C + 2;
+  uint32_t R[8], S[8];
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {
+    R[c] = rbase_sub + (rp0 << 7) + ((jch ^ ((rp0 + c) & 7u)) << 4);
+    S[c] = abase_sub + (ar0 << 7) + ((jch ^ ((ar0 + c) & 7u)) << 4);
+  }
+  f32x2 acc[3][2][2];
+#pragma unroll
+  for (int yy = 0; yy < TH_C + 2; ++yy) {
+    uint2 q[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) q[k] = ld_shared_v2(R[(yy * RW + k) & 7] + (uint32_t)((yy * RW + k) * 128));
+    f32x2 f[4][2];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { f[k][0] = bf2_to_f2<RELU>(q[k].x); f[k][1] = bf2_to_f2<RELU>(q[k].y); }
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky) {
+      const int o = yy - ky;
+      if (o < 0 || o >= TH_C) continue;
+#pragma unroll
+      for (int col = 0; col < 2; ++col) {
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          f32x2 a = (ky == 0) ? fmul2(f[col][c], wr[0][c]) : ffma2(f[col][c], wr[3 * ky][c], acc[o % 3][col][c]);
+          a = ffma2(f[col + 1][c], wr[3 * ky + 1][c], a);
+          acc[o % 3][col][c] = ffma2(f[col + 2][c], wr[3 * ky + 2][c], a);
+        }
+      }
+    }
+    if (yy >= 2) {
+      const int o = yy - 2;
+#pragma unroll
+      for (int col = 0; col < 2; ++col)
+        st_shared_v2(S[(o * TW_C + col) & 7] + (uint32_t)((o * TW_C + col) * 128),
+                     make_uint2(f2_to_bf2(acc[o % 3][col][0]), f2_to_bf2(acc[o % 3][col][1])));
+    }
+  }
+}
+
 // One 64-column chunk of a thread's accumulator row: TMEM -> + shift (from shared memory) -> [ReLU] -> bf16 ->
 // swizzled staging row.  Packed fp32 pairs: one FADD2 per two columns, ReLU folded into the bf16 convert.
 __device__ __forceinline__ void ld_shared_v4f(uint32_t addr, f32x2& a, f32x2& b) {
@@ -385,7 +431,13 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
             const int n = ci >> p.tw_log, x = ci & (TW - 1);
             const uint32_t rp0 = (uint32_t)((n * RH) * RW + x);   // raw pixel (n, yy = 0, xx = x)
             const uint32_t ar0 = (uint32_t)((n * TH) * TW + x);   // A row of output (n, y = 0, x)
-            if (!relu) {
+            if (TH == 8 && TW == 16) {
+              if (!relu) dw_column2_fixed<8, 16, false>(rbase, abase, rp0, ar0, jch, wr);
+              else dw_column2_fixed<8, 16, true>(rbase, abase, rp0, ar0, jch, wr);
+            } else if (TH == 8 && TW == 8) {
+              if (!relu) dw_column2_fixed<8, 8, false>(rbase, abase, rp0, ar0, jch, wr);
+              else dw_column2_fixed<8, 8, true>(rbase, abase, rp0, ar0, jch, wr);
+            } else if (!relu) {
               if (TH == 8) dw_column2<8, false>(rbase, abase, rp0, ar0, RW, TW, jch, wr);
               else if (TH == 4) dw_column2<4, false>(rbase, abase, rp0, ar0, RW, TW, jch, wr);
               else if (TH == 16) dw_column2<16, false>(rbase, abase, rp0, ar0, RW, TW, jch, wr);
