@@ -25,12 +25,14 @@ constexpr int HALO_THREADS = 192;
 constexpr int HTW = 8, HTH = 16;                 // tile: 8 x 16 pixels of one image
 constexpr int MAX_STAGES = 8;
 constexpr int MAX_RAW = 4;
+constexpr int MAX_Z = 4;                          // addend (half-resolution Z) tiles staged by the producer
 constexpr int PITCH = HTW + 2;                    // raw row pitch in pixels = box width of the raw load
 
 struct HaloParams {
   int tiles_x, tiles_y, tiles_b, tiles_n, total_tiles;
   int nslab, Cin;
   int raw_bytes, raw_tx, n_raw, n_stage;
+  int n_z;           // > 0: ring of addend tiles (add_shift == 1): 4 x 8 pixels x 64 channels per 64 output columns
   EpiParams e;
 };
 
@@ -48,7 +50,7 @@ __device__ __forceinline__ uint64_t umma_desc_sw128_ex(uint32_t saddr, uint32_t 
 template <int BN, bool BRES>
 __global__ void __launch_bounds__(HALO_THREADS, 1)
 conv_halo_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constant__ CUtensorMap tmB,
-                 const __grid_constant__ TcOutMaps om, const __grid_constant__ HaloParams p) {
+                 const __grid_constant__ CUtensorMap tmZ, const __grid_constant__ TcOutMaps om, const __grid_constant__ HaloParams p) {
   constexpr int B_TILE_BYTES = BN * KSLAB * 2;
   constexpr int TMEM_COLS = (2 * BN <= 32) ? 32 : 2 * BN;
   extern __shared__ uint8_t smem_raw[];
@@ -57,7 +59,9 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
   const uint32_t b_base = smem_base;
   const uint32_t raw_base = (b_base + n_btiles * B_TILE_BYTES + 1023u) & ~1023u;
   const uint32_t stg_base = raw_base + p.n_raw * p.raw_bytes;
-  const uint32_t bar_base = stg_base + N_STG * STG_BYTES;
+  constexpr int Z_BYTES = (BN >= 64 ? BN / 64 : 1) * 4096;
+  const uint32_t z_base = stg_base + N_STG * STG_BYTES;
+  const uint32_t bar_base = z_base + p.n_z * Z_BYTES;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (MAX_STAGES + s); };
   auto rfull_bar = [&](int s) { return bar_base + 8u * (2 * MAX_STAGES + s); };
@@ -65,7 +69,9 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
   auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * MAX_STAGES + 2 * MAX_RAW + s); };
   auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * MAX_STAGES + 2 * MAX_RAW + 2 + s); };
   const uint32_t bres_bar = bar_base + 8u * (2 * MAX_STAGES + 2 * MAX_RAW + 4);
-  constexpr int TMEM_SLOT = 8 * (2 * MAX_STAGES + 2 * MAX_RAW + 5);
+  auto zfull_bar = [&](int s) { return bar_base + 8u * (2 * MAX_STAGES + 2 * MAX_RAW + 5 + s); };
+  auto zempty_bar = [&](int s) { return bar_base + 8u * (2 * MAX_STAGES + 2 * MAX_RAW + 5 + MAX_Z + s); };
+  constexpr int TMEM_SLOT = 8 * (2 * MAX_STAGES + 2 * MAX_RAW + 5 + 2 * MAX_Z);
   const uint32_t tmem_slot = bar_base + TMEM_SLOT;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
   volatile uint32_t* tmem_slot_gen =
@@ -79,6 +85,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
     for (int s = 0; s < MAX_RAW; ++s) { mbar_init(rfull_bar(s), 1); mbar_init(rempty_bar(s), 1); }
     for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 128); }
     mbar_init(bres_bar, 1);
+    for (int s = 0; s < MAX_Z; ++s) { mbar_init(zfull_bar(s), 1); mbar_init(zempty_bar(s), 128); }
     fence_barrier_init();
     fence_proxy_async();
     tma_prefetch_desc(&tmRaw);
@@ -114,6 +121,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
     const int items = my_tiles * p.nslab;
     int stage = 0; uint32_t phase = 0;
     int ri = 0, rs = 0; uint32_t rphase = 0;       // next raw item to issue
+    int zs = 0; uint32_t zphase = 0;
     // Raw tiles run ahead of the B loads.  With streamed B the look-ahead is n_raw - 2 items, so the slot
     // a raw load waits for was released two items ago and the wait never delays this item's B loads;
     // with resident B the producer has nothing else to do and simply keeps the ring full.
@@ -129,6 +137,20 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
           tma_load_4d(raw_base + rs * p.raw_bytes, &tmRaw, rfull_bar(rs), c * KSLAB, x0 - 1, y0 - 1, b0);
         }
         __syncwarp();
+        if (p.n_z > 0 && ri % p.nslab == 0) {
+          // the tile's addend: Z[b, y0/2 .. +8, x0/2 .. +4, nt*BN .. +BN), long before the epilogue needs it
+          mbar_wait(zempty_bar(zs), zphase ^ 1);
+          if (lane == 0) {
+            int k = ri / p.nslab;
+            int nt, x0, y0, b0;
+            decode((int)blockIdx.x + k * (int)gridDim.x, nt, x0, y0, b0);
+            mbar_expect_tx(zfull_bar(zs), Z_BYTES);
+            for (int cc = 0; cc < Z_BYTES / 4096; ++cc)
+              tma_load_4d(z_base + zs * Z_BYTES + cc * 4096, &tmZ, zfull_bar(zs), nt * BN + cc * 64, x0 >> 1, y0 >> 1, b0);
+          }
+          __syncwarp();
+          if (++zs == p.n_z) { zs = 0; zphase ^= 1; }
+        }
         ++ri;
         if (++rs == p.n_raw) { rs = 0; rphase ^= 1; }
       }
@@ -202,6 +224,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
     const uint32_t sw = (uint32_t)(row & 7);
     const EpiParams& e = p.e;
     int sbuf = 0;
+    int zs = 0; uint32_t zphase = 0;
     for (int it = 0; it < my_tiles; ++it) {
       const int as = it & 1;
       const uint32_t aphase = (it >> 1) & 1;
@@ -210,8 +233,19 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
       const int x = x0 + tx_in, y = y0 + ty_in, b = b0;
       const bool valid = (x < e.W) && (y < e.H);
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
+      uint32_t z_row = 0, zsw = 0;
+      if (p.n_z > 0) {
+        const uint32_t pz = (uint32_t)((ty_in >> 1) * (HTW / 2) + (tx_in >> 1));
+        mbar_wait(zfull_bar(zs), zphase);
+        z_row = z_base + zs * Z_BYTES + pz * 128u;
+        zsw = pz & 7u;
+      }
       tc_epilogue_tile<BN>(e, om, taddr, 0, nt, x0, y0, b0, x, y, b, valid, stg_base, stg_row, sw, leader, sbuf,
-                           tempty_bar(as), tfull_bar(as), aphase, bar_base + 512u);
+                           tempty_bar(as), tfull_bar(as), aphase, bar_base + 512u, z_row, zsw);
+      if (p.n_z > 0) {
+        mbar_arrive(zempty_bar(zs));
+        if (++zs == p.n_z) { zs = 0; zphase ^= 1; }
+      }
     }
     if (leader) tma_store_wait_all();
   }
@@ -221,7 +255,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
   if (warp == 1) tmem_dealloc<TMEM_COLS>(tmem_base);
 }
 
-struct HaloPlan { int BN, n_raw, n_stage, raw_bytes, raw_tx, b_resident, smem; };
+struct HaloPlan { int BN, n_raw, n_stage, raw_bytes, raw_tx, b_resident, n_z, smem; };
 
 int g_halo_mode = -1;
 int halo_mode() {   // 0 off, 1 on (env TMAT_HALO)
@@ -249,23 +283,31 @@ bool plan_halo(const ConvOp& op, int mode, HaloPlan* pl) {
   pl->raw_bytes = (pl->raw_tx + 1023) / 1024 * 1024;
   const int nslab = op.a0_C / KSLAB;
   const int btile = pl->BN * KSLAB * 2;
-  const int budget = 227 * 1024 - 3072 - N_STG * STG_BYTES;
+  // the half-resolution addend of the up path comes through a producer-fed ring instead of a per-thread gather
+  // (only next to resident weights: with streamed weights the ring would throttle the weight loads)
+  const bool z_ok = (op.epi == EPI_STORE && op.add_src && op.add_shift == 1 && op.W % 2 == 0 && op.H % 2 == 0);
   const int tiles_n = op.Npad / pl->BN;
-  for (int n_raw = 3; n_raw >= 2; --n_raw) {
-    int left = budget - n_raw * pl->raw_bytes;
-    if (left < 2 * btile) continue;
-    pl->n_raw = n_raw;
-    if (tiles_n == 1 && 9 * nslab * btile <= left) { pl->b_resident = 1; pl->n_stage = 1; }
-    else { pl->b_resident = 0; pl->n_stage = std::min(MAX_STAGES, left / btile); }
-    int nb = pl->b_resident ? 9 * nslab : pl->n_stage;
-    pl->smem = nb * btile + n_raw * pl->raw_bytes + N_STG * STG_BYTES + 3072;
-    return true;
+  for (int with_z = z_ok ? 1 : 0; with_z >= 0; --with_z) {
+    pl->n_z = with_z ? MAX_Z : 0;
+    const int z_bytes = pl->n_z * (pl->BN >= 64 ? pl->BN / 64 : 1) * 4096;
+    const int budget = 227 * 1024 - 3072 - N_STG * STG_BYTES - z_bytes;
+    for (int n_raw = 3; n_raw >= 2; --n_raw) {
+      int left = budget - n_raw * pl->raw_bytes;
+      if (left < 2 * btile) continue;
+      pl->n_raw = n_raw;
+      if (tiles_n == 1 && 9 * nslab * btile <= left) { pl->b_resident = 1; pl->n_stage = 1; }
+      else { pl->b_resident = 0; pl->n_stage = std::min(MAX_STAGES, left / btile); }
+      if (with_z && !pl->b_resident) continue;
+      int nb = pl->b_resident ? 9 * nslab : pl->n_stage;
+      pl->smem = nb * btile + n_raw * pl->raw_bytes + N_STG * STG_BYTES + z_bytes + 3072;
+      return true;
+    }
   }
   return false;
 }
 
 template <int BN, bool BRES>
-int launch_halo(tmat_ctx* ctx, const CUtensorMap& raw, const CUtensorMap& b, const TcOutMaps& om, const HaloParams& p,
+int launch_halo(tmat_ctx* ctx, const CUtensorMap& raw, const CUtensorMap& b, const CUtensorMap& z, const TcOutMaps& om, const HaloParams& p,
                 int smem, cudaStream_t st) {
   static bool configured = false;
   if (!configured) {
@@ -282,7 +324,7 @@ int launch_halo(tmat_ctx* ctx, const CUtensorMap& raw, const CUtensorMap& b, con
     rec.flops = 2.0 * p.e.B * p.e.H * p.e.W * (double)(p.tiles_n * BN) * (double)(9 * p.Cin);
     CUDA_TRY(cudaEventRecord(rec.a, st));
   }
-  conv_halo_kernel<BN, BRES><<<grid, HALO_THREADS, smem, st>>>(raw, b, om, p);
+  conv_halo_kernel<BN, BRES><<<grid, HALO_THREADS, smem, st>>>(raw, b, z, om, p);
   KERNEL_CHECK(ctx);
   if (ctx->profiling) {
     CUDA_TRY(cudaEventRecord(rec.b, st));
@@ -317,8 +359,9 @@ int conv_run_halo(tmat_ctx* ctx, const ConvOp& op, int mode, cudaStream_t st) {
   p.total_tiles = (int)total;
   p.nslab = op.a0_C / KSLAB; p.Cin = op.a0_C;
   p.raw_bytes = pl.raw_bytes; p.raw_tx = pl.raw_tx; p.n_raw = pl.n_raw; p.n_stage = pl.n_stage;
+  p.n_z = pl.n_z;
   p.e = epi_of(op);
-  CUtensorMap mRaw, mB;
+  CUtensorMap mRaw, mB, mZ;
   TcOutMaps om;
   TMAT_TRY(tc_make_act_map(&mRaw, op.a0, op.B, op.H, op.W, op.a0_C, PITCH, HTH + 2, 1));
   TMAT_TRY(tc_make_weight_map(&mB, op.wmat, op.Npad, op.K, pl.BN));
@@ -330,14 +373,16 @@ int conv_run_halo(tmat_ctx* ctx, const ConvOp& op, int mode, cudaStream_t st) {
   } else {
     om.m[0] = om.m[1] = om.m[2] = om.m[3] = om.m2 = mRaw;
   }
+  if (pl.n_z > 0) TMAT_TRY(tc_make_act_map(&mZ, op.add_src, op.B, op.H / 2, op.W / 2, op.Cout, HTW / 2, HTH / 2, 1));
+  else mZ = mRaw;
   const int key = pl.BN * 2 + (pl.b_resident ? 1 : 0);
   switch (key) {
-    case 128 * 2 + 0: return launch_halo<128, false>(ctx, mRaw, mB, om, p, pl.smem, st);
-    case 128 * 2 + 1: return launch_halo<128, true>(ctx, mRaw, mB, om, p, pl.smem, st);
-    case 64 * 2 + 0: return launch_halo<64, false>(ctx, mRaw, mB, om, p, pl.smem, st);
-    case 64 * 2 + 1: return launch_halo<64, true>(ctx, mRaw, mB, om, p, pl.smem, st);
-    case 16 * 2 + 0: return launch_halo<16, false>(ctx, mRaw, mB, om, p, pl.smem, st);
-    case 16 * 2 + 1: return launch_halo<16, true>(ctx, mRaw, mB, om, p, pl.smem, st);
+    case 128 * 2 + 0: return launch_halo<128, false>(ctx, mRaw, mB, mZ, om, p, pl.smem, st);
+    case 128 * 2 + 1: return launch_halo<128, true>(ctx, mRaw, mB, mZ, om, p, pl.smem, st);
+    case 64 * 2 + 0: return launch_halo<64, false>(ctx, mRaw, mB, mZ, om, p, pl.smem, st);
+    case 64 * 2 + 1: return launch_halo<64, true>(ctx, mRaw, mB, mZ, om, p, pl.smem, st);
+    case 16 * 2 + 0: return launch_halo<16, false>(ctx, mRaw, mB, mZ, om, p, pl.smem, st);
+    case 16 * 2 + 1: return launch_halo<16, true>(ctx, mRaw, mB, mZ, om, p, pl.smem, st);
   }
   return TMAT_ERR_INVALID;
 }

@@ -172,6 +172,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
       const int x = x0 + tx_in, y = y0 + ty_in, b = b0 + tb_in;
       const bool valid = (x < e.W) && (y < e.H) && (b < e.B);
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
+      if (BN >= 64 && e.add_src != nullptr && tile + 2 * (int)gridDim.x < p.total_tiles) {
+        // addend rows of the tile after next -> L2
+        int gn, ntn, x0n, y0n, b0n;
+        decode(tile + 2 * (int)gridDim.x, gn, ntn, x0n, y0n, b0n);
+        tc_prefetch_addend(e, ntn * BN, BN, x0n + tx_in, y0n + ty_in, b0n + tb_in);
+      }
       tc_epilogue_tile<BN>(e, om, taddr, g, nt, x0, y0, b0, x, y, b, valid, stg_base, stg_row, sw, leader, sbuf,
                            tempty_bar(as), tfull_bar(as), aphase, smem_base + L::SHIFT_OFFSET);
     }

@@ -75,6 +75,11 @@ __device__ __forceinline__ void tma_store_wait_read() {
 __device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 // named barrier among the 128 epilogue threads (barrier 0 is __syncthreads)
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+__device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
 __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint4 v) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
@@ -218,6 +223,16 @@ struct TcOutMaps {
 
 namespace tcptx {
 
+// L2 prefetch of the addend row a thread will need for a later tile (columns [col0, col0 + ncols) of pixel
+// (b, y, x)): the gather otherwise waits out a full DRAM latency per tile with nothing else in flight.
+__device__ __forceinline__ void tc_prefetch_addend(const EpiParams& e, int col0, int ncols, int x, int y, int b) {
+  if (e.add_src == nullptr || x >= e.W || y >= e.H || b >= e.B) return;
+  const int s = e.add_shift;
+  const int Ha = (e.H + (1 << s) - 1) >> s, Wa = (e.W + (1 << s) - 1) >> s;
+  const bf16* a = e.add_src + (((int64_t)b * Ha + (y >> s)) * Wa + (x >> s)) * e.Cout + col0;
+  for (int c = 0; c < ncols; c += 64) asm volatile("prefetch.global.L2 [%0];" ::"l"(a + c));
+}
+
 constexpr int N_STG = 2;   // staging tiles of STG_BYTES each at stg_base
 
 // Epilogue of one output tile, executed by the 128 epilogue threads (thread = GEMM row = TMEM lane):
@@ -230,7 +245,9 @@ __device__ __forceinline__ void tc_epilogue_tile(const EpiParams& e, const TcOut
                                                  int x0, int y0, int b0, int x, int y, int b, bool valid,
                                                  uint32_t stg_base, uint32_t stg_row, uint32_t sw, bool leader,
                                                  int& sbuf, uint32_t tempty, uint32_t tfull, uint32_t tphase,
-                                                 uint32_t shift_smem) {
+                                                 uint32_t shift_smem, uint32_t z_row = 0, uint32_t zsw = 0) {
+      // z_row != 0: the addend of this thread's pixel was staged in shared memory by the producer (one
+      // 128-byte-swizzled row of 64 channels per 4096-byte block, block c64 / 64); else it is gathered from e.add_src
       if constexpr (BN >= 64) {
         // this tile's BN shift values -> shared memory (read back as broadcast 16-byte loads below); the
         // hand-over barrier of the first chunk orders the writes, the last barrier of the previous tile the reuse
@@ -240,7 +257,7 @@ __device__ __forceinline__ void tc_epilogue_tile(const EpiParams& e, const TcOut
         }
         const bool dual = (e.out2 != nullptr);
         const bf16* addp = nullptr;
-        if (e.add_src != nullptr && valid) {
+        if (e.add_src != nullptr && valid && z_row == 0) {
           const int s = e.add_shift;
           const int Ha = (e.H + (1 << s) - 1) >> s, Wa = (e.W + (1 << s) - 1) >> s;
           addp = e.add_src + (((int64_t)b * Ha + (y >> s)) * Wa + (x >> s)) * e.Cout;
@@ -253,11 +270,15 @@ __device__ __forceinline__ void tc_epilogue_tile(const EpiParams& e, const TcOut
           // the addend (8 x 16 bytes per thread) is fetched before anything that waits: its L2 latency hides
           // behind the accumulator wait / the staging hand-over
           uint4 av[8];
-          if (addp != nullptr) {
+          if (z_row != 0) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) av[j] = ld_shared_v4(z_row + (uint32_t)(c64 >> 6) * 4096u + ((((uint32_t)j) ^ zsw) << 4));
+          } else if (addp != nullptr) {
             const uint4* ap = reinterpret_cast<const uint4*>(addp + ch0);
 #pragma unroll
             for (int j = 0; j < 8; ++j) av[j] = __ldg(ap + j);
           }
+          const bool has_add = (addp != nullptr) || (z_row != 0);
           if (c64 == 0) {
             mbar_wait(tfull, tphase);
             tc_fence_after();
@@ -282,7 +303,7 @@ __device__ __forceinline__ void tc_epilogue_tile(const EpiParams& e, const TcOut
 #pragma unroll
               for (int i = 0; i < 16; ++i)
                 v[i] = fadd2(pack2(__uint_as_float(rr[2 * i]), __uint_as_float(rr[2 * i + 1])), v[i]);
-              if (addp != nullptr) {
+              if (has_add) {
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                   const uint4 u = av[half * 4 + j];
