@@ -16,62 +16,71 @@ namespace {
 constexpr int STEM_ROWS = 8;
 constexpr int STEM_COLS = 32;
 
-__global__ void __launch_bounds__(256) stem_kernel(StemSrc src, int B, int ws, const float* __restrict__ w,
+__global__ void __launch_bounds__(256, 2) stem_kernel(StemSrc src, int B, int ws, const float* __restrict__ w,
                                                    const float* __restrict__ shift, int C0,
-                                                   bf16* __restrict__ out) {
+                                                   bf16* __restrict__ out, int tiles_x, int tiles_y) {
+  // Persistent blocks walk the (patch, strip) tiles; the input window of the NEXT tile is fetched into
+  // registers before the current tile is computed and lands in the other shared-memory buffer afterwards,
+  // so the global-load latency of the fill hides behind the FFMA2 work.  Weights are loaded once per block.
   constexpr int IR = 2 * STEM_ROWS + 1, IC = 2 * STEM_COLS + 1;
-  __shared__ float tile[IR][IC + 2];
+  constexpr int FILL = (IR * IC + 255) / 256;
+  __shared__ float tile[2][IR][IC + 2];
   const int S = ws >> 1;
-  const int b = blockIdx.z;
-  const int y0 = blockIdx.y * STEM_ROWS, x0 = blockIdx.x * STEM_COLS;
-  {
-    int g = 0, ti = 0, tj = 0;
+  const int total = tiles_x * tiles_y * B;
+  // window of tile t -> tile[buf], asynchronously (cp.async, 4 bytes per element; padding / out-of-range
+  // elements are plain stores of the constant), so no registers are held while the loads are in flight
+  auto fill_async = [&](int t, int buf) {
+    const int b = t / (tiles_x * tiles_y), rem = t - b * (tiles_x * tiles_y);
+    const int y0 = (rem / tiles_x) * STEM_ROWS, x0 = (rem % tiles_x) * STEM_COLS;
     float minval = 0.f;
     const float* pp = nullptr;
-    if (src.use_geom) {
-      const StpGeom& G = src.geom;
-      int p = src.first_patch + b;
-      if (src.patch_list) p = __ldg(src.patch_list + p);
-      int per = G.tiles_per_orient();
-      g = p / per;
-      int t = p - g * per;
-      int tc = G.tile_cols(g);
-      ti = t / tc; tj = t - ti * tc;
-      minval = src.minmax[0];
-    } else {
-      pp = src.patches + (int64_t)b * ws * ws;
-    }
     // the D4 tile map is affine in (i, j): three probes give its coefficients for the whole block
     int r00 = 0, c00 = 0, dri = 0, dci = 0, drj = 0, dcj = 0;
     if (src.use_geom) {
       const StpGeom& G = src.geom;
+      int p = src.first_patch + b;
+      if (src.patch_list) p = __ldg(src.patch_list + p);
+      const int per = G.tiles_per_orient();
+      const int g = p / per;
+      const int tt = p - g * per;
+      const int tc = G.tile_cols(g);
+      const int ti = tt / tc, tj = tt - ti * tc;
+      minval = src.minmax[0];
       int r10, c10, r01, c01;
       d4_rot_to_orig(g, ti * G.step, tj * G.step, G.PM, G.PN, &r00, &c00);
       d4_rot_to_orig(g, ti * G.step + 1, tj * G.step, G.PM, G.PN, &r10, &c10);
       d4_rot_to_orig(g, ti * G.step, tj * G.step + 1, G.PM, G.PN, &r01, &c01);
       dri = r10 - r00; dci = c10 - c00; drj = r01 - r00; dcj = c01 - c00;
+    } else {
+      pp = src.patches + (int64_t)b * ws * ws;
     }
-    // all global loads of the fill are issued before the first shared-memory store (latency overlap)
-    constexpr int FILL = (IR * IC + 255) / 256;
-    float vals[FILL];
 #pragma unroll
     for (int k = 0; k < FILL; ++k) {
       const int idx = threadIdx.x + k * 256;
+      if (idx >= IR * IC) break;
       const int r = idx / IC, c = idx - r * IC;
       const int i = 2 * y0 + r, j = 2 * x0 + c;
-      float v = 0.f;
-      if (idx < IR * IC && i < ws && j < ws)
-        v = src.use_geom ? stp_padded_value(src.img, src.geom, r00 + i * dri + j * drj, c00 + i * dci + j * dcj, minval)
-                         : __ldg(pp + (int64_t)i * ws + j);
-      vals[k] = v;
+      float* dst = &tile[buf][r][c];
+      const float* gp = nullptr;
+      float cv = 0.f;
+      if (i < ws && j < ws) {
+        if (src.use_geom) {
+          const StpGeom& G = src.geom;
+          const int y = r00 + i * dri + j * drj - G.aug, x = c00 + i * dci + j * dcj - G.aug;
+          if (y >= 0 && y < G.H && x >= 0 && x < G.W) gp = src.img + (int64_t)y * G.W + x;
+          else cv = minval;
+        } else {
+          gp = pp + (int64_t)i * ws + j;
+        }
+      }
+      if (gp != nullptr) {
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(gp) : "memory");
+      } else {
+        *dst = cv;
+      }
     }
-#pragma unroll
-    for (int k = 0; k < FILL; ++k) {
-      const int idx = threadIdx.x + k * 256;
-      if (idx < IR * IC) tile[idx / IC][idx % IC] = vals[k];
-    }
-  }
-  __syncthreads();
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
   const int groups = C0 >> 3;                  // 8 when C0 == 64
   const int px_per_pass = blockDim.x / groups;
   const int cg = threadIdx.x % groups;
@@ -85,36 +94,48 @@ __global__ void __launch_bounds__(256) stem_kernel(StemSrc src, int B, int ws, c
   }
 #pragma unroll
   for (int c = 0; c < 4; ++c) sh[c] = pack2(__ldg(shift + cg * 8 + 2 * c), __ldg(shift + cg * 8 + 2 * c + 1));
-  for (int xl = threadIdx.x / groups; xl < STEM_COLS; xl += px_per_pass) {
-    const int x = x0 + xl;
-    if (x >= S) break;
+  int t = blockIdx.x;
+  if (t < total) fill_async(t, 0);
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncthreads();
+  for (int buf = 0; t < total; t += gridDim.x, buf ^= 1) {
+    const int tn = t + gridDim.x;
+    if (tn < total) fill_async(tn, buf ^ 1);
+    const int b = t / (tiles_x * tiles_y), rem = t - b * (tiles_x * tiles_y);
+    const int y0 = (rem / tiles_x) * STEM_ROWS, x0 = (rem % tiles_x) * STEM_COLS;
+    for (int xl = threadIdx.x / groups; xl < STEM_COLS; xl += px_per_pass) {
+      const int x = x0 + xl;
+      if (x >= S) break;
 #pragma unroll
-    for (int r = 0; r < STEM_ROWS; ++r) {
-      const int y = y0 + r;
-      if (y >= S) break;
-      f32x2 acc[4];
+      for (int r = 0; r < STEM_ROWS; ++r) {
+        const int y = y0 + r;
+        if (y >= S) break;
+        f32x2 acc[4];
 #pragma unroll
-      for (int c = 0; c < 4; ++c) acc[c] = sh[c];
+        for (int c = 0; c < 4; ++c) acc[c] = sh[c];
 #pragma unroll
-      for (int ky = 0; ky < 3; ++ky)
+        for (int ky = 0; ky < 3; ++ky)
 #pragma unroll
-        for (int kx = 0; kx < 3; ++kx) {
-          const float v = tile[2 * r + ky][2 * xl + kx];
-          const f32x2 vv = pack2(v, v);
+          for (int kx = 0; kx < 3; ++kx) {
+            const float v = tile[buf][2 * r + ky][2 * xl + kx];
+            const f32x2 vv = pack2(v, v);
 #pragma unroll
-          for (int c = 0; c < 4; ++c) acc[c] = ffma2(vv, wr[ky * 3 + kx][c], acc[c]);
+            for (int c = 0; c < 4; ++c) acc[c] = ffma2(vv, wr[ky * 3 + kx][c], acc[c]);
+          }
+        uint4 o;
+        uint32_t* ow = reinterpret_cast<uint32_t*>(&o);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          float lo, hi;
+          unpack2(acc[c], lo, hi);
+          __nv_bfloat162 h = __floats2bfloat162_rn(fmaxf(lo, 0.f), fmaxf(hi, 0.f));
+          ow[c] = *reinterpret_cast<uint32_t*>(&h);
         }
-      uint4 o;
-      uint32_t* ow = reinterpret_cast<uint32_t*>(&o);
-#pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        float lo, hi;
-        unpack2(acc[c], lo, hi);
-        __nv_bfloat162 h = __floats2bfloat162_rn(fmaxf(lo, 0.f), fmaxf(hi, 0.f));
-        ow[c] = *reinterpret_cast<uint32_t*>(&h);
+        *reinterpret_cast<uint4*>(out + (((int64_t)b * S + y) * S + x) * C0 + cg * 8) = o;
       }
-      *reinterpret_cast<uint4*>(out + (((int64_t)b * S + y) * S + x) * C0 + cg * 8) = o;
     }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
   }
 }
 
@@ -250,8 +271,11 @@ int stem_run(tmat_ctx* ctx, const StemSrc& src, int B, int ws, const float* w, c
   int S = ws / 2;
   TMAT_REQUIRE(C0 % 8 == 0 && C0 / 8 <= 256 && 256 % (C0 / 8) == 0, "stem: unsupported channel count %d", C0);
   TMAT_REQUIRE(B <= 65535, "stem: batch %d too large", B);
-  dim3 grid(cdiv(S, STEM_COLS), cdiv(S, STEM_ROWS), B);
-  stem_kernel<<<grid, 256, 0, st>>>(src, B, ws, w, shift, C0, out);
+  const int tiles_x = cdiv(S, STEM_COLS), tiles_y = cdiv(S, STEM_ROWS);
+  const int64_t total = (int64_t)tiles_x * tiles_y * B;
+  TMAT_REQUIRE(total < (1ll << 31), "stem: too many tiles");
+  const int grid = (int)std::min<int64_t>(total, 2 * (int64_t)ctx->sm_count);   // persistent, two blocks per SM
+  stem_kernel<<<grid, 256, 0, st>>>(src, B, ws, w, shift, C0, out, tiles_x, tiles_y);
   KERNEL_CHECK(ctx);
   return TMAT_OK;
 }
