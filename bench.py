@@ -244,6 +244,20 @@ def main():
         patches = 8 * n_r * n_r
         algo_flops_step = flops_patch * patches
         tc_ms_step = tc_ms / args.steps
+        # DRAM bytes of the GEMM kernels over one step, from the committed ncu pass of this same command
+        # (profiles/r1_dram_traffic.json; a profiler number, so it is read, not re-measured here)
+        traffic, traffic_note = None, "no committed ncu DRAM capture for this size"
+        try:
+            if args.size == 2048:
+                with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_dram_traffic.json")) as f:
+                    tr = json.load(f)
+                traffic = tr["gemm_dram_bytes_per_step"]
+                traffic_note = ("dram__bytes_read.sum + dram__bytes_write.sum summed over the %d GEMM launches of one step "
+                                "(ncu, cache-control none); all %d launches of the step: %.1f GB" %
+                                (tr["gemm_launches"], tr["launches_in_step"], tr["all_dram_bytes_per_step"] / 1e9))
+        except (OSError, KeyError, ValueError):
+            pass
+
         achieved = algo_flops_step / (tc_ms_step / 1e3) / 1e12
         line = {
             "metric": METRIC, "value": value, "unit": "MP/s", "n_gpus": world, "steps": args.steps, "warmup": warmup,
@@ -256,7 +270,7 @@ def main():
                              "256-patch chunk) exceeds the 126 MB L2; no explicit flush",
                        "parallelism": f"image-sharded x{world}"},
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": pk["bf16_sustained"], "unit": "TFLOP/s",
-                         "frac": achieved / pk["bf16_sustained"], "traffic": None,
+                         "frac": achieved / pk["bf16_sustained"], "traffic": traffic, "traffic_note": traffic_note,
                          "kernel": "the tcgen05 GEMM kernels of the UNet: conv_tc_kernel (implicit-GEMM convolution), "
                                    "conv_dwpw_kernel (fused SeparableConv2D), conv_halo_kernel (3x3, haloed tile)",
                          "algorithmic_flops_per_step": algo_flops_step, "executed_flops_per_step": tc_flops / args.steps,

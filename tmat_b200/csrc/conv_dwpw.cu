@@ -2,14 +2,15 @@
 // as ONE tcgen05 kernel.  The depthwise result never goes to HBM: it is produced straight into the
 // 128-byte-swizzled A-operand stage of the pointwise GEMM.
 //
-//   warp 0       TMA producer: per (tile, 64-channel slab) one haloed raw input tile
-//                (64 ch x (TW+2) x (TH+2) x TN, zero-filled outside the image = 'same' padding) into the raw
-//                ring, and the slab's pointwise weights [BN x 64] into the B half of a GEMM stage
-//   warps 6..13  depthwise: each thread owns 4 channels of one tile column and slides down the rows
-//                (one 8-byte ld.shared per tap column per row, 36 fp32 weights in registers, fp32
-//                accumulate), rounds to bf16 and writes the A half of the stage in UMMA layout
+//   warp 0       raw-tile producer: per (tile, 64-channel slab) one haloed raw input tile
+//                (64 ch x (TW+2) x (TH+2) x TN, zero-filled outside the image = 'same' padding) into the raw ring
+//   warp 14      weight producer: all pointwise slabs once (resident, <= 64 KB) or a two-slab ring
+//   warps 6..13  depthwise, two groups of four warps taking alternate items: each thread owns 4 channels of two
+//                adjacent tile columns and slides down the rows (8-byte ld.shared per raw pixel, 36 fp32 weights
+//                in registers, FFMA2 on fp32 pairs), rounds to bf16 and writes the A ring in UMMA layout
 //   warp 1       MMA issuer (tcgen05.mma M=128, N=BN, K=16 x4 per slab), accumulator double-buffered in TMEM
-//   warps 2..5   epilogue: tcgen05.ld -> +shift, ReLU -> bf16 -> swizzled staging tile -> TMA store
+//   warps 2..5   epilogue: tcgen05.ld -> +shift (staged in smem), ReLU in the convert -> bf16 -> swizzled staging
+//                tile -> TMA store
 #include "tc_ptx.cuh"
 #include <algorithm>
 
@@ -63,42 +64,10 @@ __device__ __forceinline__ f32x2 bf2_to_f2(uint32_t x) {
   return pack2(__uint_as_float(x << 16), __uint_as_float(x & 0xffff0000u));
 }
 
-// One tile column of the depthwise 3x3 for a thread's 4 channels, RH = TH_C + 2 raw rows, fully unrolled:
-// raw row yy is tap row ky of output row yy - ky; the three live accumulators rotate by compile-time index.
-template <int TH_C, bool RELU>
-__device__ __forceinline__ void dw_column(uint32_t rbase_sub, uint32_t abase_sub, uint32_t rp0, uint32_t ar0,
-                                          uint32_t RW, uint32_t TW, uint32_t jch, const f32x2 (&wr)[9][2]) {
-  f32x2 acc[3][2];
-  auto raw_addr = [&](uint32_t rp) { return rbase_sub + (rp << 7) + ((jch ^ (rp & 7u)) << 4); };
-#pragma unroll
-  for (int yy = 0; yy < TH_C + 2; ++yy) {
-    const uint32_t rp = rp0 + (uint32_t)yy * RW;
-    const uint2 cl = ld_shared_v2(raw_addr(rp)), cc = ld_shared_v2(raw_addr(rp + 1)), cr = ld_shared_v2(raw_addr(rp + 2));
-    const f32x2 f[3][2] = {{bf2_to_f2<RELU>(cl.x), bf2_to_f2<RELU>(cl.y)},
-                           {bf2_to_f2<RELU>(cc.x), bf2_to_f2<RELU>(cc.y)},
-                           {bf2_to_f2<RELU>(cr.x), bf2_to_f2<RELU>(cr.y)}};
-#pragma unroll
-    for (int ky = 0; ky < 3; ++ky) {
-      const int o = yy - ky;                     // output row this raw row feeds through tap row ky
-      if (o < 0 || o >= TH_C) continue;
-#pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        f32x2 a = (ky == 0) ? fmul2(f[0][c], wr[0][c]) : ffma2(f[0][c], wr[3 * ky][c], acc[o % 3][c]);
-        a = ffma2(f[1][c], wr[3 * ky + 1][c], a);
-        acc[o % 3][c] = ffma2(f[2][c], wr[3 * ky + 2][c], a);
-      }
-    }
-    if (yy >= 2) {
-      const int o = yy - 2;
-      const uint32_t ar = ar0 + (uint32_t)o * TW;
-      st_shared_v2(abase_sub + (ar << 7) + ((jch ^ (ar & 7u)) << 4),
-                   make_uint2(f2_to_bf2(acc[o % 3][0]), f2_to_bf2(acc[o % 3][1])));
-    }
-  }
-}
-
-// Two adjacent tile columns (x even, x + 1) per thread: the four raw pixels x .. x+3 of a row are loaded and
-// unpacked once and feed both columns, so the per-output cost of ld.shared + bf16 unpack drops from 3 to 2.
+// Depthwise 3x3 of two adjacent tile columns (x even, x + 1) for a thread's 4 channels, RH = TH_C + 2 raw rows,
+// fully unrolled: raw row yy is tap row ky of output row yy - ky; the three live accumulators rotate by
+// compile-time index.  The four raw pixels x .. x+3 of a row are loaded and unpacked once and feed both columns,
+// so the per-output cost of ld.shared + bf16 unpack is 2 instead of 3.
 template <int TH_C, bool RELU>
 __device__ __forceinline__ void dw_column2(uint32_t rbase_sub, uint32_t abase_sub, uint32_t rp0, uint32_t ar0,
                                            uint32_t RW, uint32_t TW, uint32_t jch, const f32x2 (&wr)[9][2]) {
@@ -496,7 +465,9 @@ bool plan_dwpw(int B, int S, int C, int N, DwpwPlan* pl) {
   const int b_bytes = pl->BN * KSLAB * 2;
   const int nk = C / KSLAB;
   static const int raw_max = [] { const char* v = getenv("TMAT_DW_RAW"); int r = v ? atoi(v) : MAX_RAW; return r < 2 ? 2 : (r > MAX_RAW ? MAX_RAW : r); }();
-  static const int raw_want = [] { const char* v = getenv("TMAT_DW_RAW_WANT"); int r = v ? atoi(v) : 5; return r < 2 ? 2 : r; }();
+  // three slots (two in work, one in flight) are enough: depths 2..6 measured the same, and the options below
+  // that buy more slots cost the second staging buffer, which the epilogue does wait for
+  constexpr int raw_want = 3;
   pl->b_resident = (N == pl->BN && nk * b_bytes <= 64 * 1024 && nk <= MAX_B) ? 1 : 0;
   pl->n_b = pl->b_resident ? nk : 2;
   const int budget = 227 * 1024 - TAIL_BYTES - pl->n_b * b_bytes;
