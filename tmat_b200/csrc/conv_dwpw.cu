@@ -186,7 +186,8 @@ __global__ void __launch_bounds__(DW_THREADS, 1)
 conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ DwpwParams p) {
   constexpr int B_BYTES = BN * KSLAB * 2;
-  constexpr int TMEM_COLS = 2 * BN;
+  constexpr int N_ACC = (BN <= 128) ? 4 : 2;      // accumulator buffers: all 512 TMEM columns
+  constexpr int TMEM_COLS = N_ACC * BN < 32 ? 32 : N_ACC * BN;
   extern __shared__ uint8_t smem_raw[];
   // [A ring | B ring or resident slabs | raw ring | store staging | barriers]
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -201,8 +202,8 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
   auto rfull_bar = [&](int s) { return bar_base + 8u * (2 * MAX_A + 2 * MAX_B + s); };
   auto rempty_bar = [&](int s) { return bar_base + 8u * (2 * MAX_A + 2 * MAX_B + MAX_RAW + s); };
   auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * MAX_A + 2 * MAX_B + 2 * MAX_RAW + s); };
-  auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * MAX_A + 2 * MAX_B + 2 * MAX_RAW + 2 + s); };
-  constexpr int TMEM_SLOT = 8 * (2 * MAX_A + 2 * MAX_B + 2 * MAX_RAW + 4);
+  auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * MAX_A + 2 * MAX_B + 2 * MAX_RAW + 4 + s); };
+  constexpr int TMEM_SLOT = 8 * (2 * MAX_A + 2 * MAX_B + 2 * MAX_RAW + 8);
   constexpr int ISSUED_SLOT = TMEM_SLOT + 8;
   const uint32_t shift_base = bar_base + BAR_BYTES;      // the layer's N shift values (fp32), staged once
   const uint32_t tmem_slot = bar_base + TMEM_SLOT;
@@ -222,7 +223,7 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
     for (int s = 0; s < p.n_b; ++s) { mbar_init(bfull_bar(s), 1); mbar_init(bempty_bar(s), 1); }
     for (int s = 0; s < p.n_raw; ++s) { mbar_init(rfull_bar(s), 1); mbar_init(rempty_bar(s), DW_GROUP_WARPS); }
     *issued = 0;
-    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 128); }
+    for (int s = 0; s < N_ACC; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 128); }
     fence_barrier_init();
     fence_proxy_async();
     tma_prefetch_desc(&tmRaw);
@@ -302,8 +303,8 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
         for (int ks = 0; ks < p.nk; ++ks) mbar_wait(bfull_bar(ks), 0);
       }
       for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
-        const int as = it & 1;
-        const uint32_t aphase = (it >> 1) & 1;
+        const int as = it % N_ACC;
+        const uint32_t aphase = (it / N_ACC) & 1;
         mbar_wait(tempty_bar(as), aphase ^ 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + as * BN;
@@ -337,8 +338,8 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
     int sbuf = 0;
     int it = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
-      const int as = it & 1;
-      const uint32_t aphase = (it >> 1) & 1;
+      const int as = it % N_ACC;
+      const uint32_t aphase = (it / N_ACC) & 1;
       int nt, x0, y0, b0;
       decode(tile, nt, x0, y0, b0);
       mbar_wait(tfull_bar(as), aphase);
