@@ -61,6 +61,11 @@ int  tmat_ctx_sync(tmat_ctx* ctx);
 /* number of kernels of this library launched through `ctx` since creation (bench.py's
  * gpu_launches claim is read from here). */
 int  tmat_ctx_launch_count(tmat_ctx* ctx, int64_t* out);
+/* Page-locked host buffer for *_host arguments (cudaHostAlloc): a copy to or from it runs at full PCIe
+ * speed and is truly asynchronous.  The reference allocates its result with numpy (pageable,
+ * smooth_tiled_predictions.py:244-262); the Python mirror hands out results backed by these buffers. */
+int  tmat_host_alloc(int64_t bytes, void** out);
+int  tmat_host_free(void* p);
 
 /* Per-launch CUDA-event timing of the tensor-core convolution kernel (bench.py's roofline leg).
  * collect: out3[0] = summed kernel time in ms since the last collect, out3[1] = launches,

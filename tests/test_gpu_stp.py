@@ -75,3 +75,28 @@ def test_row_strips_are_bit_identical_to_the_full_prediction(world):
     assert np.array_equal(np.concatenate(parts), full)
     n_total = len(patches_for_rows(200, 150, ws, 2, 0, 200))
     assert n_total < n_eval < 2 * n_total
+
+
+@pytest.mark.gpu
+def test_pinned_result_buffers_are_recycled_and_writable():
+    """Results of the all-device path live in cudaHostAlloc memory (tmat_host_alloc): a dropped result's
+    buffer is handed out again, a live one never is, and the arrays behave like ordinary numpy arrays."""
+    import gc
+    from tmat_b200 import _ffi
+    a = _ffi.pinned_empty((64, 48), np.float64)
+    assert a.shape == (64, 48) and a.dtype == np.float64 and a.flags["C_CONTIGUOUS"] and a.flags["WRITEABLE"]
+    a[:] = 3.5
+    addr_a = a.ctypes.data
+    b = _ffi.pinned_empty((64, 48), np.float64)
+    assert b.ctypes.data != addr_a          # a is still alive
+    view = a[10:20]
+    del a
+    gc.collect()
+    c = _ffi.pinned_empty((64, 48), np.float64)
+    assert c.ctypes.data != addr_a          # the view keeps a's buffer alive
+    assert float(view[0, 0]) == 3.5
+    del view
+    gc.collect()
+    d = _ffi.pinned_empty((64, 48), np.float64)
+    assert d.ctypes.data == addr_a          # recycled
+    assert _ffi.pinned_empty((0, 4), np.float32).size == 0

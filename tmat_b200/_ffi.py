@@ -7,6 +7,7 @@ missing it is built in-tree (nvcc); if no sm_100 device is present every compute
 import ctypes as C
 import os
 import threading
+import weakref
 
 import numpy as np
 
@@ -43,6 +44,8 @@ SIGNATURES = {
     "tmat_ctx_destroy": [_vp],
     "tmat_ctx_sync": [_vp],
     "tmat_ctx_launch_count": [_vp, C.POINTER(_i64)],
+    "tmat_host_alloc": [_i64, C.POINTER(_vp)],
+    "tmat_host_free": [_vp],
     "tmat_ctx_profile_enable": [_vp, _i],
     "tmat_ctx_profile_collect": [_vp, C.POINTER(C.c_double)],
     "tmat_zproj_dev": [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp],
@@ -173,6 +176,67 @@ def default_context():
         ctx = Context(dev)
         _tls.ctx = ctx
     return ctx
+
+
+# ---- page-locked result buffers ---------------------------------------------------------------------------
+# Results handed back to the caller are numpy arrays over cudaHostAlloc memory, so the device->host copy of a
+# result runs at PCIe speed.  Buffers return to a small per-size pool when the array (and every view of it) is
+# garbage-collected; beyond _PINNED_LIVE_CAP live bytes the result is an ordinary pageable array.
+_PINNED_LIVE_CAP = 1 << 30
+_pinned_lock = threading.Lock()
+_pinned_pool = {}        # nbytes -> [address, ...]
+_pinned_live = 0
+
+
+def _pinned_release(addr, nbytes):
+    global _pinned_live
+    with _pinned_lock:
+        _pinned_live -= nbytes
+        free = _pinned_pool.setdefault(nbytes, [])
+        if len(free) < 2:
+            free.append(addr)
+            return
+    try:
+        lib().tmat_host_free(_vp(addr))
+    except Exception:
+        pass
+
+
+def pinned_empty(shape, dtype):
+    """np.empty(shape, dtype) over page-locked memory (pageable when the live cap is reached)."""
+    global _pinned_live
+    dtype = np.dtype(dtype)
+    nbytes = int(np.prod(shape)) * dtype.itemsize
+    if nbytes == 0:
+        return np.empty(shape, dtype)
+    addr = None
+    with _pinned_lock:
+        free = _pinned_pool.get(nbytes)
+        if free:
+            addr = free.pop()
+        elif _pinned_live + nbytes > _PINNED_LIVE_CAP:
+            return np.empty(shape, dtype)
+        _pinned_live += nbytes
+    if addr is None:
+        p = _vp()
+        try:
+            check(lib().tmat_host_alloc(nbytes, C.byref(p)))
+        except Exception:
+            with _pinned_lock:
+                _pinned_live -= nbytes
+            raise
+        addr = p.value
+        # a caller that rebinds `res = f(...)` in a loop holds the previous result while the next one is
+        # produced: keep one spare of a size the first time it is seen, so the second call does not page-lock
+        spare = _vp()
+        with _pinned_lock:
+            want_spare = not _pinned_pool.get(nbytes) and _pinned_live + nbytes <= _PINNED_LIVE_CAP
+        if want_spare and lib().tmat_host_alloc(nbytes, C.byref(spare)) == 0:
+            with _pinned_lock:
+                _pinned_pool.setdefault(nbytes, []).append(spare.value)
+    buf = (C.c_char * nbytes).from_address(addr)
+    weakref.finalize(buf, _pinned_release, addr, nbytes)
+    return np.frombuffer(buf, dtype=dtype).reshape(shape)
 
 
 def ptr(a):

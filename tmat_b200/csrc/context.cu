@@ -66,6 +66,18 @@ extern "C" int tmat_ctx_destroy(tmat_ctx* ctx) {
   return TMAT_OK;
 }
 
+extern "C" int tmat_host_alloc(int64_t bytes, void** out) {
+  TMAT_REQUIRE(out && bytes > 0, "tmat_host_alloc: bad argument");
+  *out = nullptr;
+  CUDA_TRY(cudaHostAlloc(out, (size_t)bytes, cudaHostAllocDefault));
+  return TMAT_OK;
+}
+
+extern "C" int tmat_host_free(void* p) {
+  if (p) CUDA_TRY(cudaFreeHost(p));
+  return TMAT_OK;
+}
+
 extern "C" int tmat_ctx_sync(tmat_ctx* ctx) {
   TMAT_REQUIRE(ctx, "tmat_ctx_sync: ctx is NULL");
   CUDA_TRY(cudaSetDevice(ctx->device));
