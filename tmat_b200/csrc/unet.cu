@@ -103,12 +103,23 @@ int upload_bf16(tmat_unet* net, const std::vector<float>& h, bf16** d) {
 int parity_lowtap(int par, int kk) { int v = par + kk - 1; return v < 0 ? -1 : v / 2; }
 
 // Column groups of the parity GEMM: enough parities are merged into one group (sharing the union of
-// their taps, with zero weight blocks) to give the MMA an N of 256 where Cout allows it.
+// their taps, with zero weight blocks) to give the MMA an N of 128 .. 256.
 struct ParityPlan { int ngroups, gtaps, ppg; int8_t dy[CONV_MAX_GROUPS][9], dx[CONV_MAX_GROUPS][9]; };
 ParityPlan parity_plan(int f) {
   ParityPlan pl;
   memset(&pl, 0, sizeof(pl));
-  pl.ngroups = f >= 256 ? 4 : (f >= 128 ? 2 : 1);
+  // f = 64: two groups of N = 128 over 6 taps beat one group of N = 256 over 9 (a third fewer MMA cycles,
+  // measured -0.8 ms per 2048^2 image); f = 128: two groups of N = 256 and four of N = 128 measure the same
+  pl.ngroups = f >= 256 ? 4 : (f >= 64 ? 2 : 1);
+  {
+    // experiment hook: TMAT_PAR_GROUPS="<groups for f < 128>,<groups for 128 <= f < 256>"
+    static const char* env = getenv("TMAT_PAR_GROUPS");
+    int g64 = 0, g128 = 0;
+    if (env && sscanf(env, "%d,%d", &g64, &g128) == 2) {
+      if (f >= 64 && f < 128 && (g64 == 1 || g64 == 2 || g64 == 4)) pl.ngroups = g64;
+      if (f >= 128 && f < 256 && (g128 == 1 || g128 == 2 || g128 == 4)) pl.ngroups = g128;
+    }
+  }
   pl.ppg = 4 / pl.ngroups;
   for (int g = 0; g < pl.ngroups; ++g) {
     int n = 0;
