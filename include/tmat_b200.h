@@ -165,6 +165,10 @@ int tmat_debug_set_halo_mode(int mode);
  * vs the unfused pair (depthwise kernel, CUDA-core GEMM) on random data. */
 int tmat_debug_dwpw_selftest(tmat_ctx* ctx, int B, int S, int C, int N, int relu_in, int relu_out,
                              uint64_t seed, double* max_abs_diff, double* max_abs_ref);
+/* the same kernel with MaxPool2D(3, strides=2, 'same') (models.py:139) folded into its epilogue, against the unfused
+ * kernel followed by the stand-alone pooling kernel: max_abs_diff must be 0. */
+int tmat_debug_dwpw_pool_selftest(tmat_ctx* ctx, int B, int S, int C, int N, int relu_in, int relu_out,
+                                  uint64_t seed, double* max_abs_diff, double* max_abs_ref);
 /* FLOPs (2*MAC of every convolution as written in models.py:110-171) of one patch */
 int tmat_unet_flops_per_patch(const tmat_unet_desc* desc, double* flops);
 

@@ -60,6 +60,25 @@ def test_fused_separable_conv_matches_unfused(case):
     assert d.value <= m.value * 2 ** -7, (d.value, m.value)
 
 
+DWPW_POOL_CASES = [
+    # B, S, C, N, relu_in, relu_out: the second SeparableConv2D of the three down blocks (+ odd batch, ReLU variants)
+    (1, 160, 128, 128, 0, 0), (3, 80, 256, 256, 0, 0), (4, 40, 512, 512, 0, 0), (6, 40, 256, 512, 1, 1),
+    (2, 32, 64, 128, 0, 1), (2, 16, 64, 64, 1, 0), (8, 8, 64, 64, 0, 0),
+]
+
+
+@pytest.mark.parametrize("case", DWPW_POOL_CASES)
+def test_fused_maxpool_epilogue_is_bit_identical(case):
+    """conv_dwpw_kernel with MaxPool2D(3, 2, same) in its epilogue (max-reducing TMA stores of per-tile boxes) vs
+    the same kernel + maxpool_kernel (models.py:134-139)."""
+    from tmat_b200 import _ffi
+    ctx = _ffi.default_context()
+    d, m = C.c_double(), C.c_double()
+    _ffi.check(_ffi.lib().tmat_debug_dwpw_pool_selftest(ctx.handle, *case, 13, C.byref(d), C.byref(m)))
+    assert m.value > 0.1
+    assert d.value == 0.0, (d.value, m.value)
+
+
 @pytest.mark.parametrize("fc,ws,n,impl", [((8, 16, 32, 64), 64, 2, "simt"), ((64, 128, 256, 512), 64, 3, "tc"),
                                           ((64, 128, 256, 512), 96, 5, "tc"), ((64, 64, 128, 128), 64, 2, "tc")])
 def test_unet_forward_vs_oracle(fc, ws, n, impl):

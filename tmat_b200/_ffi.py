@@ -72,6 +72,8 @@ SIGNATURES = {
     "tmat_debug_set_halo_mode": [_i],
     "tmat_debug_dwpw_selftest": [_vp, _i, _i, _i, _i, _i, _i, C.c_uint64, C.POINTER(C.c_double),
                                  C.POINTER(C.c_double)],
+    "tmat_debug_dwpw_pool_selftest": [_vp, _i, _i, _i, _i, _i, _i, C.c_uint64, C.POINTER(C.c_double),
+                                      C.POINTER(C.c_double)],
     "tmat_unet_flops_per_patch": [C.POINTER(UnetDesc), C.POINTER(C.c_double)],
     "tmat_gmm2_threshold_dev": [_vp, _vp, _i64, C.c_double, _vp, _vp, _vp],
     "tmat_gmm2_threshold_host": [_vp, _vp, _i64, C.c_double, _vp, _vp],

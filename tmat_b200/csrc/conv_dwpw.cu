@@ -37,6 +37,8 @@ struct DwpwParams {
   int raw_tx;        // bytes one raw TMA load delivers
   int n_raw, n_a, n_b, n_stg;
   int b_resident;    // all nk weight slabs stay in smem for the whole kernel (n_b == nk, tiles_n == 1)
+  int pool;          // epilogue max-pools (3, stride 2, same) the tile and max-reduces it into the pooled tensor
+  int pw, ph;        // pooled box of a tile: (TW/2 + 1) x (TH/2 + 1), origin (x0/2 - 1, y0/2 - 1)
   const float* dw;   // [9][C]
   EpiParams e;
 };
@@ -181,10 +183,95 @@ __device__ __forceinline__ void dwpw_epi_chunk(uint32_t taddr, uint32_t shift_ad
   }
 }
 
+__device__ __forceinline__ uint32_t bf2_max(uint32_t a, uint32_t b) {
+  uint32_t d;
+  asm("max.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+  return d;
+}
+
+constexpr int POOL_BUF_BYTES = STG_BYTES / 2;      // two pooled boxes share the second staging tile
+constexpr int POOL_MAX_ROWS = POOL_BUF_BYTES / 128;
+
+// MaxPool2D(3, strides=2, 'same') of one staged 64-channel tile (models.py:139; pads 0 before / 1 after, padding
+// excluded).  Pooled pixel (k, l) of the tile's box covers tile rows 2k-2 .. 2k and columns 2l-2 .. 2l clipped to the
+// tile: rows/columns k = 0, l = 0 and the last ones are partial and are completed by the neighbouring tiles' boxes
+// through the max-reducing store.  Eight consecutive threads take the eight 16-byte chunks of one pooled pixel, so
+// every quarter-warp reads and writes one whole 128-byte swizzle row.
+// (ox, oy) = 1 for tiles on the left / top image edge: their box starts one pooled pixel later (a TMA store must not
+// start at coordinate -1) and its last column / row, which then belongs to the next tile, stays at -inf.
+__device__ __forceinline__ void dwpw_pool_tile(uint32_t stg, uint32_t pbuf, int et, int TW, int TH, int TN, int PW,
+                                               int PH, int ox, int oy) {
+  const uint32_t c = (uint32_t)(et & 7);
+  const int rows = TN * PH * PW;
+  for (int pr = et >> 3; pr < rows; pr += 16) {
+    const int n = pr / (PH * PW), r2 = pr - n * (PH * PW);
+    const int kb = r2 / PW;
+    const int k = kb + oy, l = r2 - kb * PW + ox;
+    const int ylo = max(2 * k - 2, 0), yhi = min(2 * k, TH - 1);
+    const int xlo = max(2 * l - 2, 0), xhi = min(2 * l, TW - 1);
+    uint4 m = make_uint4(0xff80ff80u, 0xff80ff80u, 0xff80ff80u, 0xff80ff80u);   // -inf
+    for (int yy = ylo; yy <= yhi; ++yy) {
+      for (int xx = xlo; xx <= xhi; ++xx) {
+        const uint32_t srow = (uint32_t)((n * TH + yy) * TW + xx);
+        const uint4 v = ld_shared_v4(stg + srow * 128u + ((c ^ (srow & 7u)) << 4));
+        m.x = bf2_max(m.x, v.x); m.y = bf2_max(m.y, v.y); m.z = bf2_max(m.z, v.z); m.w = bf2_max(m.w, v.w);
+      }
+    }
+    st_shared_v4(pbuf + (uint32_t)pr * 128u + ((c ^ ((uint32_t)pr & 7u)) << 4), m);
+  }
+}
+
+// The same for a compile-time tile shape (TW a multiple of 8, so a staged pixel's swizzle phase is its column & 7):
+// the nine taps of a pooled pixel are clamped into the tile -- a duplicate tap does not change a maximum -- so all nine
+// 16-byte loads are independent and in flight together.
+template <int TWL, int THL>
+__device__ __forceinline__ void dwpw_pool_tile_fixed(uint32_t stg, uint32_t pbuf, int et, int ox, int oy) {
+  constexpr int TW = 1 << TWL, TH = 1 << THL, TN = 128 / (TW * TH), PW = TW / 2 + 1, PH = TH / 2 + 1;
+  constexpr int ROWS = TN * PH * PW;
+  static_assert(TW % 8 == 0 && ROWS <= POOL_MAX_ROWS, "tile shape");
+  const uint32_t c = (uint32_t)(et & 7);
+#pragma unroll
+  for (int j = 0; j < (ROWS + 15) / 16; ++j) {
+    const int pr = (et >> 3) + 16 * j;
+    if (pr < ROWS) {
+      const int n = pr / (PH * PW), r2 = pr - n * (PH * PW);
+      const int kb = r2 / PW, lb = r2 - kb * PW;
+      const int k = kb + oy, l = lb + ox;
+      uint4 m = make_uint4(0xff80ff80u, 0xff80ff80u, 0xff80ff80u, 0xff80ff80u);   // -inf
+      if (k <= TH / 2 && l <= TW / 2) {
+        uint32_t yo[3], xo[3];
+#pragma unroll
+        for (int d = 0; d < 3; ++d) {
+          const int y = min(max(2 * k - 2 + d, 0), TH - 1), x = min(max(2 * l - 2 + d, 0), TW - 1);
+          yo[d] = stg + (uint32_t)((n * TH + y) * TW) * 128u;
+          xo[d] = (uint32_t)x * 128u + ((c ^ ((uint32_t)x & 7u)) << 4);
+        }
+        uint4 v[9];
+#pragma unroll
+        for (int dy = 0; dy < 3; ++dy)
+#pragma unroll
+          for (int dx = 0; dx < 3; ++dx) v[3 * dy + dx] = ld_shared_v4(yo[dy] + xo[dx]);
+        m = v[0];
+#pragma unroll
+        for (int i = 1; i < 9; ++i) {
+          m.x = bf2_max(m.x, v[i].x); m.y = bf2_max(m.y, v[i].y); m.z = bf2_max(m.z, v[i].z); m.w = bf2_max(m.w, v[i].w);
+        }
+      }
+      st_shared_v4(pbuf + (uint32_t)pr * 128u + ((c ^ ((uint32_t)pr & 7u)) << 4), m);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) fill_neg_inf_bf16(uint4* __restrict__ p, int64_t n16) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n16) p[i] = make_uint4(0xff80ff80u, 0xff80ff80u, 0xff80ff80u, 0xff80ff80u);
+}
+
 template <int BN>
 __global__ void __launch_bounds__(DW_THREADS, 1)
 conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constant__ CUtensorMap tmB,
-                 const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ DwpwParams p) {
+                 const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmPool,
+                 const __grid_constant__ DwpwParams p) {
   constexpr int B_BYTES = BN * KSLAB * 2;
   constexpr int N_ACC = (BN <= 128) ? 4 : 2;      // accumulator buffers: all 512 TMEM columns
   constexpr int TMEM_COLS = N_ACC * BN < 32 ? 32 : N_ACC * BN;
@@ -229,6 +316,7 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
     tma_prefetch_desc(&tmRaw);
     tma_prefetch_desc(&tmB);
     tma_prefetch_desc(&tmOut);
+    tma_prefetch_desc(&tmPool);
   }
   {
     float* shift_gen = reinterpret_cast<float*>(smem_gen + (bar_base - smem_base) + BAR_BYTES);
@@ -345,6 +433,35 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
       mbar_wait(tfull_bar(as), aphase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
+      if (p.pool) {
+        // fused MaxPool: the 64-channel tile is staged (generic proxy only), pooled into one of two small boxes and
+        // max-reduced into the pooled tensor; the full-resolution tensor is never written
+#pragma unroll 1
+        for (int c64 = 0; c64 < BN; c64 += 64) {
+          const int ch0 = nt * BN + c64;
+          const uint32_t pbuf = stg_base + STG_BYTES + (uint32_t)sbuf * POOL_BUF_BYTES;
+          if (leader) tma_store_wait_read<1>();            // the reduce that last read this pooled box is done
+          if (e.relu) dwpw_epi_chunk<true>(taddr + c64, shift_base + (uint32_t)ch0 * 4u, stg_base + stg_row, sw);
+          else dwpw_epi_chunk<false>(taddr + c64, shift_base + (uint32_t)ch0 * 4u, stg_base + stg_row, sw);
+          if (c64 + 64 >= BN) {
+            tc_fence_before();
+            mbar_arrive(tempty_bar(as));
+          }
+          epi_bar_sync();                                  // tile staged; leader's wait is behind everyone
+          const int ox = (x0 == 0), oy = (y0 == 0);
+          if (p.tw_log == 4 && p.th_log == 3) dwpw_pool_tile_fixed<4, 3>(stg_base, pbuf, row, ox, oy);
+          else if (p.tw_log == 3 && p.th_log == 3) dwpw_pool_tile_fixed<3, 3>(stg_base, pbuf, row, ox, oy);
+          else dwpw_pool_tile(stg_base, pbuf, row, TW, TH, TN, p.pw, p.ph, ox, oy);
+          fence_proxy_async();
+          epi_bar_sync();                                  // box complete, staging tile free again
+          if (leader) {
+            tma_reduce_max_4d(&tmPool, pbuf, ch0, (x0 >> 1) - 1 + ox, (y0 >> 1) - 1 + oy, b0);
+            tma_store_commit();
+          }
+          sbuf ^= 1;
+        }
+        continue;
+      }
 #pragma unroll 1
       for (int c64 = 0; c64 < BN; c64 += 64) {
         const int ch0 = nt * BN + c64;
@@ -488,7 +605,7 @@ bool plan_dwpw(int B, int S, int C, int N, DwpwPlan* pl) {
 
 template <int BN>
 int launch_dwpw(tmat_ctx* ctx, const CUtensorMap& raw, const CUtensorMap& b, const CUtensorMap& out,
-                const DwpwParams& p, int smem, cudaStream_t st) {
+                const CUtensorMap& pool, const DwpwParams& p, int smem, cudaStream_t st) {
   static int configured = 0;
   if (configured < smem) {
     CUDA_TRY(cudaFuncSetAttribute(conv_dwpw_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
@@ -504,7 +621,7 @@ int launch_dwpw(tmat_ctx* ctx, const CUtensorMap& raw, const CUtensorMap& b, con
     rec.flops = 2.0 * p.e.B * p.e.H * p.e.W * ((double)(p.tiles_n * BN) * (double)p.C + 9.0 * p.C);
     CUDA_TRY(cudaEventRecord(rec.a, st));
   }
-  conv_dwpw_kernel<BN><<<grid, DW_THREADS, smem, st>>>(raw, b, out, p);
+  conv_dwpw_kernel<BN><<<grid, DW_THREADS, smem, st>>>(raw, b, out, pool, p);
   KERNEL_CHECK(ctx);
   if (ctx->profiling) {
     CUDA_TRY(cudaEventRecord(rec.b, st));
@@ -520,10 +637,25 @@ bool dwpw_supported(int B, int S, int C, int N) {
   return plan_dwpw(B, S, C, N, &pl);
 }
 
+// The pooled epilogue needs whole even tiles inside the image, both staging tiles and a pooled box that fits half of one.
+static bool pool_plan_ok(const DwpwPlan& pl, int S) {
+  const int TW = 1 << pl.tw_log, TH = 1 << pl.th_log, TN = 1 << pl.tn_log;
+  return S % 2 == 0 && TW >= 2 && TH >= 2 && S % TW == 0 && S % TH == 0 && pl.n_stg == 2 &&
+         TN * (TW / 2 + 1) * (TH / 2 + 1) <= POOL_MAX_ROWS;
+}
+
+bool dwpw_pool_supported(int B, int S, int C, int N) {
+  DwpwPlan pl;
+  return plan_dwpw(B, S, C, N, &pl) && pool_plan_ok(pl, S);
+}
+
 int dwpw_run(tmat_ctx* ctx, const bf16* in, int B, int S, int C, const float* dw, int relu_in, const bf16* wmat,
-             const float* shift, int N, int relu_out, bf16* out, cudaStream_t st) {
+             const float* shift, int N, int relu_out, bf16* out, cudaStream_t st, bf16* pool_out) {
   DwpwPlan pl;
   TMAT_REQUIRE(plan_dwpw(B, S, C, N, &pl), "dwpw: shape (B=%d, S=%d, C=%d, N=%d) not supported", B, S, C, N);
+  TMAT_REQUIRE(pool_out == nullptr || pool_plan_ok(pl, S), "dwpw: pooled epilogue not supported for (B=%d, S=%d, C=%d, N=%d)",
+               B, S, C, N);
+  TMAT_REQUIRE(out != nullptr || pool_out != nullptr, "dwpw: no output");
   const int TW = 1 << pl.tw_log, TH = 1 << pl.th_log, TN = 1 << pl.tn_log;
   DwpwParams p;
   memset(&p, 0, sizeof(p));
@@ -539,14 +671,25 @@ int dwpw_run(tmat_ctx* ctx, const bf16* in, int B, int S, int C, const float* dw
   memset(&p.e, 0, sizeof(p.e));
   p.e.mode = EPI_STORE; p.e.relu = relu_out; p.e.B = B; p.e.H = S; p.e.W = S; p.e.Cout = N; p.e.ppg = 1;
   p.e.shift = shift; p.e.out = out;
-  CUtensorMap mRaw, mB, mOut;
+  CUtensorMap mRaw, mB, mOut, mPool;
   TMAT_TRY(tc_make_act_map(&mRaw, in, B, S, S, C, TW + 2, TH + 2, TN));
   TMAT_TRY(tc_make_weight_map(&mB, wmat, N, C, pl.BN));
-  TMAT_TRY(tc_make_act_map(&mOut, out, B, S, S, N, TW, TH, TN));
+  if (pool_out != nullptr) {
+    // the pooled tensor starts at -inf: every tile max-reduces its (partial) box into it
+    p.pool = 1; p.pw = TW / 2 + 1; p.ph = TH / 2 + 1;
+    const int64_t n16 = (int64_t)B * (S / 2) * (S / 2) * N / 8;
+    fill_neg_inf_bf16<<<(unsigned)cdiv64(n16, 256), 256, 0, st>>>(reinterpret_cast<uint4*>(pool_out), n16);
+    KERNEL_CHECK(ctx);
+    TMAT_TRY(tc_make_act_map(&mPool, pool_out, B, S / 2, S / 2, N, p.pw, p.ph, TN));
+    mOut = mPool;
+  } else {
+    TMAT_TRY(tc_make_act_map(&mOut, out, B, S, S, N, TW, TH, TN));
+    mPool = mOut;
+  }
   switch (pl.BN) {
-    case 256: return launch_dwpw<256>(ctx, mRaw, mB, mOut, p, pl.smem, st);
-    case 128: return launch_dwpw<128>(ctx, mRaw, mB, mOut, p, pl.smem, st);
-    case 64: return launch_dwpw<64>(ctx, mRaw, mB, mOut, p, pl.smem, st);
+    case 256: return launch_dwpw<256>(ctx, mRaw, mB, mOut, mPool, p, pl.smem, st);
+    case 128: return launch_dwpw<128>(ctx, mRaw, mB, mOut, mPool, p, pl.smem, st);
+    case 64: return launch_dwpw<64>(ctx, mRaw, mB, mOut, mPool, p, pl.smem, st);
   }
   return TMAT_ERR_INVALID;
 }

@@ -286,9 +286,13 @@ __global__ void __launch_bounds__(256) flip_small(const int* __restrict__ parent
   if (i < n && parent[i] >= 0 && area[parent[i]] < min_size) mask[i] = set_to;
 }
 __global__ void __launch_bounds__(256) area_image_kernel(const int* __restrict__ parent, const unsigned int* __restrict__ area,
-                                                         int64_t n, double* __restrict__ out) {
+                                                         int64_t n, int prop, double* __restrict__ out) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) out[i] = parent[i] >= 0 ? (double)area[parent[i]] : 0.0;
+  if (i >= n) return;
+  double a = parent[i] >= 0 ? (double)area[parent[i]] : 0.0;
+  // skimage regionprops: equivalent_diameter_area = sqrt(4 * area / pi), IEEE operations in that order
+  if (prop == 1) a = __dsqrt_rn(__ddiv_rn(4.0 * a, 3.141592653589793));
+  out[i] = a;
 }
 
 }  // namespace
@@ -614,9 +618,20 @@ extern "C" int tmat_remove_small_islands_host(tmat_ctx* ctx, const uint8_t* mask
   });
 }
 
-// transforms.py:291-303 with prop = 'area': label (full connectivity) and paint each component's area
+// transforms.py:291-303 with prop = 'area' (0) or 'equivalent_diameter_area' (1): label (full connectivity) and paint
+// each component's value
+extern "C" int tmat_region_prop_image_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W, int prop,
+                                           double* out_host);
 extern "C" int tmat_area_image_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W, double* out_host) {
-  TMAT_REQUIRE(ctx && mask_host && out_host && H >= 1 && W >= 1, "tmat_area_image: bad argument");
+  return tmat_region_prop_image_host(ctx, mask_host, H, W, 0, out_host);
+}
+extern "C" int tmat_region_prop_image_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W, int prop,
+                                           double* out_host) {
+  TMAT_REQUIRE(ctx && mask_host && out_host && H >= 1 && W >= 1, "tmat_region_prop_image: bad argument");
+  if (prop != 0 && prop != 1) {
+    tmat_set_error("tmat_region_prop_image: only area (0) and equivalent_diameter_area (1) are built");
+    return TMAT_ERR_UNSUPPORTED;
+  }
   TMAT_TRY(arena_reset(ctx));
   size_t n = (size_t)H * W;
   uint8_t* d_in;
@@ -632,7 +647,7 @@ extern "C" int tmat_area_image_host(tmat_ctx* ctx, const uint8_t* mask_host, int
   CUDA_TRY(cudaMemsetAsync(area, 0, n * 4, 0));
   root_area<<<grid1d((int64_t)n), 256>>>(parent, (int64_t)n, area);
   KERNEL_CHECK(ctx);
-  area_image_kernel<<<grid1d((int64_t)n), 256>>>(parent, area, (int64_t)n, d_out);
+  area_image_kernel<<<grid1d((int64_t)n), 256>>>(parent, area, (int64_t)n, prop, d_out);
   KERNEL_CHECK(ctx);
   CUDA_TRY(cudaMemcpyAsync(out_host, d_out, n * 8, cudaMemcpyDeviceToHost, 0));
   CUDA_TRY(cudaStreamSynchronize(0));

@@ -363,15 +363,19 @@ int unet_forward(tmat_ctx* ctx, tmat_unet* net, const StemSrc& src, int B, float
       TMAT_TRY(arena_get(ctx, px * D.cin, &d1));
       TMAT_TRY(arena_get(ctx, px * D.f, &d2));
     }
+    // MaxPool folded into the second SeparableConv2D's epilogue: its full-resolution output is never stored
+    static const bool no_fuse_pool = getenv("TMAT_NO_FUSE_POOL") != nullptr;
+    const bool fuse_pool = fused && !no_fuse_pool && !net->keep_taps && dwpw_pool_supported(B, S, D.f, D.f);
     TMAT_TRY(arena_get(ctx, px * D.f, &a1));
-    TMAT_TRY(arena_get(ctx, px * D.f, &b2));
+    if (!fuse_pool) TMAT_TRY(arena_get(ctx, px * D.f, &b2));
+    else b2 = nullptr;
     TMAT_TRY(arena_get(ctx, px / 4 * D.f, &pooled));
     TMAT_TRY(arena_get(ctx, px / 4 * D.f, &out));
     if (i == 2) TMAT_TRY(arena_get(ctx, px / 4 * D.f, &outr));
     if (fused) {
       // SeparableConv2D as one kernel each: [ReLU] -> depthwise -> pointwise + BN [+ ReLU]
       TMAT_TRY(dwpw_run(ctx, P, B, S, D.cin, D.dw1, i != 0, D.pw1, D.sh1, D.f, 1, a1, st));
-      TMAT_TRY(dwpw_run(ctx, a1, B, S, D.f, D.dw2, 0, D.pw2, D.sh2, D.f, 0, b2, st));
+      TMAT_TRY(dwpw_run(ctx, a1, B, S, D.f, D.dw2, 0, D.pw2, D.sh2, D.f, 0, b2, st, fuse_pool ? pooled : nullptr));
     } else {
       TMAT_TRY(dwconv_run(ctx, P, B, S, D.cin, D.dw1, i != 0, d1, nullptr, st));
       ConvOp op;
@@ -387,9 +391,9 @@ int unet_forward(tmat_ctx* ctx, tmat_unet* net, const StemSrc& src, int B, float
       TMAT_TRY(run_op(ctx, net, op2, st));
     }
     record(net, (std::string("down") + std::to_string(i) + ".r1").c_str(), a1, B, S, S, D.f);
-    record(net, (std::string("down") + std::to_string(i) + ".b2").c_str(), b2, B, S, S, D.f);
+    if (b2) record(net, (std::string("down") + std::to_string(i) + ".b2").c_str(), b2, B, S, S, D.f);
     // MaxPool(3, 2, same)(b2) + residual 1x1 stride-2 conv of the block input
-    TMAT_TRY(maxpool_run(ctx, b2, B, S, D.f, pooled, st));
+    if (!fuse_pool) TMAT_TRY(maxpool_run(ctx, b2, B, S, D.f, pooled, st));
     ConvOp op3;
     op3.name = "down.res"; op3.a0 = P; op3.a0_C = D.cin; op3.a0_stride = 2; op3.B = B; op3.H = S / 2; op3.W = S / 2;
     set_tap1x1(op3);
@@ -886,6 +890,41 @@ extern "C" int tmat_debug_conv_selftest(tmat_ctx* ctx, int B, int H, int W, int 
     max_abs_diff_kernel<bf16><<<256, 256>>>(o1, o2, (int64_t)out_elems, stats);
     if (dual) max_abs_diff_kernel<bf16><<<256, 256>>>(r1, r2, (int64_t)out_elems, stats);
   }
+  float h[2];
+  CUDA_TRY(cudaMemcpy(h, stats, 8, cudaMemcpyDeviceToHost));
+  *max_abs_diff = h[0];
+  *max_abs_ref = h[1];
+  return TMAT_OK;
+}
+
+// Fused SeparableConv2D with the pooled epilogue vs the same kernel followed by maxpool_kernel: bit-identical.
+extern "C" int tmat_debug_dwpw_pool_selftest(tmat_ctx* ctx, int B, int S, int C, int N, int relu_in, int relu_out,
+                                             uint64_t seed, double* max_abs_diff, double* max_abs_ref) {
+  TMAT_REQUIRE(ctx && max_abs_diff && max_abs_ref, "tmat_debug_dwpw_pool_selftest: NULL argument");
+  TMAT_REQUIRE(dwpw_pool_supported(B, S, C, N), "tmat_debug_dwpw_pool_selftest: shape not supported by the pooled epilogue");
+  TMAT_TRY(arena_reset(ctx));
+  size_t px = (size_t)B * S * S;
+  bf16 *in, *w, *full, *p1, *p2;
+  float *dw, *shift, *stats;
+  TMAT_TRY(arena_get(ctx, px * C, &in));
+  TMAT_TRY(arena_get(ctx, (size_t)N * C, &w));
+  TMAT_TRY(arena_get(ctx, px * N, &full));
+  TMAT_TRY(arena_get(ctx, px / 4 * N, &p1));
+  TMAT_TRY(arena_get(ctx, px / 4 * N, &p2));
+  TMAT_TRY(arena_get(ctx, (size_t)9 * C, &dw));
+  TMAT_TRY(arena_get(ctx, (size_t)N, &shift));
+  TMAT_TRY(arena_get(ctx, 2, &stats));
+  fill_random_bf16<<<(unsigned)cdiv64(px * C, 256), 256>>>(in, (int64_t)(px * C), seed + 1, 1.f);
+  fill_random_bf16<<<(unsigned)cdiv64((int64_t)N * C, 256), 256>>>(w, (int64_t)N * C, seed + 2, 1.f / sqrtf((float)C));
+  fill_random_f32<<<cdiv(9 * C, 256), 256>>>(dw, 9 * C, seed + 3, 0.5f);
+  fill_random_f32<<<cdiv(N, 256), 256>>>(shift, N, seed + 4, 0.5f);
+  CUDA_TRY(cudaMemsetAsync(stats, 0, 8, 0));
+  CUDA_TRY(cudaMemsetAsync(p1, 0xff, px / 4 * N * 2, 0));
+  CUDA_TRY(cudaMemsetAsync(p2, 0x7f, px / 4 * N * 2, 0));
+  TMAT_TRY(dwpw_run(ctx, in, B, S, C, dw, relu_in, w, shift, N, relu_out, full, 0));
+  TMAT_TRY(maxpool_run(ctx, full, B, S, N, p1, 0));
+  TMAT_TRY(dwpw_run(ctx, in, B, S, C, dw, relu_in, w, shift, N, relu_out, nullptr, 0, p2));
+  max_abs_diff_kernel<bf16><<<256, 256>>>(p1, p2, (int64_t)(px / 4 * N), stats);
   float h[2];
   CUDA_TRY(cudaMemcpy(h, stats, 8, cudaMemcpyDeviceToHost));
   *max_abs_diff = h[0];

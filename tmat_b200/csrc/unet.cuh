@@ -122,10 +122,13 @@ int dwconv_run(tmat_ctx* ctx, const bf16* in, int B, int S, int C, const float* 
 int maxpool_run(tmat_ctx* ctx, const bf16* in, int B, int S, int C, bf16* out, cudaStream_t st);
 
 // Fused SeparableConv2D on the tcgen05 path (conv_dwpw.cu): out = [relu](BN(pointwise(depthwise([relu](in)))))
+// pool_out != nullptr: the epilogue applies MaxPool2D(3, strides=2, 'same') (models.py:139) and leaves only the pooled
+// tensor (B, S/2, S/2, N) in pool_out -- `out` is not written (bit-identical to dwpw_run + maxpool_run).
 bool dwpw_supported(int B, int S, int C, int N);
+bool dwpw_pool_supported(int B, int S, int C, int N);
 int dwpw_run(tmat_ctx* ctx, const bf16* in, int B, int S, int C, const float* dw /*[9][C]*/, int relu_in,
              const bf16* wmat /*[N][C], BN scale folded*/, const float* shift, int N, int relu_out, bf16* out,
-             cudaStream_t st);
+             cudaStream_t st, bf16* pool_out = nullptr);
 
 // 3x3 convolution with the haloed A tile loaded once per tile (conv_halo.cu); conv_run_tc dispatches to it
 // for single-group 3x3 ops with N <= 128 (and the head) when conv_halo_supported().
