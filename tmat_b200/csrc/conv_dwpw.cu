@@ -2,15 +2,22 @@
 // as ONE tcgen05 kernel.  The depthwise result never goes to HBM: it is produced straight into the
 // 128-byte-swizzled A-operand stage of the pointwise GEMM.
 //
-//   warp 0       raw-tile producer: per (tile, 64-channel slab) one haloed raw input tile
-//                (64 ch x (TW+2) x (TH+2) x TN, zero-filled outside the image = 'same' padding) into the raw ring
-//   warp 14      weight producer: all pointwise slabs once (resident, <= 64 KB) or a two-slab ring
-//   warps 6..13  depthwise, two groups of four warps taking alternate items: each thread owns 4 channels of two
-//                adjacent tile columns and slides down the rows (8-byte ld.shared per raw pixel, 36 fp32 weights
-//                in registers, FFMA2 on fp32 pairs), rounds to bf16 and writes the A ring in UMMA layout
-//   warp 1       MMA issuer (tcgen05.mma M=128, N=BN, K=16 x4 per slab), accumulator double-buffered in TMEM
-//   warps 2..5   epilogue: tcgen05.ld -> +shift (staged in smem), ReLU in the convert -> bf16 -> swizzled staging
-//                tile -> TMA store
+// Five warpgroups (20 warps); roles are warpgroup-aligned so that setmaxnreg can move registers between them
+// (launch: 96 per thread = 61440 per CTA, and a CTA can only re-distribute what it was launched with: warpgroup 0
+// keeps 40, the epilogue warpgroups stay at 96, the depthwise ones grow to 120 -- 60416 in total):
+//   warp 0        raw-tile producer: per (tile, 64-channel slab) one haloed raw input tile
+//                 (64 ch x (TW+2) x (TH+2) x TN, zero-filled outside the image = 'same' padding) into the raw ring
+//   warp 1        MMA issuer (tcgen05.mma M=128, N=BN, K=16 x4 per slab), accumulators in all 512 TMEM columns
+//   warp 2        weight producer: all pointwise slabs once (resident, <= 64 KB) or a two-slab ring
+//   warps 4..11   epilogue, two warpgroups taking alternate tiles (ncu: the single epilogue warpgroup was busy all
+//                 the time with one dependent instruction stream per scheduler while the MMA warp waited for a free
+//                 accumulator 60-70 % of its time and the depthwise warps for a free A stage 45 %): tcgen05.ld ->
+//                 +shift (staged in smem), ReLU in the convert -> bf16 -> swizzled staging tile -> TMA store, or
+//                 -> 3x3/2 max-pool of the staged tile -> TMA max-reduce.  Each warpgroup has its own staging
+//                 buffers, named barrier and store leader.
+//   warps 12..19  depthwise, two groups of four warps taking alternate items: each thread owns 4 channels of two
+//                 adjacent tile columns and slides down the rows (8-byte ld.shared per raw pixel, 36 fp32 weights
+//                 in registers, FFMA2 on fp32 pairs), rounds to bf16 and writes the A ring in UMMA layout
 #include "tc_ptx.cuh"
 #include <algorithm>
 
@@ -18,8 +25,11 @@ using namespace tcptx;
 
 namespace {
 
-constexpr int DW_THREADS = 480;     // 15 warps
-constexpr int DW_GROUP_WARPS = 4;    // depthwise warps 6..13: two groups of four, each owning every other (tile, slab) item
+constexpr int DW_THREADS = 640;     // 20 warps = 5 warpgroups
+constexpr int DW_GROUP_WARPS = 4;    // depthwise warps 12..19: two groups of four, each owning every other (tile, slab) item
+constexpr int WARP_RAW = 0, WARP_MMA = 1, WARP_WEIGHTS = 2, WARP_EPI0 = 4, WARP_DW0 = 12;
+constexpr int REGS_LIGHT = 40, REGS_EPI = 96, REGS_DW = 120;
+static_assert(128 * REGS_LIGHT + 256 * REGS_EPI + 256 * REGS_DW <= DW_THREADS * 96, "register budget of the CTA");
 constexpr int MAX_A = 4;             // A (depthwise output) ring
 constexpr int MAX_B = 8;             // pointwise-weight slabs: ring entries, or all nk slabs when resident
 constexpr int MAX_RAW = 8;           // raw haloed input tiles
@@ -35,11 +45,14 @@ struct DwpwParams {
   int relu_in;
   int raw_bytes;     // one raw ring slot (1024-aligned)
   int raw_tx;        // bytes one raw TMA load delivers
-  int n_raw, n_a, n_b, n_stg;
+  int n_raw, n_a, n_b;
   int b_resident;    // all nk weight slabs stay in smem for the whole kernel (n_b == nk, tiles_n == 1)
   int pool;          // epilogue max-pools (3, stride 2, same) the tile and max-reduces it into the pooled tensor
   int pw, ph;        // pooled box of a tile: (TW/2 + 1) x (TH/2 + 1), origin (x0/2 - 1, y0/2 - 1)
-  int epi_w0, dw_w0; // first epilogue warp (4 warps) and first depthwise warp (8 warps)
+  int n_epi;         // epilogue warpgroups in use (2, or 1 when shared memory has no room for a second set of buffers)
+  int stg_wg_bytes;  // staging bytes of one epilogue warpgroup
+  int spw;           // store staging tiles per epilogue warpgroup (plain epilogue)
+  int npb;           // pooled boxes per epilogue warpgroup (pooled epilogue)
   const float* dw;   // [9][C]
   EpiParams e;
 };
@@ -300,7 +313,7 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
   const uint32_t b_base = smem_base + p.n_a * A_STAGE_BYTES;
   const uint32_t raw_base = b_base + p.n_b * B_BYTES;
   const uint32_t stg_base = raw_base + p.n_raw * p.raw_bytes;
-  const uint32_t bar_base = stg_base + p.n_stg * STG_BYTES;
+  const uint32_t bar_base = stg_base + p.n_epi * p.stg_wg_bytes;
   auto afull_bar = [&](int s) { return bar_base + 8u * s; };
   auto aempty_bar = [&](int s) { return bar_base + 8u * (MAX_A + s); };
   auto bfull_bar = [&](int s) { return bar_base + 8u * (2 * MAX_A + s); };
@@ -341,7 +354,7 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
     float* shift_gen = reinterpret_cast<float*>(smem_gen + (bar_base - smem_base) + BAR_BYTES);
     for (int i = threadIdx.x; i < p.e.Cout; i += DW_THREADS) shift_gen[i] = __ldg(p.e.shift + i);
   }
-  if (warp == 1) tmem_alloc<TMEM_COLS>(tmem_slot);
+  if (warp == WARP_MMA) tmem_alloc<TMEM_COLS>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -357,7 +370,11 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
     x0 = tx << p.tw_log; y0 = ty << p.th_log; b0 = tb << p.tn_log;
   };
 
-  if (warp == 0) {
+  // registers follow the work: warpgroup 0 (three single-warp roles) gives its registers up, the epilogue and
+  // depthwise warpgroups grow (setmaxnreg sits at the head of each warpgroup's own branch)
+  if (warp < 4) {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(REGS_LIGHT));
+  if (warp == WARP_RAW) {
     // ================= raw-tile producer =================
     // Only the raw ring gates this warp (the weight slabs have their own producer), so it runs as far ahead of
     // the depthwise groups as the ring allows: n_raw - 2 haloed tiles in flight while two are being worked on.
@@ -376,7 +393,7 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
         if (++rs == p.n_raw) { rs = 0; rphase ^= 1; }
       }
     }
-  } else if (warp == 14) {
+  } else if (warp == WARP_WEIGHTS) {
     // ================= pointwise-weight producer =================
     if (p.b_resident) {
       if (lane == 0) {
@@ -400,7 +417,7 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
         }
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == WARP_MMA) {
     // ================= MMA issuer (warp-convergent loop, one elected lane issues) =================
     {
       constexpr uint32_t idesc = umma_idesc<BN>();
@@ -434,11 +451,17 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
       }
     }
     __syncwarp();
-  } else if (warp >= p.epi_w0 && warp < p.epi_w0 + 4) {
-    // ================= epilogue (four warps; TMEM lane quadrant = warp & 3) =================
+  }
+  } else if (warp < WARP_DW0) {
+    // ================= epilogue (two warpgroups on alternate tiles; TMEM lane quadrant = warp & 3) =================
+    static_assert(REGS_EPI == 96, "the epilogue warpgroups keep the launch allocation");
+    const int ewg = (warp - WARP_EPI0) >> 2;
+    const uint32_t bar_id = 1u + (uint32_t)ewg;
+    auto epi_bar_sync = [&]() { asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory"); };
+    const uint32_t stg_wg = stg_base + (uint32_t)(ewg * p.stg_wg_bytes);
     const int q = warp & 3;
     const int row = q * 32 + lane;
-    const bool leader = (threadIdx.x == p.epi_w0 * 32);
+    const bool leader = (threadIdx.x == (WARP_EPI0 + 4 * ewg) * 32);
     const uint32_t stg_row = (uint32_t)row * 128u;
     const uint32_t sw = (uint32_t)(row & 7);
     const EpiParams& e = p.e;
@@ -449,6 +472,7 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
     PoolOfs pofs;
     int pofs_ox = -1, pofs_oy = -1;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+      if (ewg >= p.n_epi || (p.n_epi == 2 && (it & 1) != ewg)) continue;
       const int as = it % N_ACC;
       const uint32_t aphase = (it / N_ACC) & 1;
       int nt, x0, y0, b0;
@@ -461,40 +485,40 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
         // max-reduced into the pooled tensor; the full-resolution tensor is never written
         const int ox = (x0 == 0), oy = (y0 == 0);
         if (pool_fixed && (ox != pofs_ox || oy != pofs_oy)) {
-          if (p.tw_log == 4) pool_offsets_fixed<4, 3>(stg_base, row, ox, oy, pofs);
-          else pool_offsets_fixed<3, 3>(stg_base, row, ox, oy, pofs);
+          if (p.tw_log == 4) pool_offsets_fixed<4, 3>(stg_wg, row, ox, oy, pofs);
+          else pool_offsets_fixed<3, 3>(stg_wg, row, ox, oy, pofs);
           pofs_ox = ox; pofs_oy = oy;
         }
 #pragma unroll 1
         for (int c64 = 0; c64 < BN; c64 += 64) {
           const int ch0 = nt * BN + c64;
-          const uint32_t pbuf = stg_base + STG_BYTES + (uint32_t)sbuf * POOL_BUF_BYTES;
-          if (leader) tma_store_wait_read<1>();            // the reduce that last read this pooled box is done
-          if (e.relu) dwpw_epi_chunk<true>(taddr + c64, shift_base + (uint32_t)ch0 * 4u, stg_base + stg_row, sw);
-          else dwpw_epi_chunk<false>(taddr + c64, shift_base + (uint32_t)ch0 * 4u, stg_base + stg_row, sw);
+          const uint32_t pbuf = stg_wg + STG_BYTES + (uint32_t)sbuf * POOL_BUF_BYTES;
+          if (leader) { if (p.npb == 2) tma_store_wait_read<1>(); else tma_store_wait_read<0>(); }   // the reduce that last read this pooled box is done
+          if (e.relu) dwpw_epi_chunk<true>(taddr + c64, shift_base + (uint32_t)ch0 * 4u, stg_wg + stg_row, sw);
+          else dwpw_epi_chunk<false>(taddr + c64, shift_base + (uint32_t)ch0 * 4u, stg_wg + stg_row, sw);
           if (c64 + 64 >= BN) {
             tc_fence_before();
             mbar_arrive(tempty_bar(as));
           }
           epi_bar_sync();                                  // tile staged; leader's wait is behind everyone
           if (pool_fixed) pool_apply(pbuf, pofs);
-          else dwpw_pool_tile(stg_base, pbuf, row, TW, TH, TN, p.pw, p.ph, ox, oy);
+          else dwpw_pool_tile(stg_wg, pbuf, row, TW, TH, TN, p.pw, p.ph, ox, oy);
           fence_proxy_async();
           epi_bar_sync();                                  // box complete, staging tile free again
           if (leader) {
             tma_reduce_max_4d(&tmPool, pbuf, ch0, (x0 >> 1) - 1 + ox, (y0 >> 1) - 1 + oy, b0);
             tma_store_commit();
           }
-          sbuf ^= 1;
+          if (p.npb == 2) sbuf ^= 1;
         }
         continue;
       }
 #pragma unroll 1
       for (int c64 = 0; c64 < BN; c64 += 64) {
         const int ch0 = nt * BN + c64;
-        if (leader) { if (p.n_stg == 2) tma_store_wait_read<1>(); else tma_store_wait_read<0>(); }
+        if (leader) { if (p.spw == 2) tma_store_wait_read<1>(); else tma_store_wait_read<0>(); }
         epi_bar_sync();
-        const uint32_t buf = stg_base + sbuf * STG_BYTES;
+        const uint32_t buf = stg_wg + sbuf * STG_BYTES;
         if (e.relu) dwpw_epi_chunk<true>(taddr + c64, shift_base + (uint32_t)ch0 * 4u, buf + stg_row, sw);
         else dwpw_epi_chunk<false>(taddr + c64, shift_base + (uint32_t)ch0 * 4u, buf + stg_row, sw);
         if (c64 + 64 >= BN) {
@@ -507,13 +531,14 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
           tma_store_4d(&tmOut, buf, ch0, x0, y0, b0);
           tma_store_commit();
         }
-        if (p.n_stg == 2) sbuf ^= 1;
+        if (p.spw == 2) sbuf ^= 1;
       }
     }
     if (leader) tma_store_wait_all();
   } else {
-    // ================= depthwise (eight warps) =================
-    const int t = threadIdx.x - p.dw_w0 * 32;   // 0..255
+    // ================= depthwise (warps 12..19) =================
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(REGS_DW));
+    const int t = threadIdx.x - WARP_DW0 * 32;   // 0..255
     const int grp = t >> 7;                 // group 0 takes even items, group 1 odd items
     const int tg = t & 127;
     const int h = tg & 15;                  // 4-channel group within the 64-channel slab
@@ -578,14 +603,15 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc<TMEM_COLS>(tmem_base);
+  if (warp == WARP_MMA) tmem_dealloc<TMEM_COLS>(tmem_base);
 }
 
 struct DwpwPlan {
-  int tw_log, th_log, tn_log, BN, n_raw, n_a, n_b, n_stg, b_resident, raw_bytes, raw_tx, smem;
+  int tw_log, th_log, tn_log, BN, n_raw, n_a, n_b, b_resident, raw_bytes, raw_tx, smem;
+  int n_epi, stg_wg_bytes, spw, npb;
 };
 
-bool plan_dwpw(int B, int S, int C, int N, DwpwPlan* pl) {
+bool plan_dwpw(int B, int S, int C, int N, bool pool, DwpwPlan* pl) {
   if (C % KSLAB != 0 || N % 64 != 0 || C / KSLAB > 64 || N > MAX_N) return false;
   tc_choose_tile(B, S, S, &pl->tw_log, &pl->th_log, &pl->tn_log);
   {
@@ -616,17 +642,26 @@ bool plan_dwpw(int B, int S, int C, int N, DwpwPlan* pl) {
   pl->b_resident = (N == pl->BN && nk * b_bytes <= 64 * 1024 && nk <= MAX_B) ? 1 : 0;
   pl->n_b = pl->b_resident ? nk : 2;
   const int budget = 227 * 1024 - TAIL_BYTES - pl->n_b * b_bytes;
-  // first option (in order of preference) that reaches raw_want slots, else the one with the most slots
-  int best_raw = 0;
-  const int opts[4][2] = {{3, 2}, {3, 1}, {2, 2}, {2, 1}};     // {n_a, n_stg}
-  for (int o = 0; o < 4; ++o) {
-    int n_raw = (budget - opts[o][0] * A_STAGE_BYTES - opts[o][1] * STG_BYTES) / pl->raw_bytes;
-    n_raw = std::min(n_raw, std::min(raw_max, raw_want));
-    if (n_raw > best_raw) { best_raw = n_raw; pl->n_a = opts[o][0]; pl->n_stg = opts[o][1]; pl->n_raw = n_raw; }
-    if (best_raw >= raw_want) break;
+  // Options in order of preference: two epilogue warpgroups before one, three raw slots before two, three A stages
+  // before two, full staging (two store tiles, or the staged tile + two pooled boxes, per warpgroup) before minimal.
+  pl->n_raw = 0;
+  static const int epi_max = [] { const char* v = getenv("TMAT_DW_EPI"); return v && atoi(v) == 1 ? 1 : 2; }();
+  for (int n_epi = epi_max; n_epi >= 1 && pl->n_raw == 0; --n_epi) {
+    for (int want = std::min(raw_want, raw_max); want >= 2 && pl->n_raw == 0; --want) {
+      for (int n_a = 3; n_a >= 2 && pl->n_raw == 0; --n_a) {
+        for (int full = 1; full >= 0 && pl->n_raw == 0; --full) {
+          const int wg_bytes = pool ? STG_BYTES + (full ? 2 : 1) * POOL_BUF_BYTES : (full ? 2 : 1) * STG_BYTES;
+          const int n_raw = (budget - n_a * A_STAGE_BYTES - n_epi * wg_bytes) / pl->raw_bytes;
+          if (n_raw >= want) {
+            pl->n_raw = want; pl->n_a = n_a; pl->n_epi = n_epi; pl->stg_wg_bytes = wg_bytes;
+            pl->spw = full ? 2 : 1; pl->npb = full ? 2 : 1;
+          }
+        }
+      }
+    }
   }
-  if (best_raw < 2) return false;
-  pl->smem = pl->n_a * A_STAGE_BYTES + pl->n_b * b_bytes + pl->n_raw * pl->raw_bytes + pl->n_stg * STG_BYTES + TAIL_BYTES;
+  if (pl->n_raw < 2) return false;
+  pl->smem = pl->n_a * A_STAGE_BYTES + pl->n_b * b_bytes + pl->n_raw * pl->raw_bytes + pl->n_epi * pl->stg_wg_bytes + TAIL_BYTES;
   return true;
 }
 
@@ -661,25 +696,25 @@ int launch_dwpw(tmat_ctx* ctx, const CUtensorMap& raw, const CUtensorMap& b, con
 
 bool dwpw_supported(int B, int S, int C, int N) {
   DwpwPlan pl;
-  return plan_dwpw(B, S, C, N, &pl);
+  return plan_dwpw(B, S, C, N, false, &pl);
 }
 
 // The pooled epilogue needs whole even tiles inside the image, both staging tiles and a pooled box that fits half of one.
 static bool pool_plan_ok(const DwpwPlan& pl, int S) {
   const int TW = 1 << pl.tw_log, TH = 1 << pl.th_log, TN = 1 << pl.tn_log;
-  return S % 2 == 0 && TW >= 2 && TH >= 2 && S % TW == 0 && S % TH == 0 && pl.n_stg == 2 &&
+  return S % 2 == 0 && TW >= 2 && TH >= 2 && S % TW == 0 && S % TH == 0 &&
          TN * (TW / 2 + 1) * (TH / 2 + 1) <= POOL_MAX_ROWS;
 }
 
 bool dwpw_pool_supported(int B, int S, int C, int N) {
   DwpwPlan pl;
-  return plan_dwpw(B, S, C, N, &pl) && pool_plan_ok(pl, S);
+  return plan_dwpw(B, S, C, N, true, &pl) && pool_plan_ok(pl, S);
 }
 
 int dwpw_run(tmat_ctx* ctx, const bf16* in, int B, int S, int C, const float* dw, int relu_in, const bf16* wmat,
              const float* shift, int N, int relu_out, bf16* out, cudaStream_t st, bf16* pool_out) {
   DwpwPlan pl;
-  TMAT_REQUIRE(plan_dwpw(B, S, C, N, &pl), "dwpw: shape (B=%d, S=%d, C=%d, N=%d) not supported", B, S, C, N);
+  TMAT_REQUIRE(plan_dwpw(B, S, C, N, pool_out != nullptr, &pl), "dwpw: shape (B=%d, S=%d, C=%d, N=%d) not supported", B, S, C, N);
   TMAT_REQUIRE(pool_out == nullptr || pool_plan_ok(pl, S), "dwpw: pooled epilogue not supported for (B=%d, S=%d, C=%d, N=%d)",
                B, S, C, N);
   TMAT_REQUIRE(out != nullptr || pool_out != nullptr, "dwpw: no output");
@@ -693,12 +728,9 @@ int dwpw_run(tmat_ctx* ctx, const bf16* in, int B, int S, int C, const float* dw
   p.total_tiles = (int)total;
   p.nk = C / KSLAB; p.C = C; p.relu_in = relu_in;
   p.raw_bytes = pl.raw_bytes; p.raw_tx = pl.raw_tx;
-  p.n_raw = pl.n_raw; p.n_a = pl.n_a; p.n_b = pl.n_b; p.n_stg = pl.n_stg; p.b_resident = pl.b_resident;
+  p.n_raw = pl.n_raw; p.n_a = pl.n_a; p.n_b = pl.n_b; p.b_resident = pl.b_resident;
   p.dw = dw;
-  // warp order inside the CTA: the issue arbiter prefers the higher warp id, so the role that is on the critical
-  // path should sit above the other (TMAT_DWPW_ROLES=0: epilogue 2..5, depthwise 6..13; 1: depthwise 2..9, epilogue 10..13)
-  static const int roles = [] { const char* v = getenv("TMAT_DWPW_ROLES"); return v ? atoi(v) : 0; }();
-  p.epi_w0 = roles ? 10 : 2; p.dw_w0 = roles ? 2 : 6;
+  p.n_epi = pl.n_epi; p.stg_wg_bytes = pl.stg_wg_bytes; p.spw = pl.spw; p.npb = pl.npb;
   memset(&p.e, 0, sizeof(p.e));
   p.e.mode = EPI_STORE; p.e.relu = relu_out; p.e.B = B; p.e.H = S; p.e.W = S; p.e.Cout = N; p.e.ppg = 1;
   p.e.shift = shift; p.e.out = out;
