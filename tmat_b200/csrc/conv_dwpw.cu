@@ -549,16 +549,22 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
     const int RW = TW + 2, RH = TH + 2;
     const bool relu = p.relu_in != 0;
     int item = 0;
+    int w_ks = -1;
+    f32x2 wr[9][2];
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
       for (int ks = 0; ks < p.nk; ++ks, ++item) {
         if ((item & 1) != grp) continue;
         const int sa = item % p.n_a, rs = item % p.n_raw;
         const uint32_t pa = (uint32_t)(item / p.n_a) & 1u, rphase = (uint32_t)(item / p.n_raw) & 1u;
-        f32x2 wr[9][2];
+        // a group sees the same slab every time when nk <= 2 (item parity = slab parity): its 36 depthwise weights
+        // are then loaded once, not once per item (ncu: 16 % of the depthwise warps' samples sat behind these loads)
+        if (ks != w_ks) {
+          w_ks = ks;
 #pragma unroll
-        for (int tp = 0; tp < 9; ++tp) {
-          float4 wv = __ldg(reinterpret_cast<const float4*>(p.dw + tp * p.C + ks * KSLAB + h * 4));
-          wr[tp][0] = pack2(wv.x, wv.y); wr[tp][1] = pack2(wv.z, wv.w);
+          for (int tp = 0; tp < 9; ++tp) {
+            float4 wv = __ldg(reinterpret_cast<const float4*>(p.dw + tp * p.C + ks * KSLAB + h * 4));
+            wr[tp][0] = pack2(wv.x, wv.y); wr[tp][1] = pack2(wv.z, wv.w);
+          }
         }
         while (*issued <= item) { }
         mbar_wait(rfull_bar(rs), rphase);
@@ -636,9 +642,10 @@ bool plan_dwpw(int B, int S, int C, int N, bool pool, DwpwPlan* pl) {
   const int b_bytes = pl->BN * KSLAB * 2;
   const int nk = C / KSLAB;
   static const int raw_max = [] { const char* v = getenv("TMAT_DW_RAW"); int r = v ? atoi(v) : MAX_RAW; return r < 2 ? 2 : (r > MAX_RAW ? MAX_RAW : r); }();
-  // three slots (two in work, one in flight) are enough: depths 2..6 measured the same, and the options below
-  // that buy more slots cost the second staging buffer, which the epilogue does wait for
-  constexpr int raw_want = 3;
+  // two slots are in work (one per depthwise group), the rest are loads in flight.  With one epilogue warpgroup the
+  // depth did not matter (2..6 measured the same); with two, the depthwise groups wait for raw tiles (ncu), so the
+  // ring takes what is left after the other buffers, up to raw_want.
+  static const int raw_want = [] { const char* v = getenv("TMAT_DW_RAWWANT"); int r = v ? atoi(v) : 4; return r < 2 ? 2 : (r > MAX_RAW ? MAX_RAW : r); }();
   pl->b_resident = (N == pl->BN && nk * b_bytes <= 64 * 1024 && nk <= MAX_B) ? 1 : 0;
   pl->n_b = pl->b_resident ? nk : 2;
   const int budget = 227 * 1024 - TAIL_BYTES - pl->n_b * b_bytes;
