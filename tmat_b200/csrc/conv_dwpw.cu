@@ -551,11 +551,17 @@ conv_dwpw_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
     int item = 0;
     int w_ks = -1;
     f32x2 wr[9][2];
+    // ring slot and phase of the current item, advanced per item (every item, also the other group's) instead of
+    // item % n and item / n: the two integer divisions were ~100 instructions of each item's prologue
+    int sa = 0, rs = 0;
+    uint32_t pa = 0, rphase = 0;
+    auto ring_advance = [&]() {
+      if (++sa == p.n_a) { sa = 0; pa ^= 1u; }
+      if (++rs == p.n_raw) { rs = 0; rphase ^= 1u; }
+    };
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
-      for (int ks = 0; ks < p.nk; ++ks, ++item) {
+      for (int ks = 0; ks < p.nk; ++ks, ++item, ring_advance()) {
         if ((item & 1) != grp) continue;
-        const int sa = item % p.n_a, rs = item % p.n_raw;
-        const uint32_t pa = (uint32_t)(item / p.n_a) & 1u, rphase = (uint32_t)(item / p.n_raw) & 1u;
         // a group sees the same slab every time when nk <= 2 (item parity = slab parity): its 36 depthwise weights
         // are then loaded once, not once per item (ncu: 16 % of the depthwise warps' samples sat behind these loads)
         if (ks != w_ks) {
