@@ -21,7 +21,8 @@ using namespace tcptx;
 
 namespace {
 
-constexpr int HALO_THREADS = 192;
+constexpr int HALO_THREADS = 320;                // producer, MMA, two epilogue warpgroups (warps 2..5, 6..9) on alternate tiles
+constexpr int HALO_EPI_WGS = 2;
 constexpr int HTW = 8, HTH = 16;                 // tile: 8 x 16 pixels of one image
 constexpr int MAX_STAGES = 8;
 constexpr int MAX_RAW = 4;
@@ -60,7 +61,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
   const uint32_t raw_base = (b_base + n_btiles * B_TILE_BYTES + 1023u) & ~1023u;
   const uint32_t stg_base = raw_base + p.n_raw * p.raw_bytes;
   constexpr int Z_BYTES = (BN >= 64 ? BN / 64 : 1) * 4096;
-  const uint32_t z_base = stg_base + N_STG * STG_BYTES;
+  const uint32_t z_base = stg_base + HALO_EPI_WGS * N_STG * STG_BYTES;
   const uint32_t bar_base = z_base + p.n_z * Z_BYTES;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (MAX_STAGES + s); };
@@ -215,17 +216,24 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
     }
     __syncwarp();
   } else {
-    // ================= epilogue (warps 2..5) =================
+    // ================= epilogue (warps 2..5 and 6..9: one accumulator buffer, staging pair, shift area, named
+    // barrier and store leader per warpgroup; tile it goes to warpgroup it & 1) =================
+    const int ewg = (warp - 2) >> 2;
     const int q = warp & 3;
     const int row = q * 32 + lane;
     const int tx_in = row & (HTW - 1), ty_in = row >> 3;
-    const bool leader = (threadIdx.x == 64);
+    const bool leader = (threadIdx.x == 64 + 128 * ewg);
     const uint32_t stg_row = (uint32_t)row * 128u;
     const uint32_t sw = (uint32_t)(row & 7);
     const EpiParams& e = p.e;
+    const uint32_t stg_wg = stg_base + (uint32_t)(ewg * N_STG * STG_BYTES);
     int sbuf = 0;
     int zs = 0; uint32_t zphase = 0;
     for (int it = 0; it < my_tiles; ++it) {
+      if ((it & 1) != ewg) {          // the other warpgroup's tile (and addend slot)
+        if (p.n_z > 0 && ++zs == p.n_z) { zs = 0; zphase ^= 1; }
+        continue;
+      }
       const int as = it & 1;
       const uint32_t aphase = (it >> 1) & 1;
       int nt, x0, y0, b0;
@@ -240,8 +248,9 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmRaw, const __grid_constan
         z_row = z_base + zs * Z_BYTES + pz * 128u;
         zsw = pz & 7u;
       }
-      tc_epilogue_tile<BN>(e, om, taddr, 0, nt, x0, y0, b0, x, y, b, valid, stg_base, stg_row, sw, leader, sbuf,
-                           tempty_bar(as), tfull_bar(as), aphase, bar_base + 512u, z_row, zsw);
+      tc_epilogue_tile<BN>(e, om, taddr, 0, nt, x0, y0, b0, x, y, b, valid, stg_wg, stg_row, sw, leader, sbuf,
+                           tempty_bar(as), tfull_bar(as), aphase, bar_base + 512u + 512u * (uint32_t)ewg, z_row, zsw,
+                           1u + (uint32_t)ewg);
       if (p.n_z > 0) {
         mbar_arrive(zempty_bar(zs));
         if (++zs == p.n_z) { zs = 0; zphase ^= 1; }
@@ -290,7 +299,7 @@ bool plan_halo(const ConvOp& op, int mode, HaloPlan* pl) {
   for (int with_z = z_ok ? 1 : 0; with_z >= 0; --with_z) {
     pl->n_z = with_z ? MAX_Z : 0;
     const int z_bytes = pl->n_z * (pl->BN >= 64 ? pl->BN / 64 : 1) * 4096;
-    const int budget = 227 * 1024 - 3072 - N_STG * STG_BYTES - z_bytes;
+    const int budget = 227 * 1024 - 3072 - HALO_EPI_WGS * N_STG * STG_BYTES - z_bytes;
     for (int n_raw = 3; n_raw >= 2; --n_raw) {
       int left = budget - n_raw * pl->raw_bytes;
       if (left < 2 * btile) continue;
@@ -299,7 +308,7 @@ bool plan_halo(const ConvOp& op, int mode, HaloPlan* pl) {
       else { pl->b_resident = 0; pl->n_stage = std::min(MAX_STAGES, left / btile); }
       if (with_z && !pl->b_resident) continue;
       int nb = pl->b_resident ? 9 * nslab : pl->n_stage;
-      pl->smem = nb * btile + n_raw * pl->raw_bytes + N_STG * STG_BYTES + z_bytes + 3072;
+      pl->smem = nb * btile + n_raw * pl->raw_bytes + HALO_EPI_WGS * N_STG * STG_BYTES + z_bytes + 3072;
       return true;
     }
   }

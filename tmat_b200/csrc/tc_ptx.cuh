@@ -76,7 +76,7 @@ __device__ __forceinline__ void tma_store_wait_read() {
 }
 __device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 // named barrier among the 128 epilogue threads (barrier 0 is __syncthreads)
-__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+__device__ __forceinline__ void epi_bar_sync(uint32_t id = 1) { asm volatile("bar.sync %0, 128;" ::"r"(id) : "memory"); }
 __device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
   uint4 v;
   asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
@@ -247,7 +247,8 @@ __device__ __forceinline__ void tc_epilogue_tile(const EpiParams& e, const TcOut
                                                  int x0, int y0, int b0, int x, int y, int b, bool valid,
                                                  uint32_t stg_base, uint32_t stg_row, uint32_t sw, bool leader,
                                                  int& sbuf, uint32_t tempty, uint32_t tfull, uint32_t tphase,
-                                                 uint32_t shift_smem, uint32_t z_row = 0, uint32_t zsw = 0) {
+                                                 uint32_t shift_smem, uint32_t z_row = 0, uint32_t zsw = 0,
+                                                 uint32_t bar_id = 1) {
       // z_row != 0: the addend of this thread's pixel was staged in shared memory by the producer (one
       // 128-byte-swizzled row of 64 channels per 4096-byte block, block c64 / 64); else it is gathered from e.add_src
       if constexpr (BN >= 64) {
@@ -287,7 +288,7 @@ __device__ __forceinline__ void tc_epilogue_tile(const EpiParams& e, const TcOut
           }
           // the staging buffer(s) about to be written must have been read out by their last store
           if (leader) { if (dual) tma_store_wait_read<0>(); else tma_store_wait_read<1>(); }
-          epi_bar_sync();
+          epi_bar_sync(bar_id);
           const uint32_t buf0 = stg_base + (dual ? 0 : sbuf * STG_BYTES) + stg_row;
           const uint32_t buf1 = stg_base + STG_BYTES + stg_row;
           auto chunk = [&](auto relu_c) {
@@ -336,7 +337,7 @@ __device__ __forceinline__ void tc_epilogue_tile(const EpiParams& e, const TcOut
             mbar_arrive(tempty);
           }
           fence_proxy_async();                   // generic-proxy smem writes -> visible to the TMA unit
-          epi_bar_sync();
+          epi_bar_sync(bar_id);
           if (leader) {
             tma_store_4d(&om.m[par], buf0 - stg_row, ch0, x0, y0, b0);
             if (dual) tma_store_4d(&om.m2, buf1 - stg_row, ch0, x0, y0, b0);
