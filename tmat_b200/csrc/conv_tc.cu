@@ -30,13 +30,14 @@ using namespace tcptx;
 namespace {
 
 constexpr int MAX_KSTEPS = 160;                    // over all groups
-constexpr int TC_THREADS = 192;
+constexpr int TC_THREADS = 320;                    // producer, MMA, two epilogue warpgroups (warps 2..5, 6..9)
 
 struct TcParams {
   int tw_log, th_log, tn_log;   // tile = 2^tw x 2^th pixels x 2^tn images (product 128)
   int tiles_x, tiles_y, tiles_b, tiles_n, ngroups, total_tiles;
   int nk;                       // k-steps per group
   int npad;                     // GEMM columns per group
+  int n_epi;                    // epilogue warpgroups in use: 2 (alternate tiles, one staging tile each) or 1
   uint16_t kstep[MAX_KSTEPS];   // [group][nk]: bit0 src | bits1-2 dy+1 | bits3-4 dx+1 | bits5.. c0/64
   EpiParams e;
 };
@@ -49,7 +50,9 @@ struct TcSmem {
   static constexpr int STG_OFFSET = STAGES * STAGE_BYTES;
   static constexpr int BAR_OFFSET = STG_OFFSET + N_STG * STG_BYTES;
   static constexpr int SHIFT_OFFSET = BAR_OFFSET + 256;     // BN fp32 shift values of the current tile
-  static constexpr int BYTES = SHIFT_OFFSET + (BN < 64 ? 64 : BN) * 4 + 1024;   // barriers + shift + alignment slack
+  static constexpr int SHIFT_BYTES = (BN < 64 ? 64 : BN) * 4;
+  static constexpr int EPI_WGS = (BN == 128 || BN == 64) ? 2 : 1;           // BN = 256 has no room for a second shift area
+  static constexpr int BYTES = SHIFT_OFFSET + EPI_WGS * SHIFT_BYTES + 1024;  // barriers + shift + alignment slack
   static_assert(BYTES <= 227 * 1024, "shared memory budget");
 };
 
@@ -151,20 +154,25 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
     }
     __syncwarp();
   } else {
-    // ================= epilogue (warps 2..5) =================
+    // ================= epilogue (warps 2..5, and 6..9 on alternate tiles when p.n_epi == 2: the layers with few
+    // k-steps per tile are bound by the epilogue's single dependent instruction stream per scheduler) =================
+    const int ewg = (warp - 2) >> 2;
+    const bool two = (p.n_epi == 2);
     const int q = warp & 3;                   // TMEM lane quarter this warp may access
     const int row = q * 32 + lane;            // GEMM row = pixel within the tile
     const int tx_in = row & (TW - 1);
     const int ty_in = (row >> p.tw_log) & (TH - 1);
     const int tb_in = row >> (p.tw_log + p.th_log);
-    const bool leader = (threadIdx.x == 64);  // issues, commits and waits on every TMA store
-    const uint32_t stg_base = smem_base + L::STG_OFFSET;
+    const bool leader = (threadIdx.x == 64 + 128 * ewg);  // issues, commits and waits on every TMA store
+    const uint32_t stg_base = smem_base + L::STG_OFFSET + (two ? (uint32_t)(ewg * STG_BYTES) : 0u);
+    const uint32_t shift_smem = smem_base + L::SHIFT_OFFSET + (two ? (uint32_t)(ewg * L::SHIFT_BYTES) : 0u);
     const uint32_t stg_row = (uint32_t)row * 128u;
     const uint32_t sw = (uint32_t)(row & 7);
     const EpiParams& e = p.e;
     int sbuf = 0;
     int it = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+      if (ewg >= p.n_epi || (two && (it & 1) != ewg)) continue;
       const int as = it & 1;
       const uint32_t aphase = (it >> 1) & 1;
       int g, nt, x0, y0, b0;
@@ -179,7 +187,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
         tc_prefetch_addend(e, ntn * BN, BN, x0n + tx_in, y0n + ty_in, b0n + tb_in);
       }
       tc_epilogue_tile<BN>(e, om, taddr, g, nt, x0, y0, b0, x, y, b, valid, stg_base, stg_row, sw, leader, sbuf,
-                           tempty_bar(as), tfull_bar(as), aphase, smem_base + L::SHIFT_OFFSET);
+                           tempty_bar(as), tfull_bar(as), aphase, shift_smem, 0, 0, 1u + (uint32_t)ewg, two);
     }
     if (leader) tma_store_wait_all();            // smem must outlive the last store's read
   }
@@ -282,6 +290,10 @@ static int launch_tc(tmat_ctx* ctx, const CUtensorMap& a0, const CUtensorMap& a1
     configured = true;
   }
   int grid = std::min(p.total_tiles, ctx->sm_count);
+  // two epilogue warpgroups share the staging pair (one tile each): not with dual stores, which need both tiles
+  static const int epi_max = [] { const char* v = getenv("TMAT_TC_EPI"); return v && atoi(v) == 1 ? 1 : 2; }();
+  TcParams pp = p;
+  pp.n_epi = (L::EPI_WGS == 2 && p.e.out2 == nullptr && epi_max == 2) ? 2 : 1;
   tmat_ctx::ProfRec rec{nullptr, nullptr, 0.0};
   if (ctx->profiling) {
     for (cudaEvent_t* e : {&rec.a, &rec.b}) {
@@ -291,7 +303,7 @@ static int launch_tc(tmat_ctx* ctx, const CUtensorMap& a0, const CUtensorMap& a1
     rec.flops = 2.0 * p.e.B * p.e.H * p.e.W * (double)(p.ngroups * p.tiles_n * BN) * (double)(p.nk * KSLAB);
     CUDA_TRY(cudaEventRecord(rec.a, st));
   }
-  conv_tc_kernel<BN, STAGES><<<grid, TC_THREADS, L::BYTES, st>>>(a0, a1, b, om, p);
+  conv_tc_kernel<BN, STAGES><<<grid, TC_THREADS, L::BYTES, st>>>(a0, a1, b, om, pp);
   KERNEL_CHECK(ctx);
   if (ctx->profiling) {
     CUDA_TRY(cudaEventRecord(rec.b, st));

@@ -248,7 +248,8 @@ __device__ __forceinline__ void tc_epilogue_tile(const EpiParams& e, const TcOut
                                                  uint32_t stg_base, uint32_t stg_row, uint32_t sw, bool leader,
                                                  int& sbuf, uint32_t tempty, uint32_t tfull, uint32_t tphase,
                                                  uint32_t shift_smem, uint32_t z_row = 0, uint32_t zsw = 0,
-                                                 uint32_t bar_id = 1) {
+                                                 uint32_t bar_id = 1, bool single = false) {
+      // single: this epilogue warpgroup owns ONE staging tile (two warpgroups share the staging pair); not with dual
       // z_row != 0: the addend of this thread's pixel was staged in shared memory by the producer (one
       // 128-byte-swizzled row of 64 channels per 4096-byte block, block c64 / 64); else it is gathered from e.add_src
       if constexpr (BN >= 64) {
@@ -287,9 +288,9 @@ __device__ __forceinline__ void tc_epilogue_tile(const EpiParams& e, const TcOut
             tc_fence_after();
           }
           // the staging buffer(s) about to be written must have been read out by their last store
-          if (leader) { if (dual) tma_store_wait_read<0>(); else tma_store_wait_read<1>(); }
+          if (leader) { if (dual || single) tma_store_wait_read<0>(); else tma_store_wait_read<1>(); }
           epi_bar_sync(bar_id);
-          const uint32_t buf0 = stg_base + (dual ? 0 : sbuf * STG_BYTES) + stg_row;
+          const uint32_t buf0 = stg_base + ((dual || single) ? 0 : sbuf * STG_BYTES) + stg_row;
           const uint32_t buf1 = stg_base + STG_BYTES + stg_row;
           auto chunk = [&](auto relu_c) {
             constexpr bool RELU = decltype(relu_c)::value;
