@@ -51,8 +51,11 @@ struct TcSmem {
   static constexpr int BAR_OFFSET = STG_OFFSET + N_STG * STG_BYTES;
   static constexpr int SHIFT_OFFSET = BAR_OFFSET + 256;     // BN fp32 shift values of the current tile
   static constexpr int SHIFT_BYTES = (BN < 64 ? 64 : BN) * 4;
-  static constexpr int EPI_WGS = (BN == 128 || BN == 64) ? 2 : 1;           // BN = 256 has no room for a second shift area
-  static constexpr int BYTES = SHIFT_OFFSET + EPI_WGS * SHIFT_BYTES + 1024;  // barriers + shift + alignment slack
+  static constexpr int EPI_WGS = (BN >= 64) ? 2 : 1;
+  // BN = 256 has no room for a second shift area: its two warpgroups share one, which is only used when every tile
+  // has the same column tile (tiles_n == 1), i.e. both write the same values
+  static constexpr int SHIFT_AREAS = (BN == 128 || BN == 64) ? 2 : 1;
+  static constexpr int BYTES = SHIFT_OFFSET + SHIFT_AREAS * SHIFT_BYTES + 1024;  // barriers + shift + alignment slack
   static_assert(BYTES <= 227 * 1024, "shared memory budget");
 };
 
@@ -165,7 +168,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
     const int tb_in = row >> (p.tw_log + p.th_log);
     const bool leader = (threadIdx.x == 64 + 128 * ewg);  // issues, commits and waits on every TMA store
     const uint32_t stg_base = smem_base + L::STG_OFFSET + (two ? (uint32_t)(ewg * STG_BYTES) : 0u);
-    const uint32_t shift_smem = smem_base + L::SHIFT_OFFSET + (two ? (uint32_t)(ewg * L::SHIFT_BYTES) : 0u);
+    const uint32_t shift_smem = smem_base + L::SHIFT_OFFSET + ((two && L::SHIFT_AREAS == 2) ? (uint32_t)(ewg * L::SHIFT_BYTES) : 0u);
     const uint32_t stg_row = (uint32_t)row * 128u;
     const uint32_t sw = (uint32_t)(row & 7);
     const EpiParams& e = p.e;
@@ -290,10 +293,11 @@ static int launch_tc(tmat_ctx* ctx, const CUtensorMap& a0, const CUtensorMap& a1
     configured = true;
   }
   int grid = std::min(p.total_tiles, ctx->sm_count);
-  // two epilogue warpgroups share the staging pair (one tile each): not with dual stores, which need both tiles
-  static const int epi_max = [] { const char* v = getenv("TMAT_TC_EPI"); return v && atoi(v) == 1 ? 1 : 2; }();
+  // two epilogue warpgroups share the staging pair (one tile each): not with dual stores, which need both tiles; at
+  // BN = 256 only for layers with few k-steps per tile (the MMA-bound ones measured 1.5 % slower with it)
+  static const int epi_max = [] { const char* v = getenv("TMAT_TC_EPI"); return v ? atoi(v) : 3; }();   // 1: one warpgroup; 2: two for BN <= 128; 3: also BN = 256
   TcParams pp = p;
-  pp.n_epi = (L::EPI_WGS == 2 && p.e.out2 == nullptr && epi_max == 2) ? 2 : 1;
+  pp.n_epi = (L::EPI_WGS == 2 && p.e.out2 == nullptr && epi_max >= 2 && (L::SHIFT_AREAS == 2 || (p.tiles_n == 1 && p.nk <= 8 && epi_max == 3))) ? 2 : 1;
   tmat_ctx::ProfRec rec{nullptr, nullptr, 0.0};
   if (ctx->profiling) {
     for (cudaEvent_t* e : {&rec.a, &rec.b}) {
