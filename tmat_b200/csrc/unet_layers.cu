@@ -24,7 +24,9 @@ __global__ void __launch_bounds__(256, 2) stem_kernel(StemSrc src, int B, int ws
   // so the global-load latency of the fill hides behind the FFMA2 work.  Weights are loaded once per block.
   constexpr int IR = 2 * STEM_ROWS + 1, IC = 2 * STEM_COLS + 1;
   constexpr int FILL = (IR * IC + 255) / 256;
-  __shared__ float tile[2][IR][IC + 2];
+  // every window element is stored twice, as the (v, v) pair FFMA2 wants for a pixel broadcast over two channels:
+  // one 8-byte ld.shared instead of a 4-byte one plus two register moves per tap (ptxas: 144 IMAD.MOV per 8 rows)
+  __shared__ __align__(8) float2 tile[2][IR][IC + 1];
   const int S = ws >> 1;
   const int total = tiles_x * tiles_y * B;
   // window of tile t -> tile[buf], asynchronously (cp.async, 4 bytes per element; padding / out-of-range
@@ -60,7 +62,7 @@ __global__ void __launch_bounds__(256, 2) stem_kernel(StemSrc src, int B, int ws
       if (idx >= IR * IC) break;
       const int r = idx / IC, c = idx - r * IC;
       const int i = 2 * y0 + r, j = 2 * x0 + c;
-      float* dst = &tile[buf][r][c];
+      float2* dst = &tile[buf][r][c];
       const float* gp = nullptr;
       float cv = 0.f;
       if (i < ws && j < ws) {
@@ -74,9 +76,11 @@ __global__ void __launch_bounds__(256, 2) stem_kernel(StemSrc src, int B, int ws
         }
       }
       if (gp != nullptr) {
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(gp) : "memory");
+        const uint32_t da = (uint32_t)__cvta_generic_to_shared(dst);
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(da), "l"(gp) : "memory");
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(da + 4u), "l"(gp) : "memory");
       } else {
-        *dst = cv;
+        *dst = make_float2(cv, cv);
       }
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
@@ -106,8 +110,11 @@ __global__ void __launch_bounds__(256, 2) stem_kernel(StemSrc src, int B, int ws
     for (int xl = threadIdx.x / groups; xl < STEM_COLS; xl += px_per_pass) {
       const int x = x0 + xl;
       if (x >= S) break;
+      // one 64-bit address per column, advanced by a row per iteration
+      bf16* op = out + (((int64_t)b * S + y0) * S + x) * C0 + cg * 8;
+      const int64_t row_stride = (int64_t)S * C0;
 #pragma unroll
-      for (int r = 0; r < STEM_ROWS; ++r) {
+      for (int r = 0; r < STEM_ROWS; ++r, op += row_stride) {
         const int y = y0 + r;
         if (y >= S) break;
         f32x2 acc[4];
@@ -117,8 +124,7 @@ __global__ void __launch_bounds__(256, 2) stem_kernel(StemSrc src, int B, int ws
         for (int ky = 0; ky < 3; ++ky)
 #pragma unroll
           for (int kx = 0; kx < 3; ++kx) {
-            const float v = tile[buf][2 * r + ky][2 * xl + kx];
-            const f32x2 vv = pack2(v, v);
+            const f32x2 vv = *reinterpret_cast<const f32x2*>(&tile[buf][2 * r + ky][2 * xl + kx]);
 #pragma unroll
             for (int c = 0; c < 4; ++c) acc[c] = ffma2(vv, wr[ky * 3 + kx][c], acc[c]);
           }
@@ -128,10 +134,9 @@ __global__ void __launch_bounds__(256, 2) stem_kernel(StemSrc src, int B, int ws
         for (int c = 0; c < 4; ++c) {
           float lo, hi;
           unpack2(acc[c], lo, hi);
-          __nv_bfloat162 h = __floats2bfloat162_rn(fmaxf(lo, 0.f), fmaxf(hi, 0.f));
-          ow[c] = *reinterpret_cast<uint32_t*>(&h);
+          asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(ow[c]) : "f"(hi), "f"(lo));   // ReLU inside the convert
         }
-        *reinterpret_cast<uint4*>(out + (((int64_t)b * S + y) * S + x) * C0 + cg * 8) = o;
+        *reinterpret_cast<uint4*>(op) = o;
       }
     }
     asm volatile("cp.async.wait_group 0;" ::: "memory");
