@@ -13,7 +13,7 @@ namespace {
 // map when the patches come straight from the image -- and every thread computes 8 output channels
 // of one column for all rows of the strip with its 72 weights in registers.  A warp stores
 // 4 pixels x 128 bytes = 512 contiguous bytes.
-constexpr int STEM_ROWS = 8;
+constexpr int STEM_ROWS = 16;
 constexpr int STEM_COLS = 32;
 
 __global__ void __launch_bounds__(256, 2) stem_kernel(StemSrc src, int B, int ws, const float* __restrict__ w,
