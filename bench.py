@@ -266,8 +266,8 @@ def main():
             "config": {"workload": f"C4 per-image unit: one {size}x{size} float32 projection per rank per step -> "
                                    f"{patches} patches of 320x320 (ws 320, subdiv 2, 8x D4) through the random-init "
                                    "binary_segmentation UNet (64/128/256/512) + spline blend",
-                       "l2": "working set per step (554 MB of patch probabilities + ~10 GB of activations per "
-                             "256-patch chunk) exceeds the 126 MB L2; no explicit flush",
+                       "l2": "working set per step (554 MB of patch probabilities + ~13 GB of activations per "
+                             "338-patch chunk) exceeds the 126 MB L2; no explicit flush",
                        "parallelism": f"image-sharded x{world}"},
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": pk["bf16_sustained"], "unit": "TFLOP/s",
                          "frac": achieved / pk["bf16_sustained"], "traffic": traffic, "traffic_note": traffic_note,

@@ -537,14 +537,18 @@ extern "C" int tmat_unet_free(tmat_unet* net) {
   return TMAT_OK;
 }
 
-static int chunk_size(const tmat_unet* net) {
+// Patches per chunk for n patches: at most ~352 patches of 320x320 (~40 MB of bf16 activations each, 14 GB per chunk),
+// split evenly so that the last chunk is not a short one (1352 patches -> 4 x 338).  Large chunks keep the persistent
+// GEMM kernels at >= 20 tiles per SM even at the 20x20 bottleneck (measured per 2048^2 image: 64 -> 65.8, 128 -> 61.9,
+// 256 -> 60.4 ms on the first path; 256 -> 43.0, 352 -> 42.3, 512 -> 42.5 ms on the final one).
+static int chunk_size(const tmat_unet* net, int n) {
   const char* e = getenv("TMAT_CHUNK");
-  if (e && atoi(e) > 0) return atoi(e);
-  // ~40 MB of bf16 activations per 320x320 patch; 256 patches per chunk (10 GB) keep the persistent GEMM
-  // kernels at >= 20 tiles per SM even at the 20x20 bottleneck (measured: 64 -> 65.8, 128 -> 61.9, 256 -> 60.4 ms)
+  if (e && atoi(e) > 0) return std::min(n, atoi(e));
   int64_t px = (int64_t)net->desc.patch * net->desc.patch;
-  int c = (int)(256 * 102400 / px);
-  return c < 8 ? 8 : (c > 2048 ? 2048 : c);
+  int cap = (int)(352 * 102400 / px);
+  cap = cap < 8 ? 8 : (cap > 2048 ? 2048 : cap);
+  const int n_chunks = (n + cap - 1) / cap;
+  return (n + n_chunks - 1) / n_chunks;
 }
 
 extern "C" int tmat_unet_forward_dev(tmat_ctx* ctx, tmat_unet* net, const float* patches_dev, int n,
@@ -553,7 +557,7 @@ extern "C" int tmat_unet_forward_dev(tmat_ctx* ctx, tmat_unet* net, const float*
   TMAT_REQUIRE(n >= 1, "tmat_unet_forward: n=%d", n);
   TMAT_TRY(arena_reset(ctx));
   const int ws = net->desc.patch;
-  const int CH = std::min(n, chunk_size(net));
+  const int CH = chunk_size(net, n);
   TMAT_TRY(arena_reserve(ctx, forward_scratch_bytes(net, CH)));
   net->keep_taps = (n <= CH);
   for (int p0 = 0; p0 < n; p0 += CH) {
@@ -598,7 +602,7 @@ size_t stp_predict_scratch_bytes(const tmat_unet* net, int H, int W, int subdiv)
   if (stp_make_geom(H, W, net->desc.patch, subdiv, &G) != TMAT_OK) return 0;
   const int n_total = 8 * G.tiles_per_orient();
   const int ws = net->desc.patch;
-  return (size_t)n_total * ws * ws * 4 + forward_scratch_bytes(net, std::min(n_total, chunk_size(net))) + (4 << 20);
+  return (size_t)n_total * ws * ws * 4 + forward_scratch_bytes(net, chunk_size(net, n_total)) + (4 << 20);
 }
 
 // predict_img_with_smooth_windowing with pred_func = this UNet; arena must have been reset by the caller
@@ -608,7 +612,7 @@ int stp_predict_impl(tmat_ctx* ctx, tmat_unet* net, const float* img_dev, int H,
   const int ws = net->desc.patch;
   TMAT_TRY(stp_make_geom(H, W, ws, subdiv, &G));
   const int n_total = 8 * G.tiles_per_orient();
-  const int CH = std::min(n_total, chunk_size(net));
+  const int CH = chunk_size(net, n_total);
   size_t probs_bytes = (size_t)n_total * ws * ws * 4;
   TMAT_TRY(arena_reserve(ctx, probs_bytes + forward_scratch_bytes(net, CH) + (1 << 20)));
   float* minmax;
@@ -647,7 +651,7 @@ int stp_predict_rows_impl(tmat_ctx* ctx, tmat_unet* net, const float* img_dev, i
   if (n_patches) *n_patches = n_sel;
   std::vector<int> slot(n_total, -1);
   for (int i = 0; i < n_sel; ++i) slot[list[i]] = i;
-  const int CH = std::min(n_sel, chunk_size(net));
+  const int CH = chunk_size(net, n_sel);
   TMAT_TRY(arena_reserve(ctx, (size_t)n_sel * ws * ws * 4 + forward_scratch_bytes(net, CH) + (size_t)n_total * 8 + (4 << 20)));
   float *minmax, *probs;
   double* w1d;
@@ -714,7 +718,7 @@ extern "C" int tmat_stp_predict_host(tmat_ctx* ctx, tmat_unet* net, const float*
   TMAT_TRY(stp_make_geom(H, W, net->desc.patch, subdiv, &G));
   const int n_total = 8 * G.tiles_per_orient();
   const int ws = net->desc.patch;
-  TMAT_TRY(arena_reserve(ctx, (size_t)n_total * ws * ws * 4 + forward_scratch_bytes(net, std::min(n_total, chunk_size(net))) +
+  TMAT_TRY(arena_reserve(ctx, (size_t)n_total * ws * ws * 4 + forward_scratch_bytes(net, chunk_size(net, n_total)) +
                                   (size_t)H * W * 12 + (4 << 20)));
   float* d_img;
   double* d_out;
