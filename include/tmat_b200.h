@@ -74,9 +74,10 @@ int  tmat_ctx_profile_enable(tmat_ctx* ctx, int on);
 int  tmat_ctx_profile_collect(tmat_ctx* ctx, double* out3);
 
 /* ---- stage 1: Z projection  (zstacks.py:134-249) ------------------------------------ */
-/* stack: (Z,H,W) of dtype TMAT_U8|TMAT_U16 (TMAT_F32 for min/max/avg/med).  out: (H,W) of the
- * stack dtype for MIN/MAX/FS, float64 for AVG/MED.  ksize must be 5 for FS (the reference's
- * default kernel_size, zstacks.py:153). */
+/* stack: (Z,H,W) of dtype TMAT_U8|TMAT_U16, or TMAT_F32 for MIN/MAX/AVG/MED (numpy semantics:
+ * np.mean/np.median of a float32 stack stay float32; NaNs are not handled).  out: (H,W) of the
+ * stack dtype for MIN/MAX/FS; for AVG/MED float64 (integer stacks) or float32 (float32 stacks).
+ * ksize must be 5 for FS (the reference's default kernel_size, zstacks.py:153). */
 int tmat_zproj_dev(tmat_ctx* ctx, const void* stack_dev, int dtype, int Z, int H, int W,
                    int method, int ksize, void* out_dev, void* stream);
 int tmat_zproj_host(tmat_ctx* ctx, const void* stack_host, int dtype, int Z, int H, int W,
@@ -146,29 +147,6 @@ int tmat_stp_predict_rows_host(tmat_ctx* ctx, tmat_unet* net, const float* img_h
  * frame) of the patches whose window touches output rows [row0, row1).  list may be NULL to query the count. */
 int tmat_stp_rows_patches(int H, int W, int ws, int subdiv, int row0, int row1, int* list, int capacity,
                           int* n_out);
-/* debug / test hook: copy a named intermediate activation of the last forward (float32 NHWC)
- * to the host; returns TMAT_ERR_INVALID when the tap does not exist. */
-int tmat_unet_debug_tap(tmat_ctx* ctx, tmat_unet* net, const char* name, float* out_host,
-                        int64_t capacity, int64_t* n_written);
-/* debug / test hook: one implicit-GEMM convolution (the unit the UNet is built from) on seeded
- * random data through the CUDA-core executor and through the tcgen05 executor; returns the
- * max-abs difference of the outputs and the max-abs of the CUDA-core output.
- * epi: 0 store, 1 parity store (3x3 conv on the 2x nearest-upsampled input, evaluated at low
- * resolution), 3 head (sigmoid unless relu!=0).  dual: also write the ReLU'd copy (epi 0).
- * addend: 0 none, 1 same-resolution addend, 2 half-resolution addend (epi 0). */
-int tmat_debug_conv_selftest(tmat_ctx* ctx, int B, int H, int W, int C0, int C1, int Cout, int ntaps,
-                             int epi, int relu, int dual, int addend, uint64_t seed,
-                             double* max_abs_diff, double* max_abs_ref);
-/* Debug switch of the haloed-tile 3x3 kernel (conv_halo.cu): 0 off, 1 on.  Default: env TMAT_HALO or 1. */
-int tmat_debug_set_halo_mode(int mode);
-/* Self-test hook: the fused SeparableConv2D kernel (depthwise 3x3 computed into the tcgen05 A operand)
- * vs the unfused pair (depthwise kernel, CUDA-core GEMM) on random data. */
-int tmat_debug_dwpw_selftest(tmat_ctx* ctx, int B, int S, int C, int N, int relu_in, int relu_out,
-                             uint64_t seed, double* max_abs_diff, double* max_abs_ref);
-/* the same kernel with MaxPool2D(3, strides=2, 'same') (models.py:139) folded into its epilogue, against the unfused
- * kernel followed by the stand-alone pooling kernel: max_abs_diff must be 0. */
-int tmat_debug_dwpw_pool_selftest(tmat_ctx* ctx, int B, int S, int C, int N, int relu_in, int relu_out,
-                                  uint64_t seed, double* max_abs_diff, double* max_abs_ref);
 /* FLOPs (2*MAC of every convolution as written in models.py:110-171) of one patch */
 int tmat_unet_flops_per_patch(const tmat_unet_desc* desc, double* flops);
 
@@ -249,6 +227,27 @@ int tmat_remove_small_islands_host(tmat_ctx* ctx, const uint8_t* mask_host, int 
                                    int connectivity1, uint8_t* out_host);
 /* transforms.py:291-303 regionprops_image(mask, 'area'): float64 image of component areas */
 int tmat_area_image_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W, double* out_host);
+/* the same for the area-like properties the reference's callers use (scripts/compute_branches.py:276-277):
+ * prop 0 = 'area', 1 = 'equivalent_diameter_area' (= sqrt(4*area/pi), as skimage.measure.regionprops). */
+int tmat_region_prop_image_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W, int prop,
+                                double* out_host);
+/* Rank filter of a boolean image under an arbitrary footprint (fh x fw bytes, non-zero = member, both odd;
+ * centre = (fh/2, fw/2)), for the footprints the specialised kernels above do not cover:
+ * op 0 = skimage.filters.median on a bool image (-> scipy.ndimage.median_filter, mode 'nearest';
+ *        transforms.py:323 with a caller-supplied footprint), border_value ignored;
+ * op 1 = skimage.morphology.binary_erosion (-> scipy.ndimage.binary_erosion(border_value)). */
+int tmat_footprint_filter_dev(tmat_ctx* ctx, const uint8_t* mask_dev, int H, int W,
+                              const uint8_t* footprint_host, int fh, int fw, int op, int border_value,
+                              uint8_t* out_dev, void* stream);
+int tmat_footprint_filter_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W,
+                               const uint8_t* footprint_host, int fh, int fw, int op, int border_value,
+                               uint8_t* out_host);
+/* The 256-entry deletability table of the 2-D thinning (csrc/skeleton_lut.inc: derived from the
+ * Zhang-Suen conditions; parity with scikit-image 0.22's hard-coded table is UNPINNED).  set
+ * replaces it process-wide (entries 0..3; index = neighbour code, bit0 NW,1 N,2 NE,3 E,4 SE,5 S,
+ * 6 SW,7 W; 1 = deleted in sub-pass 1, 2 = in sub-pass 2, 3 = either); get reads it back. */
+int tmat_skeleton_lut_set(const uint8_t* lut256);
+int tmat_skeleton_lut_get(uint8_t* lut256);
 /* host variants of the primitives (used by the Python mirror of transforms.py) */
 int tmat_median_disk2_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W, uint8_t* out_host);
 int tmat_erode_disk_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W, int r,

@@ -13,10 +13,15 @@ Restates ``transforms.py:170-206`` (``remove_small_islands``), ``:209-288``
   skimage.morphology.binary_erosion          -> ndi.binary_erosion(border_value=True)
   skimage.morphology.disk(r)                 -> x^2 + y^2 <= r^2
 
-scikit-image is not installable in the build container, so these primitives are
+scikit-image is not installable in the build container and is absent from the GPU box's
+image (probed in round 2: ``import skimage`` fails there too), so these primitives are
 **parity unpinned**; the *composition* in ``filter_branch_seg_mask`` is pinned by
 running the reference's own ``transforms.py`` over these primitives
-(tests/golden/make_golden.py).
+(tests/golden/make_golden.py).  The thinning table in particular is DERIVED from the
+published Zhang-Suen conditions, not transcribed from scikit-image's hard-coded table
+(``_skeletonize_cy.pyx``); it lives in one data file shared with the CUDA path
+(``tmat_b200/csrc/skeleton_lut.inc``) so that a corrected table changes kernel, oracle
+and fixtures together.
 """
 import numpy as np
 from scipy import ndimage as ndi
@@ -95,7 +100,19 @@ def _zs_lut():
     return lut
 
 
-ZS_LUT = _zs_lut()
+def _shared_lut():
+    """The ONE table constant shared with the CUDA path (tmat_b200/csrc/skeleton_lut.inc): the oracle reads the
+    data file, it does not import product code.  tests/test_oracle_golden.py checks it equals _zs_lut()."""
+    import os
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tmat_b200", "csrc",
+                        "skeleton_lut.inc")
+    body = open(path).read().split("*/", 1)[1]
+    vals = [int(t) for t in body.replace(",", " ").split()]
+    assert len(vals) == 256 and all(0 <= v <= 3 for v in vals), len(vals)
+    return np.array(vals, dtype=np.uint8)
+
+
+ZS_LUT = _shared_lut()
 
 
 def neighbour_code(img):

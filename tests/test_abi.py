@@ -12,8 +12,8 @@ from tmat_b200 import _ffi
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def _declared():
-    src = open(os.path.join(ROOT, "include", "tmat_b200.h")).read()
+def _declared(header="tmat_b200.h"):
+    src = open(os.path.join(ROOT, "include", header)).read()
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
     return sorted(set(re.findall(r"\b(tmat_[a-z0-9_]+)\s*\(", src)))
 
@@ -27,6 +27,31 @@ def test_header_symbols_exported_and_bound():
     bound = set(_ffi.SIGNATURES) | set(_ffi._SPECIAL)
     assert set(names) == bound, set(names) ^ bound
     assert L.tmat_version() >= 100
+    # the test hooks live in their own header and are not part of the boundary
+    dbg = _declared("tmat_b200_debug.h")
+    assert all("debug" in n for n in dbg) and set(dbg) == set(_ffi.DEBUG_SIGNATURES), dbg
+    assert not any("debug" in n for n in names)
+    for n in dbg:
+        assert hasattr(L, n), n
+
+
+def test_skeleton_lut_is_one_shared_constant():
+    """csrc/skeleton_lut.inc is compiled into the library and parsed by the oracle: one table, two readers."""
+    from oracle import morphology as om
+    got = np.zeros(256, np.uint8)
+    _ffi.check(_ffi.lib().tmat_skeleton_lut_get(_ffi.ptr(got)))
+    assert np.array_equal(got, om.ZS_LUT)
+    alt = got.copy()
+    alt[3] = 1
+    _ffi.check(_ffi.lib().tmat_skeleton_lut_set(_ffi.ptr(alt)))
+    back = np.zeros(256, np.uint8)
+    _ffi.check(_ffi.lib().tmat_skeleton_lut_get(_ffi.ptr(back)))
+    assert np.array_equal(back, alt)
+    _ffi.check(_ffi.lib().tmat_skeleton_lut_set(_ffi.ptr(got)))
+    bad = got.copy()
+    bad[7] = 9
+    with pytest.raises(_ffi.TmatError):
+        _ffi.check(_ffi.lib().tmat_skeleton_lut_set(_ffi.ptr(bad)))
 
 
 def test_spline_window_matches_reference_golden(golden):

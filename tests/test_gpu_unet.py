@@ -152,5 +152,20 @@ def test_whole_branch_mask_path_vs_oracle():
     assert np.abs(pred - ref_pred).max() < PROB_TOL
     # downstream of the threshold the stage is bit-exact: same cleanup of OUR thresholded prediction
     assert np.array_equal(mask, om.filter_branch_seg_mask(pred > 0.5))
+    # against the oracle's own chain: the cleanup is non-local (a flipped pixel can remove or keep a whole
+    # component), so compare component-wise -- components of either cleaned mask that contain no pixel the oracle
+    # decides by less than the tolerance must be identical; the raw agreement is printed and bounded as well
     ref_mask = om.filter_branch_seg_mask(ref_pred > 0.5)
-    assert (mask == ref_mask).mean() >= 0.999 or np.abs(ref_pred - 0.5).min() < PROB_TOL
+    unsure = np.abs(ref_pred - 0.5) <= PROB_TOL
+    assert ((pred > 0.5) == (ref_pred > 0.5))[~unsure].all()
+    lab, n = om.label((pred > 0.5) | (ref_pred > 0.5) | unsure, 2)
+    tainted = np.zeros(n + 1, bool)
+    tainted[np.unique(lab[unsure])] = True
+    tainted[0] = False
+    clean = ~tainted[lab]
+    raw = float((mask == ref_mask).mean())
+    print(f"whole path: raw mask agreement {raw:.6f}; {int(unsure.sum())} pixels within {PROB_TOL} of 0.5; "
+          f"{int(clean.sum())} of {clean.size} pixels in components without such a pixel")
+    assert np.array_equal(mask[clean], ref_mask[clean])
+    assert clean.mean() > 0.5          # the comparison is not vacuous
+    assert raw >= 0.999 or unsure.any()

@@ -80,9 +80,14 @@ def test_morphology_composition_matches_reference(golden):
 
 
 def test_zhang_suen_lut_properties():
+    """The shared table (tmat_b200/csrc/skeleton_lut.inc) is what the Zhang-Suen conditions give.  This pins the
+    data file to its stated derivation -- NOT to scikit-image's shipped table (parity unpinned, see the file)."""
     lut = om.ZS_LUT
+    assert np.array_equal(lut, om._zs_lut())
     assert lut[0] == 0 and lut[255] == 0          # isolated / interior pixels survive
-    assert lut[0b00000011] == 3                    # end point with NW+N neighbours
+    rot = lambda v: ((v << 4) | (v >> 4)) & 255   # 180-degree rotation swaps the two sub-passes
+    swap = {0: 0, 1: 2, 2: 1, 3: 3}
+    assert all(swap[int(lut[v])] == lut[rot(v)] for v in range(256))
     sk = om.skeletonize(helpers.synth_mask(120, 130, 5))
     # idempotent, subset of the input, and thin (no 2x2 block survives)
     assert np.array_equal(om.skeletonize(sk), sk)

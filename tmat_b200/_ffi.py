@@ -66,14 +66,6 @@ SIGNATURES = {
     "tmat_stp_predict_rows_dev": [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, C.POINTER(_i), _vp],
     "tmat_stp_predict_rows_host": [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, C.POINTER(_i)],
     "tmat_stp_rows_patches": [_i, _i, _i, _i, _i, _i, _vp, _i, C.POINTER(_i)],
-    "tmat_unet_debug_tap": [_vp, _vp, C.c_char_p, _vp, _i64, C.POINTER(_i64)],
-    "tmat_debug_conv_selftest": [_vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, C.c_uint64,
-                                 C.POINTER(C.c_double), C.POINTER(C.c_double)],
-    "tmat_debug_set_halo_mode": [_i],
-    "tmat_debug_dwpw_selftest": [_vp, _i, _i, _i, _i, _i, _i, C.c_uint64, C.POINTER(C.c_double),
-                                 C.POINTER(C.c_double)],
-    "tmat_debug_dwpw_pool_selftest": [_vp, _i, _i, _i, _i, _i, _i, C.c_uint64, C.POINTER(C.c_double),
-                                      C.POINTER(C.c_double)],
     "tmat_unet_flops_per_patch": [C.POINTER(UnetDesc), C.POINTER(C.c_double)],
     "tmat_gmm2_threshold_dev": [_vp, _vp, _i64, C.c_double, _vp, _vp, _vp],
     "tmat_gmm2_threshold_host": [_vp, _vp, _i64, C.c_double, _vp, _vp],
@@ -95,11 +87,27 @@ SIGNATURES = {
     "tmat_filter_branch_seg_mask_host": [_vp, _vp, _i, _i, _i, _i, _vp],
     "tmat_remove_small_islands_host": [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp],
     "tmat_area_image_host": [_vp, _vp, _i, _i, _vp],
+    "tmat_region_prop_image_host": [_vp, _vp, _i, _i, _i, _vp],
+    "tmat_footprint_filter_dev": [_vp, _vp, _i, _i, _vp, _i, _i, _i, _i, _vp, _vp],
+    "tmat_footprint_filter_host": [_vp, _vp, _i, _i, _vp, _i, _i, _i, _i, _vp],
+    "tmat_skeleton_lut_set": [_vp],
+    "tmat_skeleton_lut_get": [_vp],
     "tmat_median_disk2_host": [_vp, _vp, _i, _i, _vp],
     "tmat_erode_disk_host": [_vp, _vp, _i, _i, _i, _i, _vp],
     "tmat_label_host": [_vp, _vp, _i, _i, _i, _vp, _pi],
     "tmat_skeletonize_host": [_vp, _vp, _i, _i, _vp, _pi],
     "tmat_branch_mask_dev": [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp],
+}
+# include/tmat_b200_debug.h: test hooks, not part of the drop-in boundary
+DEBUG_SIGNATURES = {
+    "tmat_unet_debug_tap": [_vp, _vp, C.c_char_p, _vp, _i64, C.POINTER(_i64)],
+    "tmat_debug_conv_selftest": [_vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, C.c_uint64,
+                                 C.POINTER(C.c_double), C.POINTER(C.c_double)],
+    "tmat_debug_set_halo_mode": [_i],
+    "tmat_debug_dwpw_selftest": [_vp, _i, _i, _i, _i, _i, _i, C.c_uint64, C.POINTER(C.c_double),
+                                 C.POINTER(C.c_double)],
+    "tmat_debug_dwpw_pool_selftest": [_vp, _i, _i, _i, _i, _i, _i, C.c_uint64, C.POINTER(C.c_double),
+                                      C.POINTER(C.c_double)],
 }
 _SPECIAL = {"tmat_version": ([], _i), "tmat_last_error": ([], C.c_char_p)}
 
@@ -113,7 +121,7 @@ def lib():
                 from . import build as _build
                 _build.build()
             L = C.CDLL(LIB_PATH)
-            for name, args in SIGNATURES.items():
+            for name, args in list(SIGNATURES.items()) + list(DEBUG_SIGNATURES.items()):
                 f = getattr(L, name)
                 f.argtypes = args
                 f.restype = _i

@@ -10,6 +10,7 @@
 #include <string>
 #include <map>
 #include "../../include/tmat_b200.h"
+#include "../../include/tmat_b200_debug.h"
 
 #define TMAT_SM_TARGET 100
 

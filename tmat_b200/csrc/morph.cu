@@ -6,6 +6,7 @@
 // All integer work: bit-exact.  Masks are uint8 images; any non-zero value is foreground.
 #include "common.cuh"
 #include <math.h>
+#include <string.h>
 #include <algorithm>
 
 namespace {
@@ -52,6 +53,31 @@ __global__ void __launch_bounds__(ER_T * 8) erode_disk_kernel(const uint8_t* __r
     }
     out[(int64_t)y * W + x] = (uint8_t)ok;
   }
+}
+
+// ---- rank filter of a boolean image under an arbitrary footprint ------------------------------------------
+// offs: (dy, dx) of the nfp footprint members relative to the centre.  clamp != 0: indices clamped to the image
+// (ndimage mode 'nearest', the median); else pixels outside count as border_value (binary_erosion).
+// out = (number of set pixels under the footprint) >= need.
+__global__ void __launch_bounds__(256) footprint_count_kernel(const uint8_t* __restrict__ in, int H, int W,
+                                                              const short2* __restrict__ offs, int nfp, int clamp,
+                                                              int border_value, int need, uint8_t* __restrict__ out) {
+  int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  if (x >= W) return;
+  int cnt = 0;
+  for (int k = 0; k < nfp; ++k) {
+    short2 o = offs[k];
+    int yy = y + o.x, xx = x + o.y;
+    if (clamp) {
+      yy = min(max(yy, 0), H - 1);
+      xx = min(max(xx, 0), W - 1);
+      cnt += in[(int64_t)yy * W + xx] != 0;
+    } else {
+      bool inside = yy >= 0 && yy < H && xx >= 0 && xx < W;
+      cnt += inside ? (in[(int64_t)yy * W + xx] != 0) : (border_value != 0);
+    }
+  }
+  out[(int64_t)y * W + x] = cnt >= need;
 }
 
 // ---- connected components: union-find on pixel indices; the root of a component is its first
@@ -298,28 +324,23 @@ __global__ void __launch_bounds__(256) area_image_kernel(const int* __restrict__
 }  // namespace
 
 // ---- host side --------------------------------------------------------------------------------------
-static const uint8_t* zs_lut_host() {
-  // Zhang-Suen deletability per 8-neighbour code (bit0 NW, 1 N, 2 NE, 3 E, 4 SE, 5 S, 6 SW, 7 W):
-  // bit 1 = deletable in sub-pass 1, bit 2 = deletable in sub-pass 2.
-  static uint8_t lut[256];
-  static bool init = false;
-  if (!init) {
-    for (int v = 0; v < 256; ++v) {
-      int nw = v & 1, n = (v >> 1) & 1, ne = (v >> 2) & 1, e = (v >> 3) & 1, se = (v >> 4) & 1, s = (v >> 5) & 1,
-          sw = (v >> 6) & 1, w = (v >> 7) & 1;
-      int ring[8] = {n, ne, e, se, s, sw, w, nw};   // P2..P9
-      int b = 0, a = 0;
-      for (int i = 0; i < 8; ++i) { b += ring[i]; a += (ring[i] == 0 && ring[(i + 1) & 7] == 1); }
-      uint8_t r = 0;
-      if (b >= 2 && b <= 6 && a == 1) {
-        if (n * e * s == 0 && e * s * w == 0) r |= 1;
-        if (n * e * w == 0 && n * s * w == 0) r |= 2;
-      }
-      lut[v] = r;
-    }
-    init = true;
-  }
-  return lut;
+// The deletability table is data, not code: csrc/skeleton_lut.inc (shared with oracle/morphology.py; derived from the
+// Zhang-Suen conditions, parity with scikit-image's shipped table UNPINNED -- see the file).  tmat_skeleton_lut_set
+// replaces it process-wide at run time.
+static uint8_t g_zs_lut[256] = {
+#include "skeleton_lut.inc"
+};
+static const uint8_t* zs_lut_host() { return g_zs_lut; }
+extern "C" int tmat_skeleton_lut_set(const uint8_t* lut256) {
+  TMAT_REQUIRE(lut256, "tmat_skeleton_lut_set: NULL table");
+  for (int v = 0; v < 256; ++v) TMAT_REQUIRE(lut256[v] <= 3, "tmat_skeleton_lut_set: entry %d = %d not in 0..3", v, lut256[v]);
+  memcpy(g_zs_lut, lut256, 256);
+  return TMAT_OK;
+}
+extern "C" int tmat_skeleton_lut_get(uint8_t* lut256) {
+  TMAT_REQUIRE(lut256, "tmat_skeleton_lut_get: NULL output");
+  memcpy(lut256, g_zs_lut, 256);
+  return TMAT_OK;
 }
 
 static inline dim3 grid2d(int H, int W) { return dim3(cdiv(W, 256), H); }
@@ -335,6 +356,32 @@ int erode_disk(tmat_ctx* ctx, const uint8_t* in, int H, int W, int r, int border
 
 int median_disk2(tmat_ctx* ctx, const uint8_t* in, int H, int W, uint8_t* out, cudaStream_t st) {
   median_disk2_kernel<<<grid2d(H, W), 256, 0, st>>>(in, H, W, out);
+  KERNEL_CHECK(ctx);
+  return TMAT_OK;
+}
+
+// op 0: median of a bool image (element of rank nfp/2 of the sorted neighbourhood is 1 iff at least nfp - nfp/2
+// members are set); op 1: erosion (all members set).
+int footprint_filter(tmat_ctx* ctx, const uint8_t* in, int H, int W, const uint8_t* fp_host, int fh, int fw, int op,
+                     int border_value, uint8_t* out, cudaStream_t st) {
+  TMAT_REQUIRE(fp_host && fh >= 1 && fw >= 1 && (fh & 1) && (fw & 1) && fh <= 255 && fw <= 255,
+               "footprint_filter: footprint must be odd-sized, got %dx%d", fh, fw);
+  TMAT_REQUIRE(op == 0 || op == 1, "footprint_filter: op %d", op);
+  std::vector<short2> offs;
+  for (int r = 0; r < fh; ++r)
+    for (int c = 0; c < fw; ++c)
+      if (fp_host[r * fw + c]) offs.push_back(make_short2((short)(r - fh / 2), (short)(c - fw / 2)));
+  const int nfp = (int)offs.size();
+  TMAT_REQUIRE(nfp >= 1, "footprint_filter: empty footprint");
+  short2* d_offs;
+  TMAT_TRY(arena_get(ctx, (size_t)nfp, &d_offs));
+  // the offsets are small: staged through the context's pinned buffer so the copy is stream-ordered
+  TMAT_REQUIRE((size_t)nfp * sizeof(short2) <= 4096, "footprint_filter: footprint with %d members is too large", nfp);
+  CUDA_TRY(cudaStreamSynchronize(st));
+  memcpy(ctx->pinned, offs.data(), (size_t)nfp * sizeof(short2));
+  CUDA_TRY(cudaMemcpyAsync(d_offs, ctx->pinned, (size_t)nfp * sizeof(short2), cudaMemcpyHostToDevice, st));
+  const int need = op == 0 ? nfp - nfp / 2 : nfp;
+  footprint_count_kernel<<<grid2d(H, W), 256, 0, st>>>(in, H, W, d_offs, nfp, op == 0, border_value, need, out);
   KERNEL_CHECK(ctx);
   return TMAT_OK;
 }
@@ -478,6 +525,16 @@ extern "C" int tmat_erode_disk_dev(tmat_ctx* ctx, const uint8_t* mask_dev, int H
   return erode_disk(ctx, mask_dev, H, W, r, border_value, out_dev, as_stream(stream));
 }
 
+extern "C" int tmat_footprint_filter_dev(tmat_ctx* ctx, const uint8_t* mask_dev, int H, int W,
+                                         const uint8_t* footprint_host, int fh, int fw, int op, int border_value,
+                                         uint8_t* out_dev, void* stream) {
+  MORPH_ARGS_OK("tmat_footprint_filter");
+  TMAT_REQUIRE(out_dev && out_dev != mask_dev, "tmat_footprint_filter: out must be a distinct buffer");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  TMAT_TRY(arena_reset(ctx));
+  return footprint_filter(ctx, mask_dev, H, W, footprint_host, fh, fw, op, border_value, out_dev, as_stream(stream));
+}
+
 extern "C" int tmat_label_dev(tmat_ctx* ctx, const uint8_t* mask_dev, int H, int W, int connectivity,
                               int32_t* labels_dev, int* n_labels, void* stream) {
   MORPH_ARGS_OK("tmat_label");
@@ -555,6 +612,13 @@ extern "C" int tmat_erode_disk_host(tmat_ctx* ctx, const uint8_t* mask_host, int
                                     uint8_t* out_host) {
   return with_host_mask(ctx, mask_host, H, W, out_host,
                         [&](uint8_t* a, uint8_t* b) { return erode_disk(ctx, a, H, W, r, border_value, b, 0); });
+}
+extern "C" int tmat_footprint_filter_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W,
+                                          const uint8_t* footprint_host, int fh, int fw, int op, int border_value,
+                                          uint8_t* out_host) {
+  return with_host_mask(ctx, mask_host, H, W, out_host, [&](uint8_t* a, uint8_t* b) {
+    return footprint_filter(ctx, a, H, W, footprint_host, fh, fw, op, border_value, b, 0);
+  });
 }
 extern "C" int tmat_skeletonize_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W, uint8_t* out_host,
                                      int* iterations) {

@@ -141,19 +141,30 @@ class CudaUNet:
         return out
 
 
+RANDOM_INIT = "random"    # explicit opt-in for a freshly initialised model (bench, tests)
+
+
 def load_checkpoint(checkpoint_file, filter_counts):
-    """Weights as a name -> array dict.  ``.npz`` files use the names of :func:`weight_names`;
-    ``None`` gives a random initialisation (the reference's trained ``checkpoint_1.h5`` is not
-    distributed with its repository)."""
-    if checkpoint_file is None:
-        return random_init_weights(filter_counts)
+    """Weights as a name -> array dict.  ``.npz`` files use the names of :func:`weight_names`; a dict is taken
+    as is; the string ``"random"`` (or ``"random:<seed>"``) is the explicit opt-in for a Keras-default random
+    initialisation.  Anything else raises, as ``model.load_weights`` does in the reference (models.py:622) --
+    a missing checkpoint must never silently give a random-init model."""
     if isinstance(checkpoint_file, dict):
         return checkpoint_file
-    if str(checkpoint_file).endswith(".npz"):
-        with np.load(checkpoint_file) as z:
-            return {k: z[k] for k in z.files}
-    raise ValueError("checkpoint must be a .npz with tmat_b200.models.weight_names() keys "
-                     "(convert a Keras .h5 with model.get_weights() in layer order)")
+    name = "" if checkpoint_file is None else os.fspath(checkpoint_file)
+    if name == RANDOM_INIT or name.startswith(RANDOM_INIT + ":"):
+        seed = int(name.split(":", 1)[1]) if ":" in name else 0
+        return random_init_weights(filter_counts, seed=seed)
+    how = ("convert the Keras checkpoint once: np.savez(path, **dict(zip([n for n, _ in "
+           "tmat_b200.models.weight_names(filter_counts)], keras_model.get_weights()))) -- see INTEGRATION.md")
+    if not name.endswith(".npz"):
+        raise ValueError(f"checkpoint {name!r}: libtmat_b200 reads .npz checkpoints with "
+                         f"tmat_b200.models.weight_names() keys (no h5py/TensorFlow here); {how}; "
+                         f"pass checkpoint_file='random' for an explicitly random-initialised model")
+    if not os.path.exists(name):
+        raise FileNotFoundError(f"checkpoint {name!r} does not exist; {how}")
+    with np.load(name) as z:
+        return {k: z[k] for k in z.files}
 
 
 class UNetXceptionPatchSegmentor:
@@ -178,13 +189,21 @@ class UNetXceptionPatchSegmentor:
         return predict_img_with_smooth_windowing(x, self.patch_size, 2, self.model.predict)
 
 
-def get_unet_patch_segmentor_from_cfg(cfg_json, checkpoint_file=None):
-    """models.py:656-684: build the segmentor from the reference's JSON config."""
+def get_unet_patch_segmentor_from_cfg(cfg_json, checkpoint_file=None, models_dir=None):
+    """models.py:656-684: build the segmentor from the reference's JSON config.  The checkpoint is looked up as
+    the reference does, ``<MODEL_TRAINING_DIR>/binary_segmentation/checkpoints/<cfg["checkpoint_file"]>``
+    (``models_dir`` stands in for ``defs.MODEL_TRAINING_DIR``; default: two levels above the config file, which is
+    where the reference keeps ``configs/``), with the ``.h5`` suffix replaced by ``.npz``.  A missing file raises.
+    ``checkpoint_file`` overrides the lookup (a path, a weight dict, or ``"random"``)."""
     with open(cfg_json, "r") as f:
         cfg = json.load(f)
     ckpt = checkpoint_file
-    if ckpt is None and cfg.get("checkpoint_file"):
-        cand = os.path.join(os.path.dirname(cfg_json), "..", "checkpoints", cfg["checkpoint_file"])
-        ckpt = cand if os.path.exists(cand) and cand.endswith(".npz") else None
-    return UNetXceptionPatchSegmentor(cfg["patch_size"], ckpt, cfg["filter_counts"], cfg.get("ds_ratio", 0.5),
-                                      cfg.get("norm_mean"), cfg.get("norm_std"), cfg.get("channels", 1))
+    if ckpt is None:
+        root = models_dir or os.path.join(os.path.dirname(os.path.abspath(cfg_json)), "..", "..")
+        name = cfg["checkpoint_file"]
+        if name.endswith((".h5", ".hdf5", ".keras")):
+            name = name.rsplit(".", 1)[0] + ".npz"
+        ckpt = os.path.normpath(os.path.join(root, "binary_segmentation", "checkpoints", name))
+    return UNetXceptionPatchSegmentor(cfg["patch_size"], ckpt, cfg["filter_counts"], ds_ratio=cfg.get("ds_ratio", 1),
+                                      norm_mean=cfg.get("norm_mean", None), norm_std=cfg.get("norm_std", None),
+                                      channels=cfg.get("channels", 1))

@@ -1,7 +1,9 @@
 """Mask cleanup on the B200: drop-in for the inference-side functions of the reference's
 ``fl_tissue_model_tools/transforms.py`` (``remove_small_islands:170``, ``regionprops_image:291``,
 ``filter_branch_seg_mask:306``) plus the scikit-image primitives they are built from, all running in
-``csrc/morph.cu``.  Integer work, bit-exact against the reference."""
+``csrc/morph.cu``.  Integer work, bit-exact against ``oracle/morphology.py``; the scikit-image primitives that
+oracle restates (notably the thinning table, ``csrc/skeleton_lut.inc``) are PARITY UNPINNED -- scikit-image is
+installable neither in the build container nor on the GPU box."""
 import ctypes as C
 
 import numpy as np
@@ -27,23 +29,34 @@ def _is_disk(footprint, r):
     return fp.shape == (2 * r + 1, 2 * r + 1) and np.array_equal(fp != 0, disk(r) != 0)
 
 
+def _footprint_filter(m, footprint, op):
+    fp = np.ascontiguousarray(np.asarray(footprint) != 0, dtype=np.uint8)
+    if fp.ndim != 2 or fp.shape[0] % 2 == 0 or fp.shape[1] % 2 == 0:
+        raise NotImplementedError(f"footprint must be 2-D with odd sides, got shape {fp.shape}")
+    out = np.empty_like(m)
+    _ffi.check(_ffi.lib().tmat_footprint_filter_host(_ffi.default_context().handle, _ffi.ptr(m), *m.shape,
+                                                     _ffi.ptr(fp), fp.shape[0], fp.shape[1], op, 1, _ffi.ptr(out)))
+    return out
+
+
 def median_filter(mask, footprint=None):
-    """skimage.filters.median(bool mask, disk(2)) (transforms.py:323)."""
-    if footprint is not None and not _is_disk(footprint, 2):
-        raise NotImplementedError("libtmat_b200 implements the reference's disk(2) median footprint")
+    """skimage.filters.median(bool mask, footprint) (transforms.py:323); disk(2) -- the reference's default -- runs
+    the specialised kernel, any other odd-sized footprint the generic rank kernel."""
     m = _mask_u8(mask)
+    if footprint is not None and not _is_disk(footprint, 2):
+        return _footprint_filter(m, footprint, 0).astype(bool)
     out = np.empty_like(m)
     _ffi.check(_ffi.lib().tmat_median_disk2_host(_ffi.default_context().handle, _ffi.ptr(m), *m.shape, _ffi.ptr(out)))
     return out.astype(bool)
 
 
 def binary_erosion(mask, footprint):
-    """skimage.morphology.binary_erosion(mask, disk(r)) (well_mask_generation.py:275)."""
+    """skimage.morphology.binary_erosion(mask, footprint) (well_mask_generation.py:275; border_value=True)."""
     fp = np.asarray(footprint)
-    r = (fp.shape[0] - 1) // 2
-    if not _is_disk(fp, r):
-        raise NotImplementedError("libtmat_b200 erodes with disk footprints")
     m = _mask_u8(mask)
+    r = (fp.shape[0] - 1) // 2
+    if fp.ndim != 2 or not _is_disk(fp, r) or r > 8:
+        return _footprint_filter(m, fp, 1).astype(bool)
     out = np.empty_like(m)
     _ffi.check(_ffi.lib().tmat_erode_disk_host(_ffi.default_context().handle, _ffi.ptr(m), *m.shape, r, 1, _ffi.ptr(out)))
     return out.astype(bool)
@@ -82,13 +95,19 @@ def remove_small_islands(mask, min_area0=100, min_area1=100, connectivity0=1, co
     return out.astype(m.dtype)
 
 
+_REGION_PROPS = {"area": 0, "equivalent_diameter_area": 1, "equivalent_diameter": 1}
+
+
 def regionprops_image(mask, prop):
-    """transforms.py:291-303.  ``area`` is computed on the GPU; other properties are outside the hot path."""
-    if prop != "area":
-        raise NotImplementedError(f"regionprops_image(prop={prop!r}): only 'area' is on the accelerated path")
+    """transforms.py:291-303.  The area-like properties (``area``, ``equivalent_diameter_area`` -- the one
+    compute_branches.py:277 asks for) are computed on the GPU; moment-based ones (``eccentricity``, :276) are
+    SURVEY 8(f) "next" and raise."""
+    if prop not in _REGION_PROPS:
+        raise NotImplementedError(f"regionprops_image(prop={prop!r}): built properties are {sorted(_REGION_PROPS)}")
     m = _mask_u8(mask)
     out = np.empty(m.shape, dtype=np.float64)
-    _ffi.check(_ffi.lib().tmat_area_image_host(_ffi.default_context().handle, _ffi.ptr(m), *m.shape, _ffi.ptr(out)))
+    _ffi.check(_ffi.lib().tmat_region_prop_image_host(_ffi.default_context().handle, _ffi.ptr(m), *m.shape,
+                                                      _REGION_PROPS[prop], _ffi.ptr(out)))
     return out
 
 
@@ -96,14 +115,27 @@ _DISK2 = object()
 
 
 def filter_branch_seg_mask(mask, footprint=_DISK2, remove_isolated=True):
-    """transforms.py:306-361.  Returns the cleaned boolean mask (the reference mutates and returns the
-    median-filtered copy; with ``footprint=None`` it mutates the caller's array -- here the input is
-    never modified)."""
+    """transforms.py:306-361.  Returns the cleaned boolean mask.  Ownership as in the reference: with a
+    footprint the input is left alone (the reference mutates the median-filtered copy, :323); with
+    ``footprint=None`` the CALLER'S array is cleaned in place and returned (:356 writes into ``mask``)."""
     use_median = footprint is not None
-    if use_median and footprint is not _DISK2 and not _is_disk(footprint, 2):
-        raise NotImplementedError("libtmat_b200 implements the reference's default disk(2) footprint")
     m = _mask_u8(mask)
+    if use_median and footprint is not _DISK2 and not _is_disk(footprint, 2):
+        m = _footprint_filter(m, footprint, 0)          # caller-supplied footprint: generic rank kernel first
+        use_median = False
     out = np.empty_like(m)
     _ffi.check(_ffi.lib().tmat_filter_branch_seg_mask_host(_ffi.default_context().handle, _ffi.ptr(m), *m.shape,
                                                            int(use_median), int(bool(remove_isolated)), _ffi.ptr(out)))
+    if footprint is None and isinstance(mask, np.ndarray) and mask.flags.writeable:
+        mask[...] = out.astype(mask.dtype)
+        return mask
     return out.astype(bool)
+
+
+def set_skeletonize_lut(lut):
+    """Replace the thinning table process-wide (256 entries in 0..3, layout of csrc/skeleton_lut.inc) -- for a
+    maintainer who can read scikit-image's shipped table (scripts/extract_skimage_lut.py)."""
+    t = np.ascontiguousarray(lut, dtype=np.uint8)
+    if t.shape != (256,):
+        raise ValueError("expected 256 entries")
+    _ffi.check(_ffi.lib().tmat_skeleton_lut_set(_ffi.ptr(t)))
