@@ -257,6 +257,42 @@ int tmat_label_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W, int c
 int tmat_skeletonize_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W, uint8_t* out_host,
                           int* iterations);
 
+/* ---- centerline weighting handed to the Morse graph ------------------ */
+/* scipy.ndimage.distance_transform_edt(mask) (scripts/compute_branches.py:342; also the `dist` that
+ * skimage.morphology.medial_axis(return_distance=True) returns, :341): float64 distance of every non-zero pixel to
+ * the nearest zero pixel, exact (sqrt of the integer squared distance).  invert != 0: transform of logical_not(mask).
+ * An image without a zero pixel gives +inf everywhere (scipy's result is undefined there). */
+int tmat_distance_transform_edt_dev(tmat_ctx* ctx, const uint8_t* mask_dev, int H, int W, int invert,
+                                    double* out_dev, void* stream);
+int tmat_distance_transform_edt_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W, int invert,
+                                     double* out_host);
+/* scripts/compute_branches.py:341-344: out = pred * dist / (dist + centerline_dt), dist = edt(seg_mask),
+ * centerline_dt = edt(~skel).  The skeleton is an input: medial_axis breaks ties with an unseeded RNG in the
+ * reference and is not reproducible even against itself. */
+int tmat_centerline_weight_dev(tmat_ctx* ctx, const double* pred_dev, const uint8_t* mask_dev,
+                               const uint8_t* skel_dev, int H, int W, double* out_dev, void* stream);
+int tmat_centerline_weight_host(tmat_ctx* ctx, const double* pred_host, const uint8_t* mask_host,
+                                const uint8_t* skel_host, int H, int W, double* out_host);
+
+/* ---- the resizes either side of the path ---------------------------- */
+/* mode: which library call is reproduced.
+ *   PIL_LANCZOS  Image.fromarray(float32).resize((Wout, Hout), Image.Resampling.LANCZOS)  models.py:630-634
+ *   PIL_NEAREST  Image.fromarray(float32).resize((Wout, Hout), Image.Resampling.NEAREST)  models.py:647-650
+ *                both float32 only and BIT-EXACT against Pillow (scalar C: double taps, float32 intermediate);
+ *   CV_LINEAR    cv2.resize(img, (Wout, Hout)) -- what scripts/compute_cell_area.py:53-56 really calls: its
+ *                cv2.INTER_AREA lands in the positional `dst` slot;
+ *   CV_LANCZOS4  cv2.resize(img, (Wout, Hout), interpolation=cv2.INTER_LANCZOS4)  scripts/compute_branches.py:309-312
+ *                uint8 / uint16 / float32; OpenCV routes these through vendor (IPP) code, so parity is a tolerance:
+ *                <= 1 grey level for integer images, 1e-5 of the range for float32. */
+#define TMAT_RESIZE_PIL_LANCZOS 0
+#define TMAT_RESIZE_PIL_NEAREST 1
+#define TMAT_RESIZE_CV_LINEAR   2
+#define TMAT_RESIZE_CV_LANCZOS4 3
+int tmat_resize_dev(tmat_ctx* ctx, const void* img_dev, int dtype, int H, int W, void* out_dev, int Hout,
+                    int Wout, int mode, void* stream);
+int tmat_resize_host(tmat_ctx* ctx, const void* img_host, int dtype, int H, int W, void* out_host, int Hout,
+                     int Wout, int mode);
+
 /* ---- whole path for one image (scripts/compute_branches.py:316-337) ------------------ */
 /* stack (Z,H,W) uint16 -> max projection (:228) -> rescale_intensity to [0,1] float32 (:316)
  * -> predict_img_with_smooth_windowing (models.py:640) -> pred > 0.5 (:334)

@@ -101,6 +101,16 @@ def gen_zproj():
         for m, f in (("min", r.proj_min), ("max", r.proj_max), ("avg", r.proj_avg), ("med", r.proj_med),
                      ("fs", r.proj_focus_stacking)):
             cases[f"{name}_{m}"] = f(st)
+    # float32 stacks: the reference's np.max/min/mean/median take any dtype and stay float32 (zstacks.py:192-249)
+    for name, (z, h, w, seed) in {"f32_odd": (5, 37, 41, 24), "f32_even": (12, 30, 52, 25), "f32_z32": (32, 24, 36, 26)}.items():
+        rng = np.random.default_rng(seed)
+        st = (helpers.synth_stack(z, h, w, seed).astype(np.float32) / np.float32(65535.0)
+              + rng.normal(0, 1e-3, (z, h, w)).astype(np.float32))
+        st[:, :4, :4] = np.float32(0.25)          # ties
+        cases[f"{name}_in"] = st
+        for m, f in (("min", r.proj_min), ("max", r.proj_max), ("avg", r.proj_avg), ("med", r.proj_med)):
+            cases[f"{name}_{m}"] = f(st)
+            assert cases[f"{name}_{m}"].dtype == np.float32
     np.savez_compressed(os.path.join(OUT, "zproj.npz"), **cases)
 
 

@@ -21,7 +21,8 @@ def test_filter_branch_seg_mask_golden(golden):
         un = _unpack(g, name)
         m = un(g[f"{name}_in"])
         assert np.array_equal(T.filter_branch_seg_mask(m), un(g[f"{name}_filter_composition"])), name
-        assert np.array_equal(T.filter_branch_seg_mask(m, None, False),
+        # footprint=None cleans the array it is given in place (transforms.py:356): hand it a copy
+        assert np.array_equal(T.filter_branch_seg_mask(m.copy(), None, False),
                               un(g[f"{name}_filter_nomedian_keepisolated_composition"])), name
         assert np.array_equal(T.remove_small_islands(m.astype(np.uint8), 30, 40, 1, 2).astype(bool),
                               un(g[f"{name}_islands_composition"])), name
@@ -43,7 +44,7 @@ def test_morphology_primitives_vs_oracle(h, w, seed):
     assert np.array_equal(sk, om.skeletonize(m)) and it == om.skeletonize.last_iterations
     for rem in (True, False):
         for fp in ("disk2", None):
-            got = T.filter_branch_seg_mask(m, T.disk(2) if fp else None, rem)
+            got = T.filter_branch_seg_mask(m.copy(), T.disk(2) if fp else None, rem)
             assert np.array_equal(got, om.filter_branch_seg_mask(m, fp, rem)), (rem, fp)
     u = m.astype(np.uint8)
     if u.min() == 0 and u.max() == 1:
@@ -173,3 +174,34 @@ def test_skeleton_lut_override_changes_the_skeleton_and_restores():
         om.ZS_LUT[:] = base
         T.set_skeletonize_lut(base)
     assert np.array_equal(T.skeletonize(m), om.skeletonize(m))
+
+
+@pytest.mark.parametrize("h,w,seed", [(64, 64, 1), (97, 131, 2), (300, 340, 3), (1, 40, 5), (40, 1, 6), (512, 512, 7)])
+def test_exact_edt_and_centerline_weighting_vs_scipy(h, w, seed):
+    """SURVEY 8(f) N1 (compute_branches.py:340-344): exact EDT pinned by scipy.ndimage.distance_transform_edt, and
+    pred * dist / (dist + centerline_dt) bit-identical to the numpy expression."""
+    from scipy import ndimage as ndi
+    from tmat_b200 import transforms as T
+    m = helpers.synth_mask(h, w, seed, density=0.15)
+    if m.all():
+        m[0, 0] = False
+    dist = ndi.distance_transform_edt(m)
+    assert np.array_equal(T.distance_transform_edt(m), dist)
+    sk = om.skeletonize(m)
+    if not sk.any():
+        sk[h // 2, w // 2] = True
+    cdt = ndi.distance_transform_edt(np.logical_not(sk))
+    assert np.array_equal(T.distance_transform_edt(sk, invert=True), cdt)
+    pred = np.random.default_rng(seed).random((h, w))
+    with np.errstate(invalid="ignore", divide="ignore"):
+        ref = pred * (dist / (dist + cdt))
+    got = T.centerline_weighting(pred, m, sk)
+    assert np.array_equal(got, ref, equal_nan=True)
+
+
+def test_edt_sparse_zeros_large_distances():
+    from scipy import ndimage as ndi
+    from tmat_b200 import transforms as T
+    m = np.ones((700, 900), bool)
+    m[13, 877] = m[650, 3] = m[300, 444] = False          # distances of several hundred pixels, columns without a zero
+    assert np.array_equal(T.distance_transform_edt(m), ndi.distance_transform_edt(m))

@@ -37,6 +37,17 @@ def _compare(out, ref, tag):
     return err, agree_raw
 
 
+def _centred(w, ws):
+    """Shift head.bias so that the oracle's median logit over three synthetic patches is 0: the blended
+    probabilities then straddle 0.5 and the mask comparison decides something (a random-init net with randomised
+    BatchNorm statistics otherwise sits on one side of the threshold everywhere)."""
+    x = np.stack([helpers.synth_projection(ws, ws, 70 + i) for i in range(3)])
+    med = float(np.median(ou.forward(w, x, return_logits=True)))
+    w = dict(w)
+    w["head.bias"] = (w["head.bias"] - np.float32(med)).astype(np.float32)
+    return w
+
+
 @pytest.fixture
 def chunk_env():
     old = os.environ.get("TMAT_CHUNK")
@@ -53,15 +64,15 @@ def test_c1_exact_config_vs_oracle(variant):
     from tmat_b200 import models
     from tmat_b200.smooth_tiled_predictions import predict_img_with_smooth_windowing
     w = (ou.make_weights(FC, seed=0) if variant == "keras_default"
-         else ou.make_weights(FC, seed=0, randomize_affine=True, head_gain=4.0))
+         else _centred(ou.make_weights(FC, seed=0, randomize_affine=True, head_gain=4.0), 320))
     img = helpers.synth_projection(1024, 1024, 1001)
     net = models.CudaUNet(w, 320, FC, impl="tc")
     out = predict_img_with_smooth_windowing(img, 320, 2, net.predict)
     ref = ostp.predict_img_with_smooth_windowing(img, 320, 2, ou.make_pred_func(w))
     _compare(out, ref, f"C1 {variant}")
     if variant == "affine_gain4":      # the spread of the probabilities makes the mask check meaningful
-        assert 0.02 < float((ref > 0.5).mean()) < 0.98
-        assert float(np.ptp(ref)) > 0.2
+        assert 0.02 < float((ref > 0.5).mean()) < 0.98, float((ref > 0.5).mean())
+        assert float(np.ptp(ref)) > 0.1, float(np.ptp(ref))
 
 
 def test_forced_multichunk_is_bit_identical(chunk_env):
@@ -85,7 +96,7 @@ def test_ws256_multichunk_vs_oracle(chunk_env):
     """C5's network (256-px windows): 600x520 image -> pad 856x776, 5x5... tiles x 8, chunks of 64."""
     from tmat_b200 import models
     from tmat_b200.smooth_tiled_predictions import predict_img_with_smooth_windowing
-    w = ou.make_weights(FC, seed=7, randomize_affine=True, head_gain=4.0)
+    w = _centred(ou.make_weights(FC, seed=7, randomize_affine=True, head_gain=2.0), 256)
     img = helpers.synth_projection(600, 520, 5001)
     net = models.CudaUNet(w, 256, FC, impl="tc")
     os.environ["TMAT_CHUNK"] = "64"

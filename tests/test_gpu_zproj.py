@@ -27,10 +27,33 @@ def test_zproj_golden_bitexact(golden):
             assert np.array_equal(out, ref), (name, m, int((out != ref).sum()))
 
 
+def test_zproj_float32_golden_bitexact(golden):
+    """float32 stacks through min/max/avg/med (numpy keeps float32); focus stacking of a float stack raises."""
+    from tmat_b200 import zstacks as z
+    g = golden("zproj")
+    for name in ("f32_odd", "f32_even", "f32_z32"):
+        st = g[f"{name}_in"]
+        for m in ("min", "max", "avg", "med"):
+            out = _fn(m)(st)
+            ref = g[f"{name}_{m}"]
+            assert out.dtype == ref.dtype == np.float32, (name, m)
+            assert np.array_equal(out, ref), (name, m, int((out != ref).sum()))
+    with pytest.raises(TypeError):
+        z.proj_focus_stacking(g["f32_odd_in"])
+    st = np.random.default_rng(1).random((70, 9, 13), dtype=np.float32)       # Z > 64: rank-selection kernel
+    for m in ("min", "max", "avg", "med"):
+        assert np.array_equal(_fn(m)(st), oz.METHODS[m](st)), m
+
+
 @pytest.mark.parametrize("shape,dtype", [((1, 5, 7), np.uint16), ((2, 33, 65), np.uint16),
                                          ((3, 64, 64), np.uint8), ((5, 70, 131), np.uint16),
                                          ((16, 96, 200), np.uint16), ((31, 40, 48), np.uint8),
-                                         ((33, 24, 40), np.uint16), ((70, 16, 24), np.uint16)])
+                                         ((33, 24, 40), np.uint16), ((70, 16, 24), np.uint16),
+                                         # the warp-tile focus kernel: several 124-column tiles, ragged last tile,
+                                         # heights off the 32-row grid, one slice, image smaller than one tile
+                                         ((9, 70, 252), np.uint16), ((4, 40, 128), np.uint16), ((6, 100, 500), np.uint16),
+                                         ((1, 33, 124), np.uint16), ((3, 8, 8), np.uint16), ((12, 65, 376), np.uint16),
+                                         ((257, 9, 12), np.uint16)])
 def test_zproj_ragged_shapes_vs_oracle(shape, dtype):
     rng = np.random.default_rng(sum(shape))
     top = np.iinfo(dtype).max

@@ -96,6 +96,12 @@ SIGNATURES = {
     "tmat_erode_disk_host": [_vp, _vp, _i, _i, _i, _i, _vp],
     "tmat_label_host": [_vp, _vp, _i, _i, _i, _vp, _pi],
     "tmat_skeletonize_host": [_vp, _vp, _i, _i, _vp, _pi],
+    "tmat_distance_transform_edt_dev": [_vp, _vp, _i, _i, _i, _vp, _vp],
+    "tmat_distance_transform_edt_host": [_vp, _vp, _i, _i, _i, _vp],
+    "tmat_centerline_weight_dev": [_vp, _vp, _vp, _vp, _i, _i, _vp, _vp],
+    "tmat_centerline_weight_host": [_vp, _vp, _vp, _vp, _i, _i, _vp],
+    "tmat_resize_dev": [_vp, _vp, _i, _i, _i, _vp, _i, _i, _i, _vp],
+    "tmat_resize_host": [_vp, _vp, _i, _i, _i, _vp, _i, _i, _i],
     "tmat_branch_mask_dev": [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp],
 }
 # include/tmat_b200_debug.h: test hooks, not part of the drop-in boundary

@@ -1,0 +1,158 @@
+// Exact Euclidean distance transform and the centerline weighting handed to the Morse graph.
+// Reference: scripts/compute_branches.py:340-344
+//     skel, dist = medial_axis(seg_mask, return_distance=True)      # dist = ndi.distance_transform_edt(seg_mask)
+//     centerline_dt = distance_transform_edt(np.logical_not(skel))
+//     relative_dt = dist / (dist + centerline_dt);   pred = pred * relative_dt
+// scipy.ndimage.distance_transform_edt returns sqrt(exact integer squared distance to the nearest zero pixel) in
+// float64, so an exact integer EDT followed by one IEEE square root is bit-identical to it.  Two separable passes:
+// nearest zero along each column (two scans), then per pixel the minimum over the row of dx^2 + g^2, searched outwards
+// and cut off as soon as dx^2 alone reaches the best value found (vessel masks: a handful of steps per pixel).
+// medial_axis itself (skimage's priority-ordered thinning with RANDOM tie-breaking, rng=None in the reference's
+// call) is not reproducible even against itself; the skeleton is an input here.
+#include "common.cuh"
+
+namespace {
+
+constexpr unsigned int EDT_INF = 0xffffffffu;
+
+// g[y][x] = distance along the column to the nearest zero pixel (EDT_INF if the column has none)
+__global__ void __launch_bounds__(128) edt_columns(const uint8_t* __restrict__ in, int H, int W, int invert,
+                                                   unsigned int* __restrict__ g) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  if (x >= W) return;
+  unsigned int d = EDT_INF;
+  for (int y = 0; y < H; ++y) {
+    const bool zero = ((in[(int64_t)y * W + x] != 0) == (invert != 0));
+    d = zero ? 0u : (d == EDT_INF ? EDT_INF : d + 1u);
+    g[(int64_t)y * W + x] = d;
+  }
+  d = EDT_INF;
+  for (int y = H - 1; y >= 0; --y) {
+    const bool zero = ((in[(int64_t)y * W + x] != 0) == (invert != 0));
+    d = zero ? 0u : (d == EDT_INF ? EDT_INF : d + 1u);
+    const int64_t i = (int64_t)y * W + x;
+    if (d < g[i]) g[i] = d;
+  }
+}
+
+__device__ __forceinline__ unsigned long long edt_row_min(const unsigned int* __restrict__ grow, int W, int x) {
+  const unsigned int g0 = grow[x];
+  unsigned long long best = g0 == EDT_INF ? ~0ull : (unsigned long long)g0 * g0;
+  for (int d = 1; d < W; ++d) {
+    const unsigned long long dd = (unsigned long long)d * d;
+    if (dd >= best) break;
+    const int xl = x - d, xr = x + d;
+    if (xl < 0 && xr >= W) break;
+    if (xl >= 0) {
+      const unsigned int gv = grow[xl];
+      if (gv != EDT_INF) { const unsigned long long c = dd + (unsigned long long)gv * gv; best = c < best ? c : best; }
+    }
+    if (xr < W) {
+      const unsigned int gv = grow[xr];
+      if (gv != EDT_INF) { const unsigned long long c = dd + (unsigned long long)gv * gv; best = c < best ? c : best; }
+    }
+  }
+  return best;
+}
+
+__global__ void __launch_bounds__(256) edt_rows(const unsigned int* __restrict__ g, int H, int W, double* __restrict__ out) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  if (x >= W) return;
+  const unsigned long long best = edt_row_min(g + (int64_t)y * W, W, x);
+  // an image without any zero pixel has no defined distance: +inf
+  out[(int64_t)y * W + x] = best == ~0ull ? __longlong_as_double(0x7ff0000000000000ll) : __dsqrt_rn((double)best);
+}
+
+// pred * dist / (dist + centerline_dt) with separately rounded IEEE operations, as numpy evaluates it
+__global__ void __launch_bounds__(256) centerline_weight(const double* __restrict__ pred, const unsigned int* __restrict__ g_mask,
+                                                         const unsigned int* __restrict__ g_skel, int H, int W,
+                                                         double* __restrict__ out) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  if (x >= W) return;
+  const int64_t i = (int64_t)y * W + x;
+  const unsigned long long a = edt_row_min(g_mask + (int64_t)y * W, W, x);
+  const unsigned long long b = edt_row_min(g_skel + (int64_t)y * W, W, x);
+  const double inf = __longlong_as_double(0x7ff0000000000000ll);
+  const double dist = a == ~0ull ? inf : __dsqrt_rn((double)a);
+  const double cdt = b == ~0ull ? inf : __dsqrt_rn((double)b);
+  const double rel = __ddiv_rn(dist, __dadd_rn(dist, cdt));
+  out[i] = __dmul_rn(pred[i], rel);
+}
+
+}  // namespace
+
+// scipy.ndimage.distance_transform_edt(mask): distance of every non-zero pixel to the nearest zero pixel.
+// invert != 0 computes the transform of logical_not(mask) without materialising it.
+extern "C" int tmat_distance_transform_edt_dev(tmat_ctx* ctx, const uint8_t* mask_dev, int H, int W, int invert,
+                                               double* out_dev, void* stream) {
+  TMAT_REQUIRE(ctx && mask_dev && out_dev && H >= 1 && W >= 1, "tmat_distance_transform_edt: bad argument");
+  TMAT_REQUIRE(H <= 65535 && W <= 65535, "tmat_distance_transform_edt: image too large");
+  TMAT_TRY(arena_reset(ctx));
+  cudaStream_t st = as_stream(stream);
+  unsigned int* g;
+  TMAT_TRY(arena_get(ctx, (size_t)H * W, &g));
+  edt_columns<<<cdiv(W, 128), 128, 0, st>>>(mask_dev, H, W, invert, g);
+  KERNEL_CHECK(ctx);
+  edt_rows<<<dim3(cdiv(W, 256), H), 256, 0, st>>>(g, H, W, out_dev);
+  KERNEL_CHECK(ctx);
+  return TMAT_OK;
+}
+
+extern "C" int tmat_distance_transform_edt_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W, int invert,
+                                                double* out_host) {
+  TMAT_REQUIRE(ctx && mask_host && out_host && H >= 1 && W >= 1, "tmat_distance_transform_edt_host: bad argument");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  const size_t n = (size_t)H * W;
+  uint8_t* d_in = nullptr;
+  double* d_out = nullptr;
+  CUDA_TRY(cudaMalloc((void**)&d_in, n));
+  if (cudaMalloc((void**)&d_out, n * 8) != cudaSuccess) { cudaFree(d_in); tmat_set_error("edt: out of memory"); return TMAT_ERR_NOMEM; }
+  int rc = cudaMemcpyAsync(d_in, mask_host, n, cudaMemcpyHostToDevice, 0) == cudaSuccess ? TMAT_OK : TMAT_ERR_CUDA;
+  if (rc == TMAT_OK) rc = tmat_distance_transform_edt_dev(ctx, d_in, H, W, invert, d_out, nullptr);
+  if (rc == TMAT_OK && cudaMemcpyAsync(out_host, d_out, n * 8, cudaMemcpyDeviceToHost, 0) != cudaSuccess) rc = TMAT_ERR_CUDA;
+  if (cudaStreamSynchronize(0) != cudaSuccess && rc == TMAT_OK) rc = TMAT_ERR_CUDA;
+  cudaFree(d_in);
+  cudaFree(d_out);
+  if (rc == TMAT_ERR_CUDA) tmat_set_error("tmat_distance_transform_edt_host: %s", cudaGetErrorString(cudaGetLastError()));
+  return rc;
+}
+
+// compute_branches.py:341-344 in one call: out = pred * edt(mask) / (edt(mask) + edt(~skel))
+extern "C" int tmat_centerline_weight_dev(tmat_ctx* ctx, const double* pred_dev, const uint8_t* mask_dev,
+                                          const uint8_t* skel_dev, int H, int W, double* out_dev, void* stream) {
+  TMAT_REQUIRE(ctx && pred_dev && mask_dev && skel_dev && out_dev && H >= 1 && W >= 1, "tmat_centerline_weight: bad argument");
+  TMAT_REQUIRE(H <= 65535 && W <= 65535, "tmat_centerline_weight: image too large");
+  TMAT_TRY(arena_reset(ctx));
+  cudaStream_t st = as_stream(stream);
+  unsigned int *gm, *gs;
+  TMAT_TRY(arena_get(ctx, (size_t)H * W, &gm));
+  TMAT_TRY(arena_get(ctx, (size_t)H * W, &gs));
+  edt_columns<<<cdiv(W, 128), 128, 0, st>>>(mask_dev, H, W, 0, gm);
+  KERNEL_CHECK(ctx);
+  edt_columns<<<cdiv(W, 128), 128, 0, st>>>(skel_dev, H, W, 1, gs);
+  KERNEL_CHECK(ctx);
+  centerline_weight<<<dim3(cdiv(W, 256), H), 256, 0, st>>>(pred_dev, gm, gs, H, W, out_dev);
+  KERNEL_CHECK(ctx);
+  return TMAT_OK;
+}
+
+extern "C" int tmat_centerline_weight_host(tmat_ctx* ctx, const double* pred_host, const uint8_t* mask_host,
+                                           const uint8_t* skel_host, int H, int W, double* out_host) {
+  TMAT_REQUIRE(ctx && pred_host && mask_host && skel_host && out_host && H >= 1 && W >= 1, "tmat_centerline_weight_host: bad argument");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  const size_t n = (size_t)H * W;
+  char* blk = nullptr;                       // pred | out | mask | skel
+  CUDA_TRY(cudaMalloc((void**)&blk, n * 18));
+  double *d_pred = (double*)blk, *d_out = (double*)(blk + n * 8);
+  uint8_t *d_mask = (uint8_t*)(blk + n * 16), *d_skel = d_mask + n;
+  int rc = TMAT_OK;
+  if (cudaMemcpyAsync(d_pred, pred_host, n * 8, cudaMemcpyHostToDevice, 0) != cudaSuccess ||
+      cudaMemcpyAsync(d_mask, mask_host, n, cudaMemcpyHostToDevice, 0) != cudaSuccess ||
+      cudaMemcpyAsync(d_skel, skel_host, n, cudaMemcpyHostToDevice, 0) != cudaSuccess) rc = TMAT_ERR_CUDA;
+  if (rc == TMAT_OK) rc = tmat_centerline_weight_dev(ctx, d_pred, d_mask, d_skel, H, W, d_out, nullptr);
+  if (rc == TMAT_OK && cudaMemcpyAsync(out_host, d_out, n * 8, cudaMemcpyDeviceToHost, 0) != cudaSuccess) rc = TMAT_ERR_CUDA;
+  if (cudaStreamSynchronize(0) != cudaSuccess && rc == TMAT_OK) rc = TMAT_ERR_CUDA;
+  cudaFree(blk);
+  if (rc == TMAT_ERR_CUDA) tmat_set_error("tmat_centerline_weight_host: %s", cudaGetErrorString(cudaGetLastError()));
+  return rc;
+}

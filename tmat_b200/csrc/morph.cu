@@ -7,6 +7,7 @@
 #include "common.cuh"
 #include <math.h>
 #include <string.h>
+#include <stdlib.h>
 #include <algorithm>
 
 namespace {

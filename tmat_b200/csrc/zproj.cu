@@ -3,6 +3,8 @@
 // All kernels are HBM-bandwidth bound streaming reductions over Z: every voxel is read once
 // (focus stacking re-reads a 4-pixel halo per tile), one output pixel is written.
 #include "common.cuh"
+#include <algorithm>
+#include <stdlib.h>
 
 namespace {
 
@@ -105,31 +107,49 @@ __global__ void __launch_bounds__(256) zproj_avg(const T* __restrict__ stack, in
 }
 
 // ------------------------------------------------------------------------------------------
-// median: in-register bitonic sorting network over Z (padded to P = next power of two with
-// 0xFFFF sentinels), two pixels packed per 32-bit register (u16x2 min/max = one instruction
-// each), two independent networks per thread for ILP.  np.median: middle value (odd Z) or the
-// float64 mean of the two middle values (even Z) -> k or k + 0.5 exactly.
+// median: in-register Batcher odd-even merge network over Z.  The stack is padded to P = next power of two with
+// 0x0000 / 0xFFFF sentinels placed so that the median pair always lands on positions P/2-1 and P/2 (for odd Z the
+// median is P/2-1 alone): only those two outputs are used, so the compiler removes every min/max that cannot
+// reach them (284 of the 382 operations of the full 32-sorter survive; the bitonic network of round 1 kept all
+// 480 and was bound by the ALU pipe at 0.44 of HBM).  Two pixels per 32-bit register (VIMNMX.U16x2), two
+// independent networks per thread.  np.median: middle value (odd Z) or the float64 mean of the two middle
+// values (even Z) -> k or k + 0.5 exactly.
 // ------------------------------------------------------------------------------------------
-template <int P>
-__device__ __forceinline__ void bitonic_sort_u16x2(uint32_t (&a)[P]) {
+// Batcher's network in its recursive form; every index is a template parameter, so the arrays stay in registers.
+struct MinMaxU16x2 {
+  __device__ __forceinline__ static void cs(uint32_t& x, uint32_t& y) {
+    const uint32_t lo = __vminu2(x, y), hi = __vmaxu2(x, y);
+    x = lo; y = hi;
+  }
+};
+struct MinMaxF32 {
+  __device__ __forceinline__ static void cs(float& x, float& y) {
+    const float lo = fminf(x, y), hi = fmaxf(x, y);
+    x = lo; y = hi;
+  }
+};
+template <typename Op, int LO, int N, int R, typename V, int P>
+__device__ __forceinline__ void oddeven_merge(V (&a)[P]) {
+  constexpr int M = 2 * R;
+  if constexpr (M < N) {
+    oddeven_merge<Op, LO, N, M>(a);
+    oddeven_merge<Op, LO + R, N, M>(a);
 #pragma unroll
-  for (int k = 2; k <= P; k <<= 1) {
-#pragma unroll
-    for (int j = k >> 1; j > 0; j >>= 1) {
-#pragma unroll
-      for (int i = 0; i < P; ++i) {
-        int l = i ^ j;
-        if (l > i) {
-          uint32_t lo = __vminu2(a[i], a[l]);
-          uint32_t hi = __vmaxu2(a[i], a[l]);
-          bool asc = ((i & k) == 0);
-          a[i] = asc ? lo : hi;
-          a[l] = asc ? hi : lo;
-        }
-      }
-    }
+    for (int i = LO + R; i + R < LO + N; i += M) Op::cs(a[i], a[i + R]);
+  } else {
+    Op::cs(a[LO], a[LO + R]);
   }
 }
+template <typename Op, int LO, int N, typename V, int P>
+__device__ __forceinline__ void oddeven_sort(V (&a)[P]) {
+  if constexpr (N > 1) {
+    oddeven_sort<Op, LO, N / 2>(a);
+    oddeven_sort<Op, LO + N / 2, N / 2>(a);
+    oddeven_merge<Op, LO, N, 1>(a);
+  }
+}
+template <int P>
+__device__ __forceinline__ void oddeven_sort_u16x2(uint32_t (&a)[P]) { oddeven_sort<MinMaxU16x2, 0, P>(a); }
 
 template <typename T, int P>
 __global__ void __launch_bounds__(128) zproj_med(const T* __restrict__ stack, int Z, int64_t n,
@@ -140,15 +160,19 @@ __global__ void __launch_bounds__(128) zproj_med(const T* __restrict__ stack, in
   uint32_t a[P], b[P];
   bool vec_ok = (i + 4 <= n) && (n % 4 == 0) &&
                 ((reinterpret_cast<uintptr_t>(stack) % (4 * sizeof(T))) == 0);
+  // P - Z sentinels: floor((P - Z) / 2) zeros in front, the rest 0xFFFF behind -> after sorting the Z samples
+  // occupy positions n_lo .. n_lo + Z - 1 and their middle sits at P/2 - 1 (and P/2 for even Z)
+  const int n_lo = (P - Z) >> 1;
 #pragma unroll
-  for (int z = 0; z < P; ++z) {
-    if (z < Z) {
+  for (int s = 0; s < P; ++s) {
+    const int z = s - n_lo;
+    if (z >= 0 && z < Z) {
       const T* p = stack + (int64_t)z * n + i;
       uint32_t v0, v1, v2, v3;
       if (vec_ok) {
         if (sizeof(T) == 2) {
           uint2 v = __ldg(reinterpret_cast<const uint2*>(p));
-          a[z] = v.x; b[z] = v.y;
+          a[s] = v.x; b[s] = v.y;
           continue;
         } else {
           uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(p));
@@ -160,31 +184,50 @@ __global__ void __launch_bounds__(128) zproj_med(const T* __restrict__ stack, in
         v2 = (i + 2 < n) ? p[2] : 0;
         v3 = (i + 3 < n) ? p[3] : 0;
       }
-      a[z] = v0 | (v1 << 16);
-      b[z] = v2 | (v3 << 16);
+      a[s] = v0 | (v1 << 16);
+      b[s] = v2 | (v3 << 16);
     } else {
-      a[z] = 0xffffffffu;
-      b[z] = 0xffffffffu;
+      a[s] = z < 0 ? 0u : 0xffffffffu;
+      b[s] = z < 0 ? 0u : 0xffffffffu;
     }
   }
-  bitonic_sort_u16x2<P>(a);
-  bitonic_sort_u16x2<P>(b);
-  // ascending; the Z real samples occupy positions 0..Z-1 (sentinels are >= every sample)
-  int hi = Z >> 1, lo = (Z - 1) >> 1;
-  uint32_t alo = 0, ahi = 0, blo = 0, bhi = 0;
-#pragma unroll
-  for (int z = 0; z < P; ++z) {
-    if (z == lo) { alo = a[z]; blo = b[z]; }
-    if (z == hi) { ahi = a[z]; bhi = b[z]; }
-  }
+  oddeven_sort_u16x2<P>(a);
+  oddeven_sort_u16x2<P>(b);
+  const uint32_t alo = a[P / 2 - 1], blo = b[P / 2 - 1];
+  const uint32_t ahi = (Z & 1) ? alo : a[P / 2], bhi = (Z & 1) ? blo : b[P / 2];
   double r0 = ((double)(alo & 0xffffu) + (double)(ahi & 0xffffu)) * 0.5;
   double r1 = ((double)(alo >> 16) + (double)(ahi >> 16)) * 0.5;
   double r2 = ((double)(blo & 0xffffu) + (double)(bhi & 0xffffu)) * 0.5;
   double r3 = ((double)(blo >> 16) + (double)(bhi >> 16)) * 0.5;
+  if (vec_ok) {
+    reinterpret_cast<double2*>(out + i)[0] = make_double2(r0, r1);
+    reinterpret_cast<double2*>(out + i)[1] = make_double2(r2, r3);
+    return;
+  }
   out[i] = r0;
   if (i + 1 < n) out[i + 1] = r1;
   if (i + 2 < n) out[i + 2] = r2;
   if (i + 3 < n) out[i + 3] = r3;
+}
+
+// float32 stacks (np.median of float32 stays float32; the mean of the two middle values is one float32 add and an
+// exact halving).  Same network on fminf/fmaxf with -inf / +inf sentinels, one pixel per register.  NaNs are not
+// handled (numpy propagates them).
+template <int P>
+__global__ void __launch_bounds__(128) zproj_med_f32(const float* __restrict__ stack, int Z, int64_t n,
+                                                     float* __restrict__ out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float a[P];
+  const int n_lo = (P - Z) >> 1;
+#pragma unroll
+  for (int s = 0; s < P; ++s) {
+    const int z = s - n_lo;
+    a[s] = (z >= 0 && z < Z) ? __ldg(stack + (int64_t)z * n + i) : (z < 0 ? -INFINITY : INFINITY);
+  }
+  oddeven_sort<MinMaxF32, 0, P>(a);
+  const float lo = a[P / 2 - 1];
+  out[i] = (Z & 1) ? lo : __fmul_rn(__fadd_rn(lo, a[P / 2]), 0.5f);
 }
 
 // Any Z: per-pixel rank selection in O(Z^2) compares on values re-read from L2.
@@ -304,6 +347,235 @@ __global__ void __launch_bounds__(FS_THREADS) zproj_focus(const T* __restrict__ 
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// focus stacking, fast path (uint16 stacks with W % 4 == 0, Z <= 256, H, W >= 8).
+//
+// One WARP owns a tile of 124 x TY output pixels for all Z; warps of a CTA are independent (no block barrier
+// anywhere).  Per slice the warp's raw tile (132 x (TY + 8) pixels: halo 4) arrives in its own shared-memory
+// ring by 8-byte cp.async while the previous slice is computed.  A lane owns 4 adjacent columns and slides down the
+// rows with the vertical filter windows in registers:
+//   * the horizontal taps work on PACKED pairs of uint16 pixels with dp2a (two 16-bit x 8-bit products + add in
+//     one instruction): no unpacking of the raw tile, three dp2a per blurred pixel;
+//   * blurred pixels are exchanged between neighbouring lanes as packed words (two shuffles per row);
+//   * the ksize-5 Laplacian S_y (x) D2_x + D2_y (x) S_x factors, in exact integers, as
+//       L = 2 * ( [1 2 2 2 1]_y [1 2 2 2 1]_x B  -  4 * [1 2 1]_y [1 2 1]_x B )
+//     (S = [1 2 1]*[1 2 1], D2 = [1 2 1]*[1 -2 1]); the arg-max compares |L| / 2;
+//   * the running arg-max is ONE 32-bit key per pixel in shared memory: (|L|/2) << 8 | (255 - z), so that max()
+//     keeps the largest response and, among equals, the earliest slice (the reference's strict '>').
+// After the last slice the output pixel is fetched from the winning slice.  BORDER_REFLECT_101: raw halo pixels are
+// loaded through the reflected index; blurring the reflected raw image gives the reflected blurred image because
+// both kernels are symmetric.
+// ------------------------------------------------------------------------------------------
+constexpr int FSW_OUT = 124;                 // valid output columns per warp tile (32 lanes x 4 - 2 x 2 halo)
+constexpr int FSW_ROWB = 264;                // bytes per raw row in shared memory: 132 pixels = 33 chunks of 8 bytes
+
+__device__ __forceinline__ uint32_t fsw_dp2a(uint32_t a, uint32_t coef, uint32_t c) { return __dp2a_lo(a, coef, c); }
+__device__ __forceinline__ constexpr uint32_t fsw_c(uint32_t lo, uint32_t hi) { return lo | (hi << 8); }
+__device__ __forceinline__ int fsw_reflect(int i, int n) {       // i in [-4, n + 3] exact; beyond: clamped (unused)
+  i = i < 0 ? -i : i;
+  i = i >= n ? 2 * (n - 1) - i : i;
+  return i < 0 ? 0 : i;
+}
+
+template <int TY, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32, 1) zproj_focus_u16_fast(const uint16_t* __restrict__ stack, int Z, int H,
+                                                                      int W, uint16_t* __restrict__ out, int ntx,
+                                                                      int nty) {
+  extern __shared__ __align__(16) unsigned char fsw_smem[];
+  constexpr int RAWH = TY + 8;
+  static_assert(RAWH % 5 == 0, "the row loop is unrolled by the period of the 5-row filter windows");
+  constexpr int STAGE_B = RAWH * FSW_ROWB;
+  constexpr int RAW_B = 2 * STAGE_B;
+  constexpr int WARP_B = RAW_B + TY * 128 * 4;
+  constexpr int NCHUNK = RAWH * 33;            // 8-byte chunks of one raw tile
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  unsigned char* wbase = fsw_smem + (size_t)warp * WARP_B;
+  const uint32_t raw_s = (uint32_t)__cvta_generic_to_shared(wbase);
+  uint4* keys = reinterpret_cast<uint4*>(wbase + RAW_B);
+  const int64_t plane = (int64_t)H * W;
+
+  for (int t = blockIdx.x * WARPS + warp; t < ntx * nty; t += gridDim.x * WARPS) {
+    const int ty = t / ntx, tx = t - ty * ntx;
+    const int ox = tx * FSW_OUT, oy = ty * TY;
+    const int rx0 = ox - 4, ry0 = oy - 4;
+    // W % 4 == 0 and rx0 % 4 == 0: a chunk lies entirely inside the image or entirely outside.  Chunks inside are
+    // copied by cp.async; the one chunk left of column 0 and the one right of column W - 1 (BORDER_REFLECT_101) are
+    // mirrored from shared memory once the slice has landed; chunks further out feed no valid output.
+    const bool left_edge = (rx0 < 0);
+    const int right_chunk = (W - rx0) >> 2;                  // chunk that starts at column W
+    const bool right_edge = right_chunk < 33;
+
+    auto load_slice = [&](int z, int stage) {
+      const uint16_t* sl = stack + (int64_t)z * plane;
+      const uint32_t sbase = raw_s + stage * STAGE_B;
+#pragma unroll 2
+      for (int c = lane; c < NCHUNK; c += 32) {
+        const int rr = c / 33, i = c - rr * 33;
+        const int x = rx0 + 4 * i;
+        if (x >= 0 && x < W) {
+          const uint16_t* src = sl + (int64_t)fsw_reflect(ry0 + rr, H) * W + x;
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sbase + rr * FSW_ROWB + 8 * i), "l"(src) : "memory");
+        }
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    auto mirror_edges = [&](int stage) {
+      if (!(left_edge || right_edge)) return;
+      unsigned char* sb = wbase + stage * STAGE_B;
+      for (int rr = lane; rr < RAWH; rr += 32) {
+        uint16_t* row = reinterpret_cast<uint16_t*>(sb + rr * FSW_ROWB);
+        if (left_edge) {                                     // columns -4..-1 <- columns 4..1 (raw index = column + 4)
+          row[0] = row[8]; row[1] = row[7]; row[2] = row[6]; row[3] = row[5];
+        }
+        if (right_edge) {                                    // columns W..W+3 <- columns W-2..W-5
+          uint16_t* q = row + 4 * right_chunk;
+          q[0] = q[-2]; q[1] = q[-3]; q[2] = q[-4]; q[3] = q[-5];
+        }
+      }
+    };
+
+    for (int i = lane; i < TY * 32; i += 32) keys[i] = make_uint4(0u, 0u, 0u, 0u);
+    load_slice(0, 0);
+    for (int z = 0; z < Z; ++z) {
+      if (z + 1 < Z) {
+        load_slice(z + 1, (z + 1) & 1);
+        asm volatile("cp.async.wait_group 1;" ::: "memory");
+      } else {
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+      }
+      __syncwarp();
+      mirror_edges(z & 1);
+      __syncwarp();
+      const uint32_t sbase = raw_s + (z & 1) * STAGE_B + 8u * lane;
+      const uint32_t zkey = 255u - (uint32_t)z;
+      uint32_t hw[5][4];     // horizontal blur taps of the last 5 raw rows
+      uint32_t pw[5][4];     // [1 2 2 2 1]_x B of the last 5 blurred rows
+      uint32_t qw[5][4];     // [1 2 1]_x B of the last 5 blurred rows (4 are live)
+#pragma unroll 1
+      for (int r0 = 0; r0 < RAWH; r0 += 5) {
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+          const int rr = r0 + k;                         // raw row; rr % 5 == k
+          uint32_t w0, w1, w2, w3;
+          asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(w0), "=r"(w1) : "r"(sbase + rr * FSW_ROWB));
+          asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(w2), "=r"(w3) : "r"(sbase + rr * FSW_ROWB + 8));
+          hw[k][0] = fsw_dp2a(w0, fsw_c(1, 4), fsw_dp2a(w1, fsw_c(6, 4), fsw_dp2a(w2, fsw_c(1, 0), 0)));
+          hw[k][1] = fsw_dp2a(w0, fsw_c(0, 1), fsw_dp2a(w1, fsw_c(4, 6), fsw_dp2a(w2, fsw_c(4, 1), 0)));
+          hw[k][2] = fsw_dp2a(w1, fsw_c(1, 4), fsw_dp2a(w2, fsw_c(6, 4), fsw_dp2a(w3, fsw_c(1, 0), 0)));
+          hw[k][3] = fsw_dp2a(w1, fsw_c(0, 1), fsw_dp2a(w2, fsw_c(4, 6), fsw_dp2a(w3, fsw_c(4, 1), 0)));
+          if (rr >= 4) {
+            // blurred row br = rr - 4 <-> image row oy - 2 + br; br % 5 == (k + 1) % 5
+            constexpr int KB = 0;  (void)KB;
+            uint32_t bl[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const uint32_t sum = hw[(k + 1) % 5][j] + hw[k][j] + 4u * (hw[(k + 2) % 5][j] + hw[(k + 4) % 5][j]) +
+                                   6u * hw[(k + 3) % 5][j];
+              bl[j] = (sum + 128u) >> 8;                 // cv2.GaussianBlur: one rounding, fits 16 bits
+            }
+            const uint32_t b01 = bl[0] | (bl[1] << 16), b23 = bl[2] | (bl[3] << 16);
+            const uint32_t lft = __shfl_up_sync(0xffffffffu, b23, 1);      // (B[-2], B[-1]) from the lane to the left
+            const uint32_t rgt = __shfl_down_sync(0xffffffffu, b01, 1);    // (B[4], B[5]) from the lane to the right
+            const uint32_t l01 = fsw_dp2a(lft, fsw_c(0, 1), 0);            // B[-1]
+            const uint32_t m22 = fsw_dp2a(b01, fsw_c(2, 2), 0), n22 = fsw_dp2a(b23, fsw_c(2, 2), 0);
+            const int kb = (k + 1) % 5;                  // slot of blurred row br in the 5-row windows
+            pw[kb][0] = fsw_dp2a(lft, fsw_c(1, 2), fsw_dp2a(b23, fsw_c(1, 0), m22));
+            pw[kb][1] = fsw_dp2a(b23, fsw_c(2, 1), m22 + l01);
+            pw[kb][2] = fsw_dp2a(b01, fsw_c(1, 2), fsw_dp2a(rgt, fsw_c(1, 0), n22));
+            pw[kb][3] = fsw_dp2a(b01, fsw_c(0, 1), fsw_dp2a(rgt, fsw_c(2, 1), n22));
+            qw[kb][0] = fsw_dp2a(b01, fsw_c(2, 1), l01);
+            qw[kb][1] = fsw_dp2a(b01, fsw_c(1, 2), fsw_dp2a(b23, fsw_c(1, 0), 0));
+            qw[kb][2] = fsw_dp2a(b01, fsw_c(0, 1), fsw_dp2a(b23, fsw_c(2, 1), 0));
+            qw[kb][3] = fsw_dp2a(b23, fsw_c(1, 2), fsw_dp2a(rgt, fsw_c(1, 0), 0));
+            if (rr >= 8) {
+              const int orow = rr - 8;                   // output row <-> image row oy + orow
+              uint4* kp = keys + orow * 32 + lane;
+              const uint4 old = *kp;
+              uint32_t key[4];
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                // window slots: blurred rows br-4 .. br sit at (kb+1)%5 .. kb
+                const int v1 = (int)(pw[(kb + 1) % 5][j] + pw[kb][j] +
+                                     2u * (pw[(kb + 2) % 5][j] + pw[(kb + 3) % 5][j] + pw[(kb + 4) % 5][j]));
+                const int v2 = (int)(qw[(kb + 2) % 5][j] + 2u * qw[(kb + 3) % 5][j] + qw[(kb + 4) % 5][j]);
+                const int half = v1 - 4 * v2;            // cv2.Laplacian(ksize=5) = 2 * half, |half| < 2^23
+                key[j] = ((uint32_t)(half < 0 ? -half : half) << 8) | zkey;
+              }
+              *kp = make_uint4(max(key[0], old.x), max(key[1], old.y), max(key[2], old.z), max(key[3], old.w));
+            }
+          }
+        }
+      }
+      __syncwarp();
+    }
+    // the output takes the ORIGINAL pixel of the winning slice (zstacks.py:181-187)
+    for (int orow = 0; orow < TY; ++orow) {
+      const int y = oy + orow;
+      if (y >= H) break;
+      const uint4 k = keys[orow * 32 + lane];
+      const uint32_t kk[4] = {k.x, k.y, k.z, k.w};
+      uint32_t v[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int x = ox - 2 + 4 * lane + j;
+        const bool valid = (lane > 0 || j >= 2) && (lane < 31 || j < 2) && x < W;
+        v[j] = valid ? (uint32_t)__ldg(stack + (int64_t)(255 - (int)(kk[j] & 255u)) * plane + (int64_t)y * W + x) : 0u;
+      }
+      // x of j = 0 is even and W is even: (j0, j1) and (j2, j3) are aligned pairs
+      const int x0 = ox - 2 + 4 * lane;
+      uint32_t* o32 = reinterpret_cast<uint32_t*>(out + (int64_t)y * W);
+      if (lane > 0 && x0 + 1 < W) o32[x0 >> 1] = v[0] | (v[1] << 16);
+      if (lane < 31 && x0 + 3 < W) o32[(x0 + 2) >> 1] = v[2] | (v[3] << 16);
+    }
+    __syncwarp();
+  }
+}
+
+template <int TY, int WARPS>
+int launch_focus_fast(tmat_ctx* ctx, const uint16_t* stack, int Z, int H, int W, uint16_t* out, cudaStream_t st) {
+  constexpr int SMEM = WARPS * (2 * (TY + 8) * FSW_ROWB + TY * 128 * 4);
+  static bool attr_set = false;
+  if (!attr_set) {
+    CUDA_TRY(cudaFuncSetAttribute(zproj_focus_u16_fast<TY, WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+    attr_set = true;
+  }
+  const int ntx = cdiv(W, FSW_OUT), nty = cdiv(H, TY);
+  const int grid = std::min(cdiv(ntx * nty, WARPS), ctx->sm_count > 0 ? ctx->sm_count : 148);
+  zproj_focus_u16_fast<TY, WARPS><<<grid, WARPS * 32, SMEM, st>>>(stack, Z, H, W, out, ntx, nty);
+  KERNEL_CHECK(ctx);
+  return TMAT_OK;
+}
+
+// float32 stacks: np.mean keeps float32 -- np.add.reduce over the leading axis accumulates slice by slice in float32,
+// then one float32 divide by Z.
+__global__ void __launch_bounds__(256) zproj_avg_f32(const float* __restrict__ stack, int Z, int64_t n,
+                                                     float* __restrict__ out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float s = stack[i];
+  for (int z = 1; z < Z; ++z) s = __fadd_rn(s, stack[(int64_t)z * n + i]);
+  out[i] = __fdiv_rn(s, (float)Z);
+}
+__global__ void __launch_bounds__(256) zproj_med_generic_f32(const float* __restrict__ stack, int Z, int64_t n,
+                                                             float* __restrict__ out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int hi = Z >> 1, lo = (Z - 1) >> 1;
+  float vlo = 0.f, vhi = 0.f;
+  for (int z = 0; z < Z; ++z) {
+    float v = stack[(int64_t)z * n + i];
+    int less = 0, eq = 0;
+    for (int y = 0; y < Z; ++y) {
+      float u = stack[(int64_t)y * n + i];
+      less += (u < v);
+      eq += (u == v);
+    }
+    if (less <= lo && lo < less + eq) vlo = v;
+    if (less <= hi && hi < less + eq) vhi = v;
+  }
+  out[i] = (Z & 1) ? vlo : __fmul_rn(__fadd_rn(vlo, vhi), 0.5f);
+}
+
 template <typename T>
 int launch_minmax(tmat_ctx* ctx, const T* stack, int Z, int64_t n, bool is_max, T* out, cudaStream_t st) {
   const int vec = 16 / sizeof(T);
@@ -337,6 +609,25 @@ int launch_med(tmat_ctx* ctx, const T* stack, int Z, int64_t n, double* out, cud
   return TMAT_OK;
 }
 
+// fast focus-stacking path: uint16, 8-byte aligned rows (cp.async), keys hold the slice in 8 bits
+template <typename T>
+bool focus_fast_ok(const T*, int, int, int, const void*) { return false; }
+template <>
+bool focus_fast_ok<uint16_t>(const uint16_t* stack, int Z, int H, int W, const void* out) {
+  static const bool off = [] { const char* e = getenv("TMAT_FS_GENERIC"); return e && atoi(e) != 0; }();
+  return !off && Z <= 256 && H >= 8 && W >= 8 && (W % 4) == 0 && (reinterpret_cast<uintptr_t>(stack) % 8) == 0 &&
+         (reinterpret_cast<uintptr_t>(out) % 4) == 0;
+}
+template <typename T>
+int launch_focus_fast_any(tmat_ctx*, const T*, int, int, int, void*, cudaStream_t) { return TMAT_ERR_UNSUPPORTED; }
+template <>
+int launch_focus_fast_any<uint16_t>(tmat_ctx* ctx, const uint16_t* stack, int Z, int H, int W, void* out, cudaStream_t st) {
+  static const int ty = [] { const char* e = getenv("TMAT_FS_TY"); return e ? atoi(e) : 32; }();
+  if (ty == 12) return launch_focus_fast<12, 13>(ctx, stack, Z, H, W, (uint16_t*)out, st);
+  if (ty == 22) return launch_focus_fast<22, 8>(ctx, stack, Z, H, W, (uint16_t*)out, st);
+  return launch_focus_fast<32, 6>(ctx, stack, Z, H, W, (uint16_t*)out, st);
+}
+
 template <typename T>
 int zproj_typed(tmat_ctx* ctx, const T* stack, int Z, int H, int W, int method, void* out, cudaStream_t st) {
   int64_t n = (int64_t)H * W;
@@ -349,6 +640,7 @@ int zproj_typed(tmat_ctx* ctx, const T* stack, int Z, int H, int W, int method, 
       return TMAT_OK;
     case TMAT_ZPROJ_MED: return launch_med<T>(ctx, stack, Z, n, (double*)out, st);
     case TMAT_ZPROJ_FS: {
+      if (focus_fast_ok<T>(stack, Z, H, W, out)) return launch_focus_fast_any(ctx, stack, Z, H, W, out, st);
       dim3 grid(cdiv(W, FS_TX), cdiv(H, FS_TY));
       zproj_focus<T><<<grid, FS_THREADS, 0, st>>>(stack, Z, H, W, (T*)out);
       KERNEL_CHECK(ctx);
@@ -383,19 +675,43 @@ extern "C" int tmat_zproj_dev(tmat_ctx* ctx, const void* stack_dev, int dtype, i
   cudaStream_t st = as_stream(stream);
   if (dtype == TMAT_U16) return zproj_typed<uint16_t>(ctx, (const uint16_t*)stack_dev, Z, H, W, method, out_dev, st);
   if (dtype == TMAT_U8) return zproj_typed<uint8_t>(ctx, (const uint8_t*)stack_dev, Z, H, W, method, out_dev, st);
-  tmat_set_error("tmat_zproj: dtype %d not supported (uint8 / uint16 stacks only)", dtype);
+  if (dtype == TMAT_F32 && method != TMAT_ZPROJ_FS) {
+    // numpy semantics for a float32 stack: every projection stays float32 (zstacks.py:192-249 call np.mean/median/max/min)
+    const float* stack = (const float*)stack_dev;
+    const int64_t n = (int64_t)H * W;
+    const unsigned g256 = (unsigned)cdiv64(n, 256);
+    switch (method) {
+      case TMAT_ZPROJ_MIN: zproj_minmax_scalar<float, false><<<g256, 256, 0, st>>>(stack, Z, n, (float*)out_dev); break;
+      case TMAT_ZPROJ_MAX: zproj_minmax_scalar<float, true><<<g256, 256, 0, st>>>(stack, Z, n, (float*)out_dev); break;
+      case TMAT_ZPROJ_AVG: zproj_avg_f32<<<g256, 256, 0, st>>>(stack, Z, n, (float*)out_dev); break;
+      default: {
+        const unsigned g128 = (unsigned)cdiv64(n, 128);
+        if (Z <= 2)       zproj_med_f32<2><<<g128, 128, 0, st>>>(stack, Z, n, (float*)out_dev);
+        else if (Z <= 4)  zproj_med_f32<4><<<g128, 128, 0, st>>>(stack, Z, n, (float*)out_dev);
+        else if (Z <= 8)  zproj_med_f32<8><<<g128, 128, 0, st>>>(stack, Z, n, (float*)out_dev);
+        else if (Z <= 16) zproj_med_f32<16><<<g128, 128, 0, st>>>(stack, Z, n, (float*)out_dev);
+        else if (Z <= 32) zproj_med_f32<32><<<g128, 128, 0, st>>>(stack, Z, n, (float*)out_dev);
+        else if (Z <= 64) zproj_med_f32<64><<<g128, 128, 0, st>>>(stack, Z, n, (float*)out_dev);
+        else zproj_med_generic_f32<<<g256, 256, 0, st>>>(stack, Z, n, (float*)out_dev);
+      }
+    }
+    KERNEL_CHECK(ctx);
+    return TMAT_OK;
+  }
+  tmat_set_error("tmat_zproj: dtype %d not supported for method %d (uint8 / uint16 stacks; float32 for min/max/avg/med -- "
+                 "cv2.GaussianBlur/Laplacian of a float stack is not restated)", dtype, method);
   return TMAT_ERR_UNSUPPORTED;
 }
 
 extern "C" int tmat_zproj_host(tmat_ctx* ctx, const void* stack_host, int dtype, int Z, int H, int W,
                                int method, int ksize, void* out_host) {
   TMAT_REQUIRE(ctx && stack_host && out_host, "tmat_zproj_host: NULL argument");
-  TMAT_REQUIRE(dtype == TMAT_U8 || dtype == TMAT_U16, "tmat_zproj_host: dtype %d not supported", dtype);
+  TMAT_REQUIRE(dtype == TMAT_U8 || dtype == TMAT_U16 || dtype == TMAT_F32, "tmat_zproj_host: dtype %d not supported", dtype);
   TMAT_REQUIRE(Z >= 1 && H >= 1 && W >= 1, "tmat_zproj_host: bad shape (%d,%d,%d)", Z, H, W);
   TMAT_TRY(arena_reset(ctx));
   size_t es = dtype_size(dtype);
   size_t in_bytes = (size_t)Z * H * W * es;
-  size_t out_es = (method == TMAT_ZPROJ_AVG || method == TMAT_ZPROJ_MED) ? 8 : es;
+  size_t out_es = (dtype != TMAT_F32 && (method == TMAT_ZPROJ_AVG || method == TMAT_ZPROJ_MED)) ? 8 : es;
   size_t out_bytes = (size_t)H * W * out_es;
   void *d_in, *d_out;
   TMAT_TRY(arena_alloc(ctx, in_bytes, &d_in));

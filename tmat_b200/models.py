@@ -180,13 +180,23 @@ class UNetXceptionPatchSegmentor:
         self.model = CudaUNet(load_checkpoint(checkpoint_file, filter_counts), patch_size, filter_counts, channels)
 
     def predict(self, x, auto_resample=True):
+        """models.py:624-653.  With ``auto_resample`` the image is Lanczos-resampled by ``ds_ratio`` before and
+        nearest-resampled back after the tiled prediction, exactly as the reference does with Pillow -- including
+        its (rows, cols) tuple handed to Pillow's (width, height) parameter and the float32 result of the
+        round trip through ``Image.fromarray``."""
+        from . import resize as rz
         x = np.asarray(x).astype(np.float32)
-        if auto_resample:
-            raise NotImplementedError("auto_resample (PIL Lanczos pre/post resize, models.py:630-651) is outside "
-                                      "the hot path; compute_branches.py calls predict(auto_resample=False)")
+        original_shape = x.shape
+        target_shape = tuple(np.round(np.multiply(original_shape[:2], self.ds_ratio)).astype(int))
+        do_resampling = original_shape != target_shape and auto_resample
+        if do_resampling:
+            x = rz.pil_resize(x, target_shape, rz.LANCZOS)
         if self.norm_mean is not None and self.norm_std is not None:
             x = (x - self.norm_mean) / self.norm_std
-        return predict_img_with_smooth_windowing(x, self.patch_size, 2, self.model.predict)
+        pred = predict_img_with_smooth_windowing(x, self.patch_size, 2, self.model.predict)
+        if do_resampling:
+            pred = rz.pil_resize(pred, original_shape, rz.NEAREST)
+        return pred
 
 
 def get_unet_patch_segmentor_from_cfg(cfg_json, checkpoint_file=None, models_dir=None):

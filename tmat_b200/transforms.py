@@ -139,3 +139,26 @@ def set_skeletonize_lut(lut):
     if t.shape != (256,):
         raise ValueError("expected 256 entries")
     _ffi.check(_ffi.lib().tmat_skeleton_lut_set(_ffi.ptr(t)))
+
+
+def distance_transform_edt(mask, invert=False):
+    """scipy.ndimage.distance_transform_edt(mask) (compute_branches.py:342), exact: float64 distance of every
+    non-zero pixel to the nearest zero pixel.  ``invert=True`` transforms ``logical_not(mask)``."""
+    m = _mask_u8(mask)
+    out = np.empty(m.shape, dtype=np.float64)
+    _ffi.check(_ffi.lib().tmat_distance_transform_edt_host(_ffi.default_context().handle, _ffi.ptr(m), *m.shape,
+                                                           int(bool(invert)), _ffi.ptr(out)))
+    return out
+
+
+def centerline_weighting(pred, seg_mask, skel):
+    """compute_branches.py:341-344 given the medial-axis skeleton: ``pred * dist / (dist + centerline_dt)`` with
+    ``dist = distance_transform_edt(seg_mask)`` and ``centerline_dt = distance_transform_edt(~skel)``."""
+    p = np.ascontiguousarray(pred, dtype=np.float64)
+    m, s = _mask_u8(seg_mask), _mask_u8(skel)
+    if p.shape != m.shape or s.shape != m.shape:
+        raise ValueError("pred, seg_mask and skel must have the same shape")
+    out = np.empty(m.shape, dtype=np.float64)
+    _ffi.check(_ffi.lib().tmat_centerline_weight_host(_ffi.default_context().handle, _ffi.ptr(p), _ffi.ptr(m), _ffi.ptr(s),
+                                                      *m.shape, _ffi.ptr(out)))
+    return out

@@ -14,11 +14,16 @@ def _project(stack, axis, method, kernel_size=5):
         stack = np.moveaxis(stack, axis, 0)
     if stack.ndim != 3:
         raise ValueError(f"expected a 3-D (Z, H, W) stack, got shape {stack.shape}")
-    if stack.dtype not in (np.uint8, np.uint16):
-        raise TypeError(f"libtmat_b200 projects uint8 / uint16 stacks, got {stack.dtype}")
+    if stack.dtype == np.float64 and method != "fs":
+        # numpy would stay float64; the kernels compute float stacks in float32
+        raise TypeError("libtmat_b200 projects uint8 / uint16 / float32 stacks; cast a float64 stack to float32 first")
+    if stack.dtype not in (np.uint8, np.uint16) and not (stack.dtype == np.float32 and method != "fs"):
+        raise TypeError(f"libtmat_b200 projects uint8 / uint16 stacks (and float32 for min/max/avg/med), got "
+                        f"{stack.dtype} for method {method!r}")
     stack = np.ascontiguousarray(stack)
     z, h, w = stack.shape
-    out_dtype = np.float64 if method in ("avg", "med") else stack.dtype
+    # numpy's result dtypes: mean/median of an integer stack are float64, of a float32 stack float32
+    out_dtype = np.float64 if (method in ("avg", "med") and stack.dtype != np.float32) else stack.dtype
     out = np.empty((h, w), dtype=out_dtype)
     ctx = _ffi.default_context()
     _ffi.check(_ffi.lib().tmat_zproj_host(ctx.handle, _ffi.ptr(stack), _ffi.DTYPES[stack.dtype],
