@@ -269,11 +269,9 @@ def stages_leg(ctx, world, rank, pk):
         segs[b] = torch.roll(seg, shifts=(11 * b, 5 * b), dims=(0, 1))
     d_m = torch.empty((S, S), dtype=torch.uint8, device="cuda")
     d_o = torch.empty((S, S), dtype=torch.uint8, device="cuda")
-    info = (C.c_int * 4)()
-
     def batch():
         for b in range(B):
-            _ffi.check(L.tmat_auto_threshold_well_dev(ctx.handle, _ffi.ptr(wells[b]), _ffi.U16, S, S, _ffi.ptr(d_m), info,
+            _ffi.check(L.tmat_auto_threshold_well_dev(ctx.handle, _ffi.ptr(wells[b]), _ffi.U16, S, S, _ffi.ptr(d_m), None,
                                                       sptr))
             _ffi.check(L.tmat_filter_branch_seg_mask_dev(ctx.handle, _ffi.ptr(segs[b]), S, S, 1, 1, _ffi.ptr(d_o), sptr))
     ms = timed(batch, iters=3, warm=1)

@@ -274,6 +274,15 @@ int tmat_centerline_weight_dev(tmat_ctx* ctx, const double* pred_dev, const uint
 int tmat_centerline_weight_host(tmat_ctx* ctx, const double* pred_host, const uint8_t* mask_host,
                                 const uint8_t* skel_host, int H, int W, double* out_host);
 
+/* ---- the Morse graph built from the weighted prediction -------------- */
+/* dmtgraph.py:38-99 compute_dmt_graph(img, delta1, delta2) (native twin: pydmtgraph DMTGraph.cpp:232-615).
+ * Sequential union-find sweeps in filtration order: native HOST code in this library (no kernel; needs no GPU).
+ * img: float32 (H, W).  vertices: int32 (n_vertices, 2) = (row, column); edges: int32 (n_edges, 2) indices into
+ * vertices -- same content AND order as the reference.  Pass NULL for both arrays to query the counts. */
+int tmat_dmt_graph_host(const float* img_host, int H, int W, float delta1, float delta2,
+                        int32_t* vertices_host, int64_t cap_vertices, int64_t* n_vertices,
+                        int32_t* edges_host, int64_t cap_edges, int64_t* n_edges);
+
 /* ---- the resizes either side of the path ---------------------------- */
 /* mode: which library call is reproduced.
  *   PIL_LANCZOS  Image.fromarray(float32).resize((Wout, Hout), Image.Resampling.LANCZOS)  models.py:630-634

@@ -48,7 +48,8 @@ def rescale_unit_f32(img):
     y = np.clip(img, lo, hi)
     if lo != hi:
         y = (y - lo) / (hi - lo)
-    return np.asarray(y * 1 + 0, dtype=ft).astype(np.float32)
+        return np.asarray(y * 1 + 0, dtype=ft).astype(np.float32)
+    return np.clip(y, 0, 1).astype(ft).astype(np.float32)     # constant image: skimage clips to the output range
 
 
 def mask_and_threshold(img, sd_coef, rand_state, well_mask=None, well_idx=None):

@@ -151,8 +151,29 @@ def gen_morphology():
     np.savez_compressed(os.path.join(OUT, "morphology.npz"), **cases)
 
 
+def gen_dmt():
+    """The reference's own numba implementation (dmtgraph.py:38-99) on small weighted-prediction-like images."""
+    from fl_tissue_model_tools import dmtgraph as r
+    cases = {}
+    for name, (h, w, d1, d2, seed) in {"a": (40, 52, 5.0, 0.0, 1), "b": (64, 64, 20.0, 10.0, 2), "c": (97, 131, 12.0, 0.0, 3),
+                                       "d": (192, 160, 8.0, 2.0, 4), "flat": (16, 16, 1.0, 0.0, 5)}.items():
+        img = (helpers.synth_projection(h, w, seed) * 255).astype(np.float32)
+        img[:5, :7] = 0                           # exact zeros: their edges are dropped (np.isclose, :73-79)
+        if name == "flat":
+            img[:] = 7.0                          # every edge ties: the index tie-breaks decide everything
+        if name == "d":
+            img = np.round(img / 8) * 8           # heavy value ties
+        v, e = r.compute_dmt_graph(img.copy(), d1, d2)
+        cases[f"{name}_in"] = img
+        cases[f"{name}_cfg"] = np.array([d1, d2], np.float32)
+        cases[f"{name}_vertices"] = v
+        cases[f"{name}_edges"] = e
+    np.savez_compressed(os.path.join(OUT, "dmt.npz"), **cases)
+
+
 if __name__ == "__main__":
     _install_stubs()
+    gen_dmt()
     gen_stp()
     gen_zproj()
     gen_thresholds()

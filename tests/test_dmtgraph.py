@@ -1,0 +1,46 @@
+"""The Morse graph: native host code of libtmat_b200 vs the reference's own numba implementation
+(dmtgraph.py:38-99) -- golden fixtures written by tests/golden/make_golden.py from the imported reference, plus a live
+comparison where the reference is installed (baseline/_ref).  Same vertices, same edges, same ORDER.  No GPU needed:
+the algorithm is a sequential union-find sweep and runs on the host inside the library."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+import helpers
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_dmt_graph_matches_reference_golden(golden):
+    from tmat_b200 import dmtgraph
+    g = golden("dmt")
+    for name in ("a", "b", "c", "d", "flat"):
+        d1, d2 = (float(x) for x in g[f"{name}_cfg"])
+        v, e = dmtgraph.compute_dmt_graph(g[f"{name}_in"], d1, d2)
+        assert v.dtype == np.int32 and e.dtype == np.int32
+        assert np.array_equal(v, g[f"{name}_vertices"]), name
+        assert np.array_equal(e, g[f"{name}_edges"]), name
+    assert len(g["c_edges"]) > 1000          # the fixtures are not trivial
+
+
+def test_dmt_graph_live_against_installed_reference():
+    ref_dir = os.path.join(ROOT, "baseline", "_ref")
+    if not os.path.isdir(os.path.join(ref_dir, "fl_tissue_model_tools")):
+        pytest.skip("baseline/_ref not installed")
+    sys.path.insert(0, ref_dir)
+    try:
+        from fl_tissue_model_tools import dmtgraph as ref
+    except Exception as e:   # noqa: BLE001 -- numba missing
+        pytest.skip(f"reference dmtgraph not importable: {e}")
+    finally:
+        sys.path.remove(ref_dir)
+    from tmat_b200 import dmtgraph
+    img = (helpers.synth_projection(120, 96, 17) * 255).astype(np.float32)
+    for d1, d2 in ((3.0, 0.0), (25.0, 5.0)):
+        rv, re_ = ref.compute_dmt_graph(img.copy(), d1, d2)
+        v, e = dmtgraph.compute_dmt_graph(img, d1, d2)
+        assert np.array_equal(v, rv) and np.array_equal(e, re_), (d1, d2)
+    with pytest.raises(ValueError):
+        dmtgraph.compute_dmt_graph(np.zeros((3, 4, 5), np.float32), 1.0)

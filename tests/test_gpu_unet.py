@@ -169,3 +169,25 @@ def test_whole_branch_mask_path_vs_oracle():
     assert np.array_equal(mask[clean], ref_mask[clean])
     assert clean.mean() > 0.5          # the comparison is not vacuous
     assert raw >= 0.999 or unsure.any()
+
+
+def test_whole_path_constant_stack_is_clipped_like_rescale_intensity():
+    """a constant image has no range to rescale; skimage's rescale_intensity then clips it to [0, 1]
+    (compute_branches.py:316) -- the raw uint16 values must not reach the UNet."""
+    import torch
+    from oracle import thresholds as ot, zstacks as oz
+    from tmat_b200 import _ffi, models
+    fc, ws = (64, 128, 256, 512), 64
+    w = ou.make_weights(fc, seed=5)
+    net = models.CudaUNet(w, ws, fc, impl="tc")
+    stack = np.full((3, 70, 66), 1234, np.uint16)
+    d_stack = torch.from_numpy(stack.view(np.int16)).cuda()
+    d_pred = torch.empty((70, 66), dtype=torch.float64, device="cuda")
+    d_mask = torch.empty((70, 66), dtype=torch.uint8, device="cuda")
+    _ffi.check(_ffi.lib().tmat_branch_mask_dev(net.ctx.handle, net._tmat_handle, _ffi.ptr(d_stack), 3, 70, 66, 2,
+                                               _ffi.ptr(d_pred), _ffi.ptr(d_mask), None))
+    torch.cuda.synchronize()
+    img = ot.rescale_unit_f32(oz.proj_max(stack))
+    assert float(img.min()) == float(img.max()) == 1.0
+    ref = ostp.predict_img_with_smooth_windowing(img, ws, 2, ou.make_pred_func(w))
+    assert np.abs(d_pred.cpu().numpy() - ref).max() < PROB_TOL

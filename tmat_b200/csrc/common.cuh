@@ -61,6 +61,7 @@ struct tmat_ctx {
   // small pinned staging area for scalars coming back from the device
   void* pinned = nullptr;
   size_t pinned_cap = 0;
+  unsigned int lut_slot = 0;     // rotating 256-byte slots (pinned + 8192 ...) for small stream-ordered uploads
   // optional per-launch timing of the tensor-core convolution kernel (bench.py's roofline leg)
   bool profiling = false;
   struct ProfRec { cudaEvent_t a, b; double flops; };

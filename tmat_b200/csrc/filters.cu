@@ -141,13 +141,100 @@ __global__ void __launch_bounds__(256) rescale_u8_hist(const T* __restrict__ x, 
     if (sh[i]) atomicAdd(&hist[i], sh[i]);
 }
 
-__global__ void __launch_bounds__(256) threshold_ge_u8(const uint8_t* __restrict__ u8, int64_t n, int invert, int thr,
+// params (device, written by otsu_decide_kernel): [0] invert, [1] Otsu threshold, [2] min, [3] max of the (inverted) image
+__global__ void __launch_bounds__(256) threshold_ge_u8(const uint8_t* __restrict__ u8, int64_t n, const int* __restrict__ params,
                                                        uint8_t* __restrict__ mask) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
+  const int invert = params[0], thr = params[1];
   int v = u8[i];
   if (invert) v = 255 - v;
   mask[i] = v >= thr ? 1 : 0;
+}
+
+// np.median of a uint8 block from its histogram
+__device__ double dev_hist_median(const unsigned int* h) {
+  unsigned long long n = 0;
+  for (int i = 0; i < 256; ++i) n += h[i];
+  if (n == 0) return __longlong_as_double(0x7ff8000000000000ll);
+  unsigned long long k0 = (n - 1) / 2, k1 = n / 2, acc = 0;
+  int v0 = -1, v1 = -1;
+  for (int i = 0; i < 256; ++i) {
+    acc += h[i];
+    if (v0 < 0 && acc > k0) v0 = i;
+    if (v1 < 0 && acc > k1) { v1 = i; break; }
+  }
+  return __ddiv_rn(__dadd_rn((double)v0, (double)v1), 2.0);
+}
+// Corner medians, invert decision and skimage.filters.threshold_otsu (well_mask_generation.py:248-272) on the device:
+// 5 x 256 counters in, four ints out -- the host no longer waits for the histogram (round 1 synchronised here).
+// One block of 256 threads, one bin each.  numpy's dtype semantics (float32 counts and class weights, float64 class
+// means) are kept, and the cumulative sums may be taken in any order because they are exact: every partial count is an
+// integer below 2^24 (n_pixels <= 2^24, checked by the caller) and every partial count*value sum below 2^53.
+__global__ void __launch_bounds__(256) otsu_decide_kernel(const unsigned int* __restrict__ hist /*[5][256]*/,
+                                                          int* __restrict__ params) {
+  __shared__ unsigned int s_cnt[256];
+  __shared__ unsigned long long s_a[256], s_b[256];
+  __shared__ double s_v[256];
+  __shared__ int s_i[256];
+  __shared__ double s_med[4];
+  __shared__ int s_misc[4];
+  const int t = threadIdx.x;
+  if (t < 4) s_med[t] = dev_hist_median(hist + t * 256);
+  const unsigned int* g = hist + 4 * 256;
+  if (t == 4) {
+    int vmin = 0, vmax = 255;
+    while (vmin < 255 && g[vmin] == 0) ++vmin;
+    while (vmax > 0 && g[vmax] == 0) --vmax;
+    s_misc[0] = vmin; s_misc[1] = vmax;
+  }
+  __syncthreads();
+  const int vmin = s_misc[0], vmax = s_misc[1];
+  const double mmin = fmin(fmin(s_med[0], s_med[1]), fmin(s_med[2], s_med[3]));
+  const double mmax = fmax(fmax(s_med[0], s_med[1]), fmax(s_med[2], s_med[3]));
+  const int invert = fabs(__dsub_rn((double)vmin, mmin)) > fabs(__dsub_rn((double)vmax, mmax)) ? 1 : 0;
+  // histogram of the (possibly inverted) image; its occupied range is [lo, hi]
+  const int lo = invert ? 255 - vmax : vmin, hi = invert ? 255 - vmin : vmax;
+  const unsigned int cnt = g[invert ? 255 - t : t];
+  s_cnt[t] = cnt;
+  // inclusive prefix sums of count and count*value (exact integers)
+  s_a[t] = cnt;
+  s_b[t] = (unsigned long long)cnt * (unsigned long long)t;
+  __syncthreads();
+  for (int o = 1; o < 256; o <<= 1) {
+    const unsigned long long a = t >= o ? s_a[t - o] : 0ull, b2 = t >= o ? s_b[t - o] : 0ull;
+    __syncthreads();
+    s_a[t] += a; s_b[t] += b2;
+    __syncthreads();
+  }
+  const unsigned long long tot_a = s_a[255], tot_b = s_b[255];
+  // candidate split after bin t (lo <= t < hi): class 1 = bins lo..t, class 2 = bins t+1..hi
+  double v = -2.0;
+  if (lo < hi && t >= lo && t < hi) {
+    const float w1 = (float)s_a[t], w2 = (float)(tot_a - s_a[t]);
+    const double m1 = __ddiv_rn((double)s_b[t], (double)w1);
+    const double m2 = __ddiv_rn((double)(tot_b - s_b[t]), (double)w2);
+    const float ww = __fmul_rn(w1, w2);
+    const double d = __dsub_rn(m1, m2);
+    v = __dmul_rn((double)ww, __dmul_rn(d, d));
+  }
+  s_v[t] = v; s_i[t] = t;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {           // first maximum wins (np.argmax)
+    if (t < o) {
+      const double v2 = s_v[t + o];
+      const int i2 = s_i[t + o];
+      if (v2 > s_v[t] || (v2 == s_v[t] && i2 < s_i[t])) { s_v[t] = v2; s_i[t] = i2; }
+    }
+    __syncthreads();
+  }
+  if (t == 0) {
+    const int thr = lo >= hi ? (lo > 255 ? 0 : lo) : s_i[0];
+    params[0] = invert;
+    params[1] = thr;
+    params[2] = lo;
+    params[3] = hi;
+  }
 }
 
 }  // namespace
@@ -298,6 +385,8 @@ static int auto_threshold_impl(tmat_ctx* ctx, const void* img, int dtype, int H,
   TMAT_REQUIRE(dtype == TMAT_U8 || dtype == TMAT_U16 || dtype == TMAT_F32 || dtype == TMAT_F64,
                "auto_threshold_well: unsupported dtype %d", dtype);
   TMAT_REQUIRE(H >= 20 && W >= 20, "auto_threshold_well: image %dx%d too small for the 5%% corner blocks", H, W);
+  TMAT_REQUIRE((int64_t)H * W <= (1ll << 24), "auto_threshold_well: images above 2^24 pixels are not supported (the float32 "
+               "class weights of threshold_otsu stop being exact integers)");
   size_t n = (size_t)H * W;
   const bool f32 = (dtype == TMAT_F32);
   void* blur;
@@ -321,25 +410,19 @@ static int auto_threshold_impl(tmat_ctx* ctx, const void* img, int dtype, int H,
   if (f32) rescale_u8_hist<float><<<blocks, 256, 0, st>>>((const float*)blur, H, W, keys, xs, xe, ys, ye, u8, hist);
   else rescale_u8_hist<double><<<blocks, 256, 0, st>>>((const double*)blur, H, W, keys, xs, xe, ys, ye, u8, hist);
   KERNEL_CHECK(ctx);
-  unsigned int* hh = (unsigned int*)ctx->pinned;
-  CUDA_TRY(cudaMemcpyAsync(hh, hist, 5 * 256 * sizeof(unsigned int), cudaMemcpyDeviceToHost, st));
-  CUDA_TRY(cudaStreamSynchronize(st));
-  // corner medians and the invert decision (:248-270)
-  double meds[4];
-  for (int c = 0; c < 4; ++c) meds[c] = hist_median(hh + c * 256);
-  int vmin = 0, vmax = 255;
-  while (vmin < 255 && hh[4 * 256 + vmin] == 0) ++vmin;
-  while (vmax > 0 && hh[4 * 256 + vmax] == 0) --vmax;
-  double mmin = std::min(std::min(meds[0], meds[1]), std::min(meds[2], meds[3]));
-  double mmax = std::max(std::max(meds[0], meds[1]), std::max(meds[2], meds[3]));
-  int invert = fabs((double)vmin - mmin) > fabs((double)vmax - mmax) ? 1 : 0;
-  uint64_t h64[256];
-  for (int i = 0; i < 256; ++i) h64[i] = hh[4 * 256 + (invert ? 255 - i : i)];
-  int thr = otsu_from_hist(h64);
-  threshold_ge_u8<<<(unsigned)cdiv64((int64_t)n, 256), 256, 0, st>>>(u8, (int64_t)n, invert, thr, thr_mask);
+  int* params;
+  TMAT_TRY(arena_get(ctx, 4, &params));
+  otsu_decide_kernel<<<1, 256, 0, st>>>(hist, params);
+  KERNEL_CHECK(ctx);
+  threshold_ge_u8<<<(unsigned)cdiv64((int64_t)n, 256), 256, 0, st>>>(u8, (int64_t)n, params, thr_mask);
   KERNEL_CHECK(ctx);
   TMAT_TRY(erode_disk(ctx, thr_mask, H, W, 5, 1, mask, st));
-  if (info) { info[0] = invert; info[1] = thr; info[2] = invert ? 255 - vmax : vmin; info[3] = invert ? 255 - vmin : vmax; }
+  if (info) {      // optional read-back: the only host synchronisation of the call
+    int* h = (int*)ctx->pinned;
+    CUDA_TRY(cudaMemcpyAsync(h, params, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    for (int k = 0; k < 4; ++k) info[k] = h[k];
+  }
   return TMAT_OK;
 }
 

@@ -100,26 +100,47 @@ __device__ __forceinline__ void uf_union(int* parent, int a, int b) {
   }
 }
 
-__global__ void __launch_bounds__(256) ccl_init(const uint8_t* __restrict__ m, int64_t n, int fg_is_zero,
+// Step 1: every foreground pixel points at the start of its horizontal run inside its 32-pixel warp segment (one
+// ballot per warp instead of one atomic per pixel pair; a tree is at most one link deep afterwards).
+__global__ void __launch_bounds__(256) ccl_init(const uint8_t* __restrict__ m, int H, int W, int fg_is_zero,
                                                 int* __restrict__ parent) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  bool fg = fg_is_zero ? (m[i] == 0) : (m[i] != 0);
-  parent[i] = fg ? (int)i : -1;
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  const bool in = x < W;
+  const bool fg = in && (fg_is_zero ? (m[(int64_t)y * W + x] == 0) : (m[(int64_t)y * W + x] != 0));
+  const unsigned int bits = __ballot_sync(0xffffffffu, fg);
+  if (!in) return;
+  const int lane = threadIdx.x & 31;
+  // highest zero bit below this lane -> the run starts one past it
+  const unsigned int below = ~bits & ((1u << lane) - 1u);
+  const int start = below ? 32 - __clz(below) : 0;
+  parent[y * W + x] = fg ? y * W + (x - lane + start) : -1;
 }
-
+// Step 2: link the runs.  A pixel only issues the unions its left neighbour has not already made:
+//   * a run that continues across a 32-pixel segment boundary is joined to the previous segment;
+//   * upwards (8-connectivity): W set -> only NE, and only if N is clear (W already met N and NW);
+//     W clear -> N if set (N's own run reaches NW and NE), else NW and NE separately.
+//   * 4-connectivity: N only, and only for the first pixel of a run or where the left neighbour had no N.
 __global__ void __launch_bounds__(256) ccl_merge(int* __restrict__ parent, int H, int W, int conn8) {
   int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
   if (x >= W) return;
   int i = y * W + x;
   if (parent[i] < 0) return;
-  if (x > 0 && parent[i - 1] >= 0) uf_union(parent, i, i - 1);
-  if (y > 0) {
-    if (parent[i - W] >= 0) uf_union(parent, i, i - W);
-    if (conn8) {
+  const bool w = x > 0 && parent[i - 1] >= 0;
+  if (w && (x & 31) == 0) uf_union(parent, i, i - 1);
+  if (y == 0) return;
+  const bool n = parent[i - W] >= 0;
+  if (conn8) {
+    const bool ne = x + 1 < W && parent[i - W + 1] >= 0;
+    if (w) {
+      if (ne && !n) uf_union(parent, i, i - W + 1);
+    } else if (n) {
+      uf_union(parent, i, i - W);
+    } else {
       if (x > 0 && parent[i - W - 1] >= 0) uf_union(parent, i, i - W - 1);
-      if (x + 1 < W && parent[i - W + 1] >= 0) uf_union(parent, i, i - W + 1);
+      if (ne) uf_union(parent, i, i - W + 1);
     }
+  } else if (n && !(w && parent[i - W - 1] >= 0)) {
+    uf_union(parent, i, i - W);          // W and NW both set: the left neighbour already joined this run to the run above
   }
 }
 
@@ -253,6 +274,55 @@ __global__ void __launch_bounds__(256) circ_flag_kernel(const unsigned int* __re
   round_flag[l + 1] = circ > 0.8;
 }
 
+// The cleanup driver keeps only the ten border codes that carry a perimeter weight (slot order = code order, which
+// is the order skimage's 50-bin dot product adds them in) and reads the label count from device memory, so that the
+// whole of filter_branch_seg_mask is enqueued without a host round trip.
+__device__ __forceinline__ int perim_slot(int code) {
+  switch (code) {
+    case 5: return 0; case 7: return 1; case 13: return 2; case 15: return 3; case 17: return 4;
+    case 21: return 5; case 23: return 6; case 25: return 7; case 27: return 8; case 33: return 9;
+  }
+  return -1;
+}
+__global__ void __launch_bounds__(256) region_stats10_kernel(const int32_t* __restrict__ lab, const uint8_t* __restrict__ border,
+                                                             int H, int W, unsigned int* __restrict__ area,
+                                                             unsigned int* __restrict__ hist10 /*[cap][10]*/) {
+  int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  if (x >= W) return;
+  int64_t i = (int64_t)y * W + x;
+  int l = lab[i];
+  if (l <= 0) return;
+  atomicAdd(&area[l - 1], 1u);
+  if (!border[i]) return;
+  int code = 0;
+#pragma unroll
+  for (int dy = -1; dy <= 1; ++dy)
+#pragma unroll
+    for (int dx = -1; dx <= 1; ++dx) {
+      int yy = y + dy, xx = x + dx;
+      if (yy < 0 || yy >= H || xx < 0 || xx >= W) continue;
+      int wgt = (dy == 0 && dx == 0) ? 1 : ((dy == 0 || dx == 0) ? 2 : 10);
+      code += border[(int64_t)yy * W + xx] ? wgt : 0;
+    }
+  const int slot = perim_slot(code);
+  if (slot >= 0) atomicAdd(&hist10[(int64_t)(l - 1) * 10 + slot], 1u);
+}
+__global__ void __launch_bounds__(256) circ_flag10_kernel(const unsigned int* __restrict__ area,
+                                                          const unsigned int* __restrict__ hist10, const int* __restrict__ n_dev,
+                                                          uint8_t* __restrict__ round_flag /*[cap+1]*/) {
+  int l = blockIdx.x * blockDim.x + threadIdx.x;
+  if (l >= *n_dev) return;
+  const double w2 = 1.4142135623730951, w3 = (1.0 + 1.4142135623730951) / 2.0;
+  const double wt[10] = {1.0, 1.0, w3, 1.0, 1.0, w2, w3, 1.0, 1.0, w2};
+  const unsigned int* h = hist10 + (int64_t)l * 10;
+  double perim = 0.0;
+#pragma unroll
+  for (int c = 0; c < 10; ++c) perim = __dadd_rn(perim, __dmul_rn((double)h[c], wt[c]));
+  double circ = __ddiv_rn(__dmul_rn(__dmul_rn(4.0, 3.141592653589793), (double)area[l]),
+                          __dadd_rn(__dmul_rn(perim, perim), 1e-7));
+  round_flag[l + 1] = circ > 0.8;
+}
+
 // ---- Zhang-Suen thinning (skimage.morphology.skeletonize, 2-D) -----------------------------------------
 __constant__ uint8_t c_zs_lut[256];
 __device__ __forceinline__ int nb_code(const uint8_t* __restrict__ m, int H, int W, int y, int x) {
@@ -272,6 +342,84 @@ __global__ void __launch_bounds__(256) thin_subpass(const uint8_t* __restrict__ 
   }
   out[i] = v;
 }
+// ---- the whole thinning in ONE cooperative launch (W % 8 == 0) ----------------------------------------------------
+// Persistent grid, 8 pixels (one 64-bit word) per work item, both sub-passes of every round separated by a grid-wide
+// barrier, convergence decided on the device: no host round trip, no per-pass launch (round 1: 2 launches per round
+// plus a device->host copy every 8 rounds, 19 us per pass on byte-wide accesses).  The image (4 MB at 2048^2) and its
+// ping-pong copy stay L2-resident after the first pass.  A word without a set pixel is copied without looking at its
+// neighbours (vessel masks: ~90 % of the words).  Co-residency of the grid comes from cudaLaunchCooperativeKernel.
+__device__ __forceinline__ void grid_barrier(unsigned int* bar, unsigned int& goal) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    goal += gridDim.x;
+    __threadfence();
+    atomicAdd(bar, 1u);
+    while (*(volatile unsigned int*)bar < goal) {}
+    __threadfence();
+  }
+  __syncthreads();
+}
+// bits 1..8 = the word's eight pixels, bit 0 / bit 9 = the pixel left / right of the word
+__device__ __forceinline__ uint32_t row_bits(const uint8_t* __restrict__ img, int W, int y, int xw, int H) {
+  if (y < 0 || y >= H) return 0u;
+  const uint8_t* row = img + (int64_t)y * W;
+  const unsigned long long w = *reinterpret_cast<const unsigned long long*>(row + 8 * xw);
+  // bytes are 0/1: gather their low bits (byte k -> bit k)
+  uint32_t b = (uint32_t)(((w & 0x0101010101010101ull) * 0x0102040810204080ull) >> 56);
+  b <<= 1;
+  if (xw > 0) b |= row[8 * xw - 1] & 1u;
+  if (8 * xw + 8 < W) b |= (uint32_t)(row[8 * xw + 8] & 1u) << 9;
+  return b;
+}
+__device__ __forceinline__ unsigned int thin_pass_words(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int H, int W,
+                                                        const uint8_t* __restrict__ s_lut, int bit) {
+  const int wpr = W >> 3;
+  const int nw = H * wpr;                       // < 2^31: the image itself is limited to 2^31 pixels
+  unsigned int removed = 0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nw; i += gridDim.x * blockDim.x) {
+    const int y = i / wpr, xw = i - y * wpr;
+    unsigned long long c = *reinterpret_cast<const unsigned long long*>(in + (int64_t)y * W + 8 * xw);
+    if (c != 0ull) {
+      const uint32_t U = row_bits(in, W, y - 1, xw, H), C = row_bits(in, W, y, xw, H), D = row_bits(in, W, y + 1, xw, H);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        if ((C >> (k + 1)) & 1u) {
+          const uint32_t code = ((U >> k) & 7u) | (((C >> (k + 2)) & 1u) << 3) | (((D >> (k + 2)) & 1u) << 4) |
+                                (((D >> (k + 1)) & 1u) << 5) | (((D >> k) & 1u) << 6) | (((C >> k) & 1u) << 7);
+          if (s_lut[code] & bit) { c &= ~(0xffull << (8 * k)); ++removed; }
+        }
+      }
+    }
+    *reinterpret_cast<unsigned long long*>(out + (int64_t)y * W + 8 * xw) = c;
+  }
+  return removed;
+}
+// img: the 0/1 image, thinned in place; tmp: scratch of the same size; counters[r] = pixels removed in round r
+// (zeroed by the caller, at least max_rounds entries); bar: zeroed barrier word; iters_out: rounds executed.
+__global__ void __launch_bounds__(256) thin_persistent(uint8_t* __restrict__ img, uint8_t* __restrict__ tmp, int H, int W,
+                                                       const uint8_t* __restrict__ lut, unsigned int* __restrict__ counters,
+                                                       int max_rounds, unsigned int* __restrict__ bar, int* __restrict__ iters_out) {
+  __shared__ uint8_t s_lut[256];
+  __shared__ unsigned int s_removed;
+  s_lut[threadIdx.x] = lut[threadIdx.x];
+  unsigned int goal = 0;
+  int round = 0;
+  for (; round < max_rounds; ++round) {
+    if (threadIdx.x == 0) s_removed = 0;
+    __syncthreads();
+    unsigned int r = thin_pass_words(img, tmp, H, W, s_lut, 1);
+    grid_barrier(bar, goal);
+    r += thin_pass_words(tmp, img, H, W, s_lut, 2);
+    for (int o = 16; o > 0; o >>= 1) r += __shfl_xor_sync(0xffffffffu, r, o);
+    if ((threadIdx.x & 31) == 0 && r) atomicAdd(&s_removed, r);
+    __syncthreads();
+    if (threadIdx.x == 0 && s_removed) atomicAdd(&counters[round], s_removed);
+    grid_barrier(bar, goal);
+    if (*(volatile unsigned int*)&counters[round] == 0u) { ++round; break; }    // this round removed nothing: done
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0 && iters_out) *iters_out = round;
+}
+
 // degree > 2 in the 8-neighbour pixel graph (transforms.py:248, :334)
 __global__ void __launch_bounds__(256) fork_kernel(const uint8_t* __restrict__ sk, int H, int W, const int* __restrict__ sk_root,
                                                    uint8_t* __restrict__ has_fork /*indexed by root pixel*/) {
@@ -393,7 +541,7 @@ static int ccl_roots(tmat_ctx* ctx, const uint8_t* mask, int H, int W, int conne
   TMAT_REQUIRE(connectivity == 1 || connectivity == 2, "label: connectivity must be 1 or 2, got %d", connectivity);
   TMAT_REQUIRE((int64_t)H * W < (1ll << 31), "label: image too large");
   int64_t n = (int64_t)H * W;
-  ccl_init<<<grid1d(n), 256, 0, st>>>(mask, n, fg_is_zero, parent);
+  ccl_init<<<grid2d(H, W), 256, 0, st>>>(mask, H, W, fg_is_zero, parent);
   KERNEL_CHECK(ctx);
   ccl_merge<<<grid2d(H, W), 256, 0, st>>>(parent, H, W, connectivity == 2);
   KERNEL_CHECK(ctx);
@@ -403,8 +551,9 @@ static int ccl_roots(tmat_ctx* ctx, const uint8_t* mask, int H, int W, int conne
 }
 
 // labels 1..n in raster order of each component's first pixel; synchronises to return n
+// n_labels == nullptr: no host round trip; the count stays on the device (*total_dev_out).
 static int label_impl(tmat_ctx* ctx, const uint8_t* mask, int H, int W, int connectivity, int32_t* labels, int* n_labels,
-                      int** parent_out, cudaStream_t st) {
+                      int** parent_out, cudaStream_t st, int** total_dev_out = nullptr) {
   int64_t n = (int64_t)H * W;
   int nb = (int)cdiv64(n, SCAN_BLOCK);
   int *parent, *rank, *bsum, *total;
@@ -421,25 +570,70 @@ static int label_impl(tmat_ctx* ctx, const uint8_t* mask, int H, int W, int conn
   KERNEL_CHECK(ctx);
   labels_from_rank<<<grid1d(n), 256, 0, st>>>(parent, rank, n, labels);
   KERNEL_CHECK(ctx);
-  int* h = (int*)ctx->pinned;
-  CUDA_TRY(cudaMemcpyAsync(h, total, sizeof(int), cudaMemcpyDeviceToHost, st));
-  CUDA_TRY(cudaStreamSynchronize(st));
-  *n_labels = *h;
+  if (total_dev_out) *total_dev_out = total;
   if (parent_out) *parent_out = parent;
+  if (n_labels) {
+    int* h = (int*)ctx->pinned;
+    CUDA_TRY(cudaMemcpyAsync(h, total, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    *n_labels = *h;
+  }
   return TMAT_OK;
 }
 
+// iterations (optional, host): rounds executed -- asking for it costs a stream synchronisation on the cooperative path.
 static int skeletonize_impl(tmat_ctx* ctx, const uint8_t* mask, int H, int W, uint8_t* out, int* iterations,
                             cudaStream_t st) {
   int64_t n = (int64_t)H * W;
-  CUDA_TRY(cudaMemcpyToSymbolAsync(c_zs_lut, zs_lut_host(), 256, 0, cudaMemcpyHostToDevice, st));
   uint8_t* tmp;
-  unsigned int* counters;
-  constexpr int BATCH = 8;
   TMAT_TRY(arena_get(ctx, (size_t)n, &tmp));
-  TMAT_TRY(arena_get(ctx, BATCH, &counters));
   binarize<<<grid1d(n), 256, 0, st>>>(mask, n, out);
   KERNEL_CHECK(ctx);
+  static const bool no_coop = [] { const char* e = getenv("TMAT_THIN_MULTILAUNCH"); return e && atoi(e) != 0; }();
+  if (!no_coop && (W % 8) == 0 && (reinterpret_cast<uintptr_t>(out) % 8) == 0 && (reinterpret_cast<uintptr_t>(tmp) % 8) == 0) {
+    const int max_rounds = std::min(H, W) / 2 + 2;         // a round that removes something peels one layer
+    uint8_t* d_lut;
+    unsigned int* counters;
+    int* d_iters;
+    TMAT_TRY(arena_get(ctx, 256, &d_lut));
+    TMAT_TRY(arena_get(ctx, (size_t)max_rounds + 2, &counters));      // [max_rounds] counters, then the barrier word
+    TMAT_TRY(arena_get(ctx, 1, &d_iters));
+    // the table goes through the context's pinned page so that the copy is stream-ordered and the call stays asynchronous
+    uint8_t* stage = (uint8_t*)ctx->pinned + 8192 + 256 * (ctx->lut_slot++ & 7);
+    memcpy(stage, zs_lut_host(), 256);
+    CUDA_TRY(cudaMemcpyAsync(d_lut, stage, 256, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemsetAsync(counters, 0, ((size_t)max_rounds + 2) * sizeof(unsigned int), st));
+    static int blocks_per_sm = 0;
+    if (!blocks_per_sm) {
+      CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, thin_persistent, 256, 0));
+      const char* e = getenv("TMAT_THIN_BLOCKS");
+      const int cap_b = e && atoi(e) > 0 ? atoi(e) : 2;
+      if (blocks_per_sm > cap_b) blocks_per_sm = cap_b;      // every block is a participant of the grid barrier
+      if (blocks_per_sm < 1) blocks_per_sm = 1;
+    }
+    const int64_t words = n / 8;
+    int grid = (int)std::min<int64_t>((int64_t)ctx->sm_count * blocks_per_sm, cdiv64(words, 256));
+    if (grid < 1) grid = 1;
+    unsigned int* bar = counters + max_rounds + 1;
+    int Hh = H, Ww = W, mr = max_rounds;
+    const uint8_t* lut_c = d_lut;
+    void* args[] = {(void*)&out, (void*)&tmp, (void*)&Hh, (void*)&Ww, (void*)&lut_c, (void*)&counters, (void*)&mr, (void*)&bar,
+                    (void*)&d_iters};
+    CUDA_TRY(cudaLaunchCooperativeKernel((const void*)thin_persistent, dim3(grid), dim3(256), args, 0, st));
+    ctx->launches++;
+    if (iterations) {
+      int* h = (int*)ctx->pinned;
+      CUDA_TRY(cudaMemcpyAsync(h, d_iters, sizeof(int), cudaMemcpyDeviceToHost, st));
+      CUDA_TRY(cudaStreamSynchronize(st));
+      *iterations = *h;
+    }
+    return TMAT_OK;
+  }
+  // any width: one launch per sub-pass, convergence counters read back every 8 rounds
+  CUDA_TRY(cudaMemcpyToSymbolAsync(c_zs_lut, zs_lut_host(), 256, 0, cudaMemcpyHostToDevice, st));
+  unsigned int* counters;
+  constexpr int BATCH = 8;
+  TMAT_TRY(arena_get(ctx, BATCH, &counters));
   unsigned int* h = (unsigned int*)ctx->pinned;
   int iters = 0;
   for (;;) {
@@ -473,36 +667,37 @@ int filter_branch_impl(tmat_ctx* ctx, const uint8_t* mask, int H, int W, int use
   TMAT_TRY(arena_get(ctx, (size_t)n, &labels));
   if (use_median) TMAT_TRY(median_disk2(ctx, mask, H, W, m, st));
   else { binarize<<<grid1d(n), 256, 0, st>>>(mask, n, m); KERNEL_CHECK(ctx); }
-  int nlab = 0;
-  TMAT_TRY(label_impl(ctx, m, H, W, 2, labels, &nlab, nullptr, st));
+  // no host round trip from here on: per-label arrays are sized by the largest possible number of 8-connected
+  // components, the actual count is read on the device
+  int* nlab_dev = nullptr;
+  TMAT_TRY(label_impl(ctx, m, H, W, 2, labels, nullptr, nullptr, st, &nlab_dev));
+  const size_t cap = (size_t)((H + 1) / 2) * ((W + 1) / 2) + 1;
   unsigned int *area, *hist;
   uint8_t *round_flag, *kill, *has_fork;
   int* sk_root;
-  TMAT_TRY(arena_get(ctx, (size_t)nlab + 1, &area));
-  TMAT_TRY(arena_get(ctx, ((size_t)nlab + 1) * 50, &hist));
-  TMAT_TRY(arena_get(ctx, (size_t)nlab + 2, &round_flag));
-  TMAT_TRY(arena_get(ctx, (size_t)nlab + 2, &kill));
+  TMAT_TRY(arena_get(ctx, cap, &area));
+  TMAT_TRY(arena_get(ctx, cap * 10, &hist));
+  TMAT_TRY(arena_get(ctx, cap + 2, &round_flag));
+  TMAT_TRY(arena_get(ctx, cap + 2, &kill));
   TMAT_TRY(arena_get(ctx, (size_t)n, &has_fork));
   TMAT_TRY(arena_get(ctx, (size_t)n, &sk_root));
-  CUDA_TRY(cudaMemsetAsync(area, 0, ((size_t)nlab + 1) * 4, st));
-  CUDA_TRY(cudaMemsetAsync(hist, 0, ((size_t)nlab + 1) * 200, st));
-  CUDA_TRY(cudaMemsetAsync(round_flag, 0, (size_t)nlab + 2, st));
-  CUDA_TRY(cudaMemsetAsync(kill, 0, (size_t)nlab + 2, st));
+  CUDA_TRY(cudaMemsetAsync(area, 0, cap * 4, st));
+  CUDA_TRY(cudaMemsetAsync(hist, 0, cap * 40, st));
+  CUDA_TRY(cudaMemsetAsync(round_flag, 0, cap + 2, st));
+  CUDA_TRY(cudaMemsetAsync(kill, 0, cap + 2, st));
   CUDA_TRY(cudaMemsetAsync(has_fork, 0, (size_t)n, st));
-  if (nlab > 0) {
-    border_kernel<<<grid2d(H, W), 256, 0, st>>>(labels, H, W, border);
-    KERNEL_CHECK(ctx);
-    region_stats_kernel<<<grid2d(H, W), 256, 0, st>>>(labels, border, H, W, area, hist);
-    KERNEL_CHECK(ctx);
-    circ_flag_kernel<<<cdiv(nlab, 256), 256, 0, st>>>(area, hist, nlab, round_flag);
-    KERNEL_CHECK(ctx);
-    TMAT_TRY(skeletonize_impl(ctx, m, H, W, sk, nullptr, st));
-    TMAT_TRY(ccl_roots(ctx, sk, H, W, 2, 0, sk_root, st));
-    fork_kernel<<<grid2d(H, W), 256, 0, st>>>(sk, H, W, sk_root, has_fork);
-    KERNEL_CHECK(ctx);
-    kill_kernel<<<grid1d(n), 256, 0, st>>>(sk_root, has_fork, labels, round_flag, n, remove_isolated, kill);
-    KERNEL_CHECK(ctx);
-  }
+  border_kernel<<<grid2d(H, W), 256, 0, st>>>(labels, H, W, border);
+  KERNEL_CHECK(ctx);
+  region_stats10_kernel<<<grid2d(H, W), 256, 0, st>>>(labels, border, H, W, area, hist);
+  KERNEL_CHECK(ctx);
+  circ_flag10_kernel<<<(unsigned)cdiv64((int64_t)cap, 256), 256, 0, st>>>(area, hist, nlab_dev, round_flag);
+  KERNEL_CHECK(ctx);
+  TMAT_TRY(skeletonize_impl(ctx, m, H, W, sk, nullptr, st));
+  TMAT_TRY(ccl_roots(ctx, sk, H, W, 2, 0, sk_root, st));
+  fork_kernel<<<grid2d(H, W), 256, 0, st>>>(sk, H, W, sk_root, has_fork);
+  KERNEL_CHECK(ctx);
+  kill_kernel<<<grid1d(n), 256, 0, st>>>(sk_root, has_fork, labels, round_flag, n, remove_isolated, kill);
+  KERNEL_CHECK(ctx);
   apply_kill<<<grid1d(n), 256, 0, st>>>(m, labels, kill, n, out);
   KERNEL_CHECK(ctx);
   return TMAT_OK;

@@ -1,8 +1,8 @@
 // Whole branching-mask path for one image (reference: scripts/compute_branches.py:228, :316-337):
 //   img.max(0) -> rescale_intensity(.., (0,1)).astype(float32) -> model.predict (tiled UNet + D4 + blend)
 //   -> pred > 0.5 -> filter_branch_seg_mask.
-// Every stage runs on the caller's stream on device-resident buffers; nothing returns to the host
-// except the label count and the thinning convergence flags inside the cleanup stage.
+// Every stage runs on the caller's stream on device-resident buffers; nothing returns to the host (the label count
+// and the thinning convergence are read on the device).
 #include "unet.cuh"
 #include <algorithm>
 
@@ -38,6 +38,7 @@ __global__ void __launch_bounds__(256) rescale_unit_f32(const uint16_t* __restri
   double lo = (double)mm[0], hi = (double)mm[1];
   double v = (double)x[i];
   if (hi != lo) v = __ddiv_rn(__dsub_rn(v, lo), __dsub_rn(hi, lo));
+  else v = fmin(fmax(v, 0.0), 1.0);      // a constant image: skimage returns np.clip(image, omin, omax)
   out[i] = (float)v;
 }
 __global__ void __launch_bounds__(256) gt_half(const double* __restrict__ p, int64_t n, uint8_t* __restrict__ m) {

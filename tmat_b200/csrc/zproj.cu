@@ -473,7 +473,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) zproj_focus_u16_fast(const uint
                                    6u * hw[(k + 3) % 5][j];
               bl[j] = (sum + 128u) >> 8;                 // cv2.GaussianBlur: one rounding, fits 16 bits
             }
-            const uint32_t b01 = bl[0] | (bl[1] << 16), b23 = bl[2] | (bl[3] << 16);
+            const uint32_t b01 = __byte_perm(bl[0], bl[1], 0x5410), b23 = __byte_perm(bl[2], bl[3], 0x5410);
             const uint32_t lft = __shfl_up_sync(0xffffffffu, b23, 1);      // (B[-2], B[-1]) from the lane to the left
             const uint32_t rgt = __shfl_down_sync(0xffffffffu, b01, 1);    // (B[4], B[5]) from the lane to the right
             const uint32_t l01 = fsw_dp2a(lft, fsw_c(0, 1), 0);            // B[-1]
@@ -622,7 +622,7 @@ template <typename T>
 int launch_focus_fast_any(tmat_ctx*, const T*, int, int, int, void*, cudaStream_t) { return TMAT_ERR_UNSUPPORTED; }
 template <>
 int launch_focus_fast_any<uint16_t>(tmat_ctx* ctx, const uint16_t* stack, int Z, int H, int W, void* out, cudaStream_t st) {
-  static const int ty = [] { const char* e = getenv("TMAT_FS_TY"); return e ? atoi(e) : 32; }();
+  static const int ty = [] { const char* e = getenv("TMAT_FS_TY"); return e ? atoi(e) : 12; }();
   if (ty == 12) return launch_focus_fast<12, 13>(ctx, stack, Z, H, W, (uint16_t*)out, st);
   if (ty == 22) return launch_focus_fast<22, 8>(ctx, stack, Z, H, W, (uint16_t*)out, st);
   return launch_focus_fast<32, 6>(ctx, stack, Z, H, W, (uint16_t*)out, st);
