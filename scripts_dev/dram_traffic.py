@@ -1,4 +1,4 @@
-"""profiles/r1_dram_traffic.json from the ncu DRAM pass of one bench step (scripts_dev/gpu_final.sh):
+"""profiles/r1_dram_traffic.json from the ncu DRAM pass of one bench step (scripts_dev/gpu.sh dram):
 per-kernel launches, DRAM bytes (read + write) and duration of the LAST step in the launch list."""
 import csv, json, re, sys, collections
 src, dst = sys.argv[1], sys.argv[2]
@@ -25,7 +25,7 @@ for d in step:
     e['launches'] += 1; e['dram_bytes'] += d['bytes']; e['time_us'] += d['ns'] / 1e3
 gemm = [k for k in per if k.startswith(('conv_tc_kernel', 'conv_dwpw_kernel', 'conv_halo_kernel'))]
 out = {'source': 'ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none '
-                 '--cache-control none over bench.py --steps 1 --warmup 3 (scripts_dev/gpu_final.sh); last step of the list',
+                 '--cache-control none over bench.py --steps 1 --warmup 3 (scripts_dev/gpu.sh dram); last step of the list',
        'launches_in_step': len(step), 'gemm_launches': sum(per[k]['launches'] for k in gemm),
        'gemm_dram_bytes_per_step': sum(per[k]['dram_bytes'] for k in gemm),
        'all_dram_bytes_per_step': sum(e['dram_bytes'] for e in per.values()),

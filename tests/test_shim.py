@@ -89,6 +89,9 @@ def test_shim_puts_the_mirrors_behind_the_reference_names(shimmed):
     assert filter_branch_seg_mask is tt.filter_branch_seg_mask and regionprops_image is not None
     from fl_tissue_model_tools import models                                                 # compute_branches.py:38
     assert models.get_unet_patch_segmentor_from_cfg is tm.get_unet_patch_segmentor_from_cfg
+    from fl_tissue_model_tools.dmtgraph import compute_dmt_graph                              # topology.py:12
+    from tmat_b200 import dmtgraph as td
+    assert compute_dmt_graph is td.compute_dmt_graph
     # the reference's script, unmodified, binds the GPU functions
     cz = importlib.import_module("fl_tissue_model_tools.scripts.compute_zproj")
     assert cz.__file__.startswith(REF)

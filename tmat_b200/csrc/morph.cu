@@ -607,7 +607,7 @@ static int skeletonize_impl(tmat_ctx* ctx, const uint8_t* mask, int H, int W, ui
     if (!blocks_per_sm) {
       CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, thin_persistent, 256, 0));
       const char* e = getenv("TMAT_THIN_BLOCKS");
-      const int cap_b = e && atoi(e) > 0 ? atoi(e) : 2;
+      const int cap_b = e && atoi(e) > 0 ? atoi(e) : 4;
       if (blocks_per_sm > cap_b) blocks_per_sm = cap_b;      // every block is a participant of the grid barrier
       if (blocks_per_sm < 1) blocks_per_sm = 1;
     }

@@ -27,6 +27,7 @@ PATCHES = {
     "transforms": ("tmat_b200.transforms", ("filter_branch_seg_mask", "remove_small_islands", "regionprops_image")),
     "well_mask_generation": ("tmat_b200.well_mask_generation", ("auto_threshold_well",)),
     "preprocessing": ("tmat_b200.preprocessing", ("apply_mask", "bin_thresh", "exec_threshold", "blur")),
+    "dmtgraph": ("tmat_b200.dmtgraph", ("compute_dmt_graph",)),
     "models": ("tmat_b200.models", ("UNetXceptionPatchSegmentor", "get_unet_patch_segmentor_from_cfg",
                                     "predict_img_with_smooth_windowing")),
 }
@@ -91,6 +92,10 @@ def install(reference_root=None, modules=None):
                 new = _with_fallback(new, getattr(ref, name))
             _set_attr(ref, name, new)
         report[leaf] = "patched"
+    # topology.py:12 binds compute_dmt_graph by name: rebind it there too when that module is already loaded
+    topo = sys.modules.get(f"{_PKG}.topology")
+    if topo is not None and hasattr(topo, "compute_dmt_graph") and "dmtgraph" in report:
+        _set_attr(topo, "compute_dmt_graph", importlib.import_module("tmat_b200.dmtgraph").compute_dmt_graph)
     _installed = True
     return report
 
