@@ -161,7 +161,7 @@ def reference_arm(args):
     t0 = time.perf_counter()
     pred(batch16, verbose=0)
     est = (time.perf_counter() - t0) * patches_of(size) / 16
-    budget = 240.0
+    budget = 130.0
     steps = int(max(1, min(args.steps, budget // max(est, 1e-3))))
     times = []
     for _ in range(steps):

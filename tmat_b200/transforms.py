@@ -21,6 +21,8 @@ def _mask_u8(mask):
     m = np.asarray(mask)
     if m.ndim != 2:
         raise ValueError(f"expected a 2-D mask, got shape {m.shape}")
+    if m.dtype == np.bool_ and m.flags["C_CONTIGUOUS"]:
+        return m.view(np.uint8)                  # bool is stored as 0 / 1: no copy (the library never writes its inputs)
     return np.ascontiguousarray(m != 0, dtype=np.uint8)
 
 
@@ -129,7 +131,7 @@ def filter_branch_seg_mask(mask, footprint=_DISK2, remove_isolated=True):
     if footprint is None and isinstance(mask, np.ndarray) and mask.flags.writeable:
         mask[...] = out.astype(mask.dtype)
         return mask
-    return out.astype(bool)
+    return out.view(np.bool_)
 
 
 def set_skeletonize_lut(lut):

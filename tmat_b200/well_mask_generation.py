@@ -34,9 +34,10 @@ def auto_threshold_well(image, return_info=False):
         raise TypeError(f"unsupported dtype {img.dtype}")
     img = np.ascontiguousarray(img)
     mask = np.empty(img.shape, dtype=np.uint8)
-    info = (C.c_int * 4)()
+    info = (C.c_int * 4)() if return_info else None          # asking for it costs a device round trip
     _ffi.check(_ffi.lib().tmat_auto_threshold_well_host(_ffi.default_context().handle, _ffi.ptr(img),
                                                         _ffi.DTYPES[img.dtype], *img.shape, _ffi.ptr(mask), info))
+    mask = mask.view(np.bool_)                                # the kernel writes 0 / 1: no copy
     if return_info:
-        return mask.astype(bool), {"invert": bool(info[0]), "otsu": info[1], "u8_min": info[2], "u8_max": info[3]}
-    return mask.astype(bool)
+        return mask, {"invert": bool(info[0]), "otsu": info[1], "u8_min": info[2], "u8_max": info[3]}
+    return mask
