@@ -405,16 +405,29 @@ __global__ void __launch_bounds__(WARPS * 32, 1) zproj_focus_u16_fast(const uint
     const int right_chunk = (W - rx0) >> 2;                  // chunk that starts at column W
     const bool right_edge = right_chunk < 33;
 
+    // the chunks a lane copies are the same for every slice of the tile: their source offset (in 8-byte units from the
+    // slice's first pixel) and shared-memory offset are computed once per tile and packed into one register each
+    constexpr int NPL = (NCHUNK + 31) / 32;
+    uint32_t plan[NPL];
+#pragma unroll
+    for (int k = 0; k < NPL; ++k) {
+      const int c = lane + 32 * k;
+      const int rr = c / 33, i = c - rr * 33;
+      const int x = rx0 + 4 * i;
+      plan[k] = 0xffffffffu;
+      if (c < NCHUNK && x >= 0 && x < W) {
+        const uint32_t goff8 = (uint32_t)(((int64_t)fsw_reflect(ry0 + rr, H) * W + x) >> 2);    // 4 pixels = 8 bytes
+        plan[k] = (goff8 << 11) | (uint32_t)((rr * FSW_ROWB + 8 * i) >> 3);
+      }
+    }
     auto load_slice = [&](int z, int stage) {
       const uint16_t* sl = stack + (int64_t)z * plane;
       const uint32_t sbase = raw_s + stage * STAGE_B;
-#pragma unroll 2
-      for (int c = lane; c < NCHUNK; c += 32) {
-        const int rr = c / 33, i = c - rr * 33;
-        const int x = rx0 + 4 * i;
-        if (x >= 0 && x < W) {
-          const uint16_t* src = sl + (int64_t)fsw_reflect(ry0 + rr, H) * W + x;
-          asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sbase + rr * FSW_ROWB + 8 * i), "l"(src) : "memory");
+#pragma unroll
+      for (int k = 0; k < NPL; ++k) {
+        if (plan[k] != 0xffffffffu) {
+          const uint16_t* src = sl + ((size_t)(plan[k] >> 11) << 2);
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sbase + ((plan[k] & 2047u) << 3)), "l"(src) : "memory");
         }
       }
       asm volatile("cp.async.commit_group;" ::: "memory");
@@ -615,7 +628,8 @@ bool focus_fast_ok(const T*, int, int, int, const void*) { return false; }
 template <>
 bool focus_fast_ok<uint16_t>(const uint16_t* stack, int Z, int H, int W, const void* out) {
   static const bool off = [] { const char* e = getenv("TMAT_FS_GENERIC"); return e && atoi(e) != 0; }();
-  return !off && Z <= 256 && H >= 8 && W >= 8 && (W % 4) == 0 && (reinterpret_cast<uintptr_t>(stack) % 8) == 0 &&
+  return !off && Z <= 256 && H >= 8 && W >= 8 && (W % 4) == 0 && (int64_t)H * W <= (1ll << 23) &&       // 21-bit source offsets in the per-tile copy plan
+         (reinterpret_cast<uintptr_t>(stack) % 8) == 0 &&
          (reinterpret_cast<uintptr_t>(out) % 4) == 0;
 }
 template <typename T>
