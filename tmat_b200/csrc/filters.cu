@@ -335,51 +335,6 @@ extern "C" int tmat_gaussian_host(tmat_ctx* ctx, const void* img_host, int dtype
 }
 
 // ---- auto_threshold_well (well_mask_generation.py:236-277) ------------------------------------------
-// np.median of a uint8 block from its histogram
-static double hist_median(const unsigned int* h) {
-  uint64_t n = 0;
-  for (int i = 0; i < 256; ++i) n += h[i];
-  if (n == 0) return NAN;
-  uint64_t k0 = (n - 1) / 2, k1 = n / 2, acc = 0;
-  int v0 = -1, v1 = -1;
-  for (int i = 0; i < 256; ++i) {
-    acc += h[i];
-    if (v0 < 0 && acc > k0) v0 = i;
-    if (v1 < 0 && acc > k1) { v1 = i; break; }
-  }
-  return ((double)v0 + (double)v1) / 2.0;
-}
-
-// skimage.filters.threshold_otsu on a uint8 image given its 256-bin histogram (numpy dtype semantics:
-// float32 counts and class weights, float64 class means)
-static int otsu_from_hist(const uint64_t* h) {
-  int lo = 0, hi = 255;
-  while (lo < 256 && h[lo] == 0) ++lo;
-  while (hi >= 0 && h[hi] == 0) --hi;
-  if (lo >= hi) return lo > 255 ? 0 : lo;
-  int n = hi - lo + 1;
-  std::vector<float> counts(n), w1(n), w2(n);
-  std::vector<double> cc(n), m1(n), m2(n);
-  for (int i = 0; i < n; ++i) { counts[i] = (float)h[lo + i]; cc[i] = (double)counts[i] * (double)(lo + i); }
-  float a = 0.f;
-  for (int i = 0; i < n; ++i) { a += counts[i]; w1[i] = a; }
-  a = 0.f;
-  for (int i = n - 1; i >= 0; --i) { a += counts[i]; w2[i] = a; }
-  double s = 0.0;
-  for (int i = 0; i < n; ++i) { s += cc[i]; m1[i] = s / (double)w1[i]; }
-  s = 0.0;
-  for (int i = n - 1; i >= 0; --i) { s += cc[i]; m2[i] = s / (double)w2[i]; }
-  int best = 0;
-  double bestv = -1.0;
-  for (int i = 0; i + 1 < n; ++i) {
-    float ww = w1[i] * w2[i + 1];
-    double d = m1[i] - m2[i + 1];
-    double v = (double)ww * (d * d);
-    if (v > bestv) { bestv = v; best = i; }
-  }
-  return lo + best;
-}
-
 static int auto_threshold_impl(tmat_ctx* ctx, const void* img, int dtype, int H, int W, uint8_t* mask, int* info,
                                cudaStream_t st) {
   TMAT_REQUIRE(dtype == TMAT_U8 || dtype == TMAT_U16 || dtype == TMAT_F32 || dtype == TMAT_F64,

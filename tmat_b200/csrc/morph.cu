@@ -3,7 +3,9 @@
 // (regionprops_image), :306-361 (filter_branch_seg_mask), well_mask_generation.py:275 (binary_erosion) and
 // the scikit-image 0.22 primitives they call (filters.median on a bool image, measure.label,
 // regionprops area / perimeter, morphology.skeletonize, remove_small_objects, disk).
-// All integer work: bit-exact.  Masks are uint8 images; any non-zero value is foreground.
+// All integer work, bit-exact against oracle/morphology.py; the scikit-image primitives that oracle restates --
+// above all the thinning table, csrc/skeleton_lut.inc -- are PARITY UNPINNED (scikit-image is installable on no
+// machine this project reaches).  Masks are uint8 images; any non-zero value is foreground.
 #include "common.cuh"
 #include <math.h>
 #include <string.h>
