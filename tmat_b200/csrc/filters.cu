@@ -10,7 +10,8 @@
 #include <algorithm>
 #include <type_traits>
 
-int erode_disk(tmat_ctx* ctx, const uint8_t* in, int H, int W, int r, int border_value, uint8_t* out, cudaStream_t st);
+int erode_disk_thr(tmat_ctx* ctx, const uint8_t* in, int H, int W, int r, int border_value, const int* thr_params_dev,
+                   uint8_t* out, cudaStream_t st);
 
 namespace {
 
@@ -58,9 +59,20 @@ __global__ void __launch_bounds__(256) gauss_axis0(const TIn* __restrict__ in, i
   out[(int64_t)y * W + x] = (TOut)tmp;
 }
 
-// horizontal pass (axis 1): one CTA per row segment, row staged in shared memory with its halo
+// ---- min / max of a float image (exact), via order-preserving integer keys -------------------------
+__device__ __forceinline__ unsigned long long f64_key(double d) {
+  unsigned long long b = (unsigned long long)__double_as_longlong(d);
+  return (b >> 63) ? ~b : (b | 0x8000000000000000ull);
+}
+__device__ __forceinline__ double f64_unkey(unsigned long long k) {
+  return __longlong_as_double((long long)((k >> 63) ? (k & 0x7fffffffffffffffull) : ~k));
+}
+// horizontal pass (axis 1): one CTA per row segment, row staged in shared memory with its halo; mm != nullptr also
+// reduces the exact min / max of the OUTPUT into mm[0], mm[1] (order-preserving keys): auto_threshold_well needs them
+// for rescale_intensity and a separate pass over the blurred image cost 20 us per 2048^2
 template <typename T>
-__global__ void __launch_bounds__(256) gauss_axis1(const T* __restrict__ in, int H, int W, GaussW g, T* __restrict__ out) {
+__global__ void __launch_bounds__(256) gauss_axis1(const T* __restrict__ in, int H, int W, GaussW g, T* __restrict__ out,
+                                                   unsigned long long* __restrict__ mm) {
   __shared__ double s[256 + 2 * GAUSS_MAX_R];
   int y = blockIdx.y;
   int x0 = blockIdx.x * 256;
@@ -71,37 +83,31 @@ __global__ void __launch_bounds__(256) gauss_axis1(const T* __restrict__ in, int
   }
   __syncthreads();
   int x = x0 + threadIdx.x;
-  if (x >= W) return;
-  int c = threadIdx.x + g.R;
-  double tmp = __dmul_rn(s[c], g.w[0]);
-  for (int j = g.R; j >= 1; --j) tmp = __dadd_rn(tmp, __dmul_rn(__dadd_rn(s[c - j], s[c + j]), g.w[j]));
-  out[(int64_t)y * W + x] = (T)tmp;
-}
-
-// ---- min / max of a float image (exact), via order-preserving integer keys -------------------------
-__device__ __forceinline__ unsigned long long f64_key(double d) {
-  unsigned long long b = (unsigned long long)__double_as_longlong(d);
-  return (b >> 63) ? ~b : (b | 0x8000000000000000ull);
-}
-__device__ __forceinline__ double f64_unkey(unsigned long long k) {
-  return __longlong_as_double((long long)((k >> 63) ? (k & 0x7fffffffffffffffull) : ~k));
-}
-__global__ void minmax64_init(unsigned long long* k) { k[0] = ~0ull; k[1] = 0ull; }
-template <typename T>
-__global__ void __launch_bounds__(256) minmax64(const T* __restrict__ x, int64_t n, unsigned long long* k) {
   unsigned long long lo = ~0ull, hi = 0ull;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    unsigned long long e = f64_key((double)x[i]);
-    lo = min(lo, e);
-    hi = max(hi, e);
+  if (x < W) {
+    int c = threadIdx.x + g.R;
+    double tmp = __dmul_rn(s[c], g.w[0]);
+    for (int j = g.R; j >= 1; --j) tmp = __dadd_rn(tmp, __dmul_rn(__dadd_rn(s[c - j], s[c + j]), g.w[j]));
+    const T v = (T)tmp;
+    out[(int64_t)y * W + x] = v;
+    lo = hi = f64_key((double)v);
   }
+  if (mm == nullptr) return;
+  __shared__ unsigned long long s_lo[8], s_hi[8];
   for (int o = 16; o > 0; o >>= 1) {
     lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
     hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
   }
-  if ((threadIdx.x & 31) == 0) { atomicMin(k, lo); atomicMax(k + 1, hi); }
+  if ((threadIdx.x & 31) == 0) { s_lo[threadIdx.x >> 5] = lo; s_hi[threadIdx.x >> 5] = hi; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < 8; ++w) { lo = min(lo, s_lo[w]); hi = max(hi, s_hi[w]); }
+    atomicMin(mm, lo);
+    atomicMax(mm + 1, hi);
+  }
 }
 
+__global__ void minmax64_init(unsigned long long* k) { k[0] = ~0ull; k[1] = 0ull; }
 // rescale_intensity(x, out_range=(0,255)).astype(uint8)  +  the 4 corner histograms + global histogram
 //   y = (x - lo) / (hi - lo);  y = y * 255 + 0;  uint8(trunc(y))      in T's precision (float64 / float32)
 template <typename T>
@@ -139,17 +145,6 @@ __global__ void __launch_bounds__(256) rescale_u8_hist(const T* __restrict__ x, 
   __syncthreads();
   for (int i = threadIdx.x; i < 5 * 256; i += blockDim.x)
     if (sh[i]) atomicAdd(&hist[i], sh[i]);
-}
-
-// params (device, written by otsu_decide_kernel): [0] invert, [1] Otsu threshold, [2] min, [3] max of the (inverted) image
-__global__ void __launch_bounds__(256) threshold_ge_u8(const uint8_t* __restrict__ u8, int64_t n, const int* __restrict__ params,
-                                                       uint8_t* __restrict__ mask) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const int invert = params[0], thr = params[1];
-  int v = u8[i];
-  if (invert) v = 255 - v;
-  mask[i] = v >= thr ? 1 : 0;
 }
 
 // np.median of a uint8 block from its histogram
@@ -256,7 +251,7 @@ static int make_gauss(double sigma, GaussW* g) {
 
 // blur: float64 (H,W) for integer input, float32 for float32 input
 static int gaussian_impl(tmat_ctx* ctx, const void* img, int dtype, int H, int W, double sigma, void* out,
-                         cudaStream_t st) {
+                         cudaStream_t st, unsigned long long* mm = nullptr) {
   GaussW g;
   TMAT_TRY(make_gauss(sigma, &g));
   dim3 grid0(cdiv(W, 256), H), grid1(cdiv(W, 256), H);
@@ -268,21 +263,21 @@ static int gaussian_impl(tmat_ctx* ctx, const void* img, int dtype, int H, int W
     if (dtype == TMAT_U8) gauss_axis0<uint8_t, double><<<grid0, 256, 0, st>>>((const uint8_t*)img, H, W, g, 1.0 / 255.0, tmp);
     else gauss_axis0<uint16_t, double><<<grid0, 256, 0, st>>>((const uint16_t*)img, H, W, g, 1.0 / 65535.0, tmp);
     KERNEL_CHECK(ctx);
-    gauss_axis1<double><<<grid1, 256, 0, st>>>(tmp, H, W, g, (double*)out);
+    gauss_axis1<double><<<grid1, 256, 0, st>>>(tmp, H, W, g, (double*)out, mm);
     KERNEL_CHECK(ctx);
   } else if (dtype == TMAT_F32) {
     float* tmp;
     TMAT_TRY(arena_get(ctx, n, &tmp));
     gauss_axis0<float, float><<<grid0, 256, 0, st>>>((const float*)img, H, W, g, 1.0, tmp);
     KERNEL_CHECK(ctx);
-    gauss_axis1<float><<<grid1, 256, 0, st>>>(tmp, H, W, g, (float*)out);
+    gauss_axis1<float><<<grid1, 256, 0, st>>>(tmp, H, W, g, (float*)out, mm);
     KERNEL_CHECK(ctx);
   } else if (dtype == TMAT_F64) {
     double* tmp;
     TMAT_TRY(arena_get(ctx, n, &tmp));
     gauss_axis0<double, double><<<grid0, 256, 0, st>>>((const double*)img, H, W, g, 1.0, tmp);
     KERNEL_CHECK(ctx);
-    gauss_axis1<double><<<grid1, 256, 0, st>>>(tmp, H, W, g, (double*)out);
+    gauss_axis1<double><<<grid1, 256, 0, st>>>(tmp, H, W, g, (double*)out, mm);
     KERNEL_CHECK(ctx);
   } else {
     tmat_set_error("gaussian: unsupported dtype %d", dtype);
@@ -346,20 +341,16 @@ static int auto_threshold_impl(tmat_ctx* ctx, const void* img, int dtype, int H,
   const bool f32 = (dtype == TMAT_F32);
   void* blur;
   TMAT_TRY(arena_alloc(ctx, n * (f32 ? 4 : 8), &blur));
-  TMAT_TRY(gaussian_impl(ctx, img, dtype, H, W, 1.0, blur, st));
   unsigned long long* keys;
   unsigned int* hist;
-  uint8_t *u8, *thr_mask;
+  uint8_t* u8;
   TMAT_TRY(arena_get(ctx, 2, &keys));
   TMAT_TRY(arena_get(ctx, 5 * 256, &hist));
   TMAT_TRY(arena_get(ctx, n, &u8));
-  TMAT_TRY(arena_get(ctx, n, &thr_mask));
   minmax64_init<<<1, 1, 0, st>>>(keys);
   KERNEL_CHECK(ctx);
+  TMAT_TRY(gaussian_impl(ctx, img, dtype, H, W, 1.0, blur, st, keys));     // min / max of the result reduced in its last pass
   int blocks = (int)std::min<int64_t>(cdiv64((int64_t)n, 256), (int64_t)ctx->sm_count * 8);
-  if (f32) minmax64<float><<<blocks, 256, 0, st>>>((const float*)blur, (int64_t)n, keys);
-  else minmax64<double><<<blocks, 256, 0, st>>>((const double*)blur, (int64_t)n, keys);
-  KERNEL_CHECK(ctx);
   CUDA_TRY(cudaMemsetAsync(hist, 0, 5 * 256 * sizeof(unsigned int), st));
   int xs = (int)(H * 0.05), xe = (int)(H * 0.95), ys = (int)(W * 0.05), ye = (int)(W * 0.95);
   if (f32) rescale_u8_hist<float><<<blocks, 256, 0, st>>>((const float*)blur, H, W, keys, xs, xe, ys, ye, u8, hist);
@@ -369,9 +360,8 @@ static int auto_threshold_impl(tmat_ctx* ctx, const void* img, int dtype, int H,
   TMAT_TRY(arena_get(ctx, 4, &params));
   otsu_decide_kernel<<<1, 256, 0, st>>>(hist, params);
   KERNEL_CHECK(ctx);
-  threshold_ge_u8<<<(unsigned)cdiv64((int64_t)n, 256), 256, 0, st>>>(u8, (int64_t)n, params, thr_mask);
-  KERNEL_CHECK(ctx);
-  TMAT_TRY(erode_disk(ctx, thr_mask, H, W, 5, 1, mask, st));
+  // '>=' (well_mask_generation.py:274) is folded into the erosion's load
+  TMAT_TRY(erode_disk_thr(ctx, u8, H, W, 5, 1, params, mask, st));
   if (info) {      // optional read-back: the only host synchronisation of the call
     int* h = (int*)ctx->pinned;
     CUDA_TRY(cudaMemcpyAsync(h, params, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
