@@ -274,6 +274,18 @@ int tmat_centerline_weight_dev(tmat_ctx* ctx, const double* pred_dev, const uint
 int tmat_centerline_weight_host(tmat_ctx* ctx, const double* pred_host, const uint8_t* mask_host,
                                 const uint8_t* skel_host, int H, int W, double* out_host);
 
+/* ---- preprocessing.py:96-163: gen_circ_mask, dt_blur, sdt_blur (notebook / training helpers) ---- */
+/* cv2.distanceTransform(mask, cv2.DIST_L2, 5) (preprocessing.py:132-134, :155-160): float32 5x5 chamfer distance of
+ * every non-zero pixel to the nearest zero pixel (invert != 0: of logical_not(mask)).  Closed-form chamfer metric;
+ * matches OpenCV's raster-scan float32 accumulation to ~1e-6 relative (a tolerance, not bit-exact). */
+int tmat_distance_transform_cv5_dev(tmat_ctx* ctx, const uint8_t* mask_dev, int H, int W, int invert,
+                                    float* out_dev, void* stream);
+int tmat_distance_transform_cv5_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W, int invert,
+                                     float* out_host);
+/* cv2.circle(zeros((H, W), uint8), (cx, cy), r, val, -1) (preprocessing.py:113-114): OpenCV's integer midpoint
+ * circle, bit-exact. */
+int tmat_circle_mask_host(tmat_ctx* ctx, int H, int W, int cx, int cy, int r, int val, uint8_t* out_host);
+
 /* ---- the Morse graph built from the weighted prediction -------------- */
 /* dmtgraph.py:38-99 compute_dmt_graph(img, delta1, delta2) (native twin: pydmtgraph DMTGraph.cpp:232-615).
  * Sequential union-find sweeps in filtration order: native HOST code in this library (no kernel; needs no GPU).

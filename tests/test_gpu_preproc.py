@@ -74,3 +74,44 @@ def test_exec_threshold_golden_and_rng_stream(golden):
     b = prep.exec_threshold(masked, np.nonzero(mask), -0.5, np.random.RandomState(123))
     assert ((b > 0) == (g["exec_threshold_idx"] > 0)).mean() >= 0.999
     assert np.array_equal(b[b > 0], masked[b > 0])
+
+
+def test_gen_circ_mask_bit_exact_vs_cv2():
+    """preprocessing.py:96-116: cv2.circle(..., thickness=-1), OpenCV's integer midpoint circle."""
+    import cv2
+    from tmat_b200 import preprocessing as prep
+    for (cx, cy), r, shape, val in (((80, 75), 33, (160, 170), 1), ((10, 12), 0, (30, 40), 255), ((5, 40), 25, (64, 48), 7),
+                                    ((-4, 10), 20, (50, 60), 3), ((30, 30), 200, (61, 61), 1), ((20, 7), 1, (15, 41), 9)):
+        ref = np.zeros(shape, np.uint8)
+        cv2.circle(ref, (cx, cy), r, val, -1)
+        out = prep.gen_circ_mask((cx, cy), r, shape, val)
+        assert out.dtype == np.uint8 and np.array_equal(out, ref), ((cx, cy), r, shape)
+
+
+def test_dt_blur_and_sdt_blur_vs_cv2_within_tolerance():
+    """preprocessing.py:118-163.  The 5x5 chamfer transform is a closed form here and a float32 raster scan in OpenCV:
+    distances agree to 1e-5 relative; after the reference's rounding the uint8 image differs in < 0.1 % of the pixels
+    by one grey level."""
+    import cv2
+    import helpers
+    from tmat_b200 import preprocessing as prep
+    m = helpers.synth_mask(200, 230, 5, density=0.3)
+    m[60:140, 80:170] = True                                   # a large blob: distances up to ~40
+    img = m.astype(np.float32) * 0.7
+    mask = np.where(img > 0, 255, 0).round().astype(np.uint8)
+    ref_dt = cv2.distanceTransform(mask, cv2.DIST_L2, 5)
+    got_dt = prep._chamfer5(mask)
+    assert got_dt.dtype == np.float32
+    assert np.abs(got_dt - ref_dt).max() <= 1e-5 * max(1.0, float(ref_dt.max()))
+    ref_in = cv2.distanceTransform(np.logical_not(mask).astype(np.uint8), cv2.DIST_L2, 5)
+    assert np.abs(prep._chamfer5(mask, invert=True) - ref_in).max() <= 1e-5 * max(1.0, float(ref_in.max()))
+    # dt_blur: uint8 result of the reference's own composition (cv2 transform + the oracle's blur restatement)
+    ref = ot.blur(ref_dt, 2, 3)
+    out = prep.dt_blur(img, 2)
+    assert out.dtype == ref.dtype == np.uint8
+    d = np.abs(out.astype(int) - ref.astype(int))
+    assert d.max() <= 1 and (d > 0).mean() < 1e-3, (int(d.max()), float((d > 0).mean()))
+    ref_s = ot.blur(ref_dt - ref_in, 1, 3, gs=False)
+    out_s = prep.sdt_blur(img, 1)
+    assert out_s.dtype == np.float32 and np.abs(out_s - ref_s).max() <= 1.0
+    assert (out_s != ref_s).mean() < 1e-3

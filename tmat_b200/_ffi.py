@@ -100,6 +100,9 @@ SIGNATURES = {
     "tmat_distance_transform_edt_host": [_vp, _vp, _i, _i, _i, _vp],
     "tmat_centerline_weight_dev": [_vp, _vp, _vp, _vp, _i, _i, _vp, _vp],
     "tmat_centerline_weight_host": [_vp, _vp, _vp, _vp, _i, _i, _vp],
+    "tmat_distance_transform_cv5_dev": [_vp, _vp, _i, _i, _i, _vp, _vp],
+    "tmat_distance_transform_cv5_host": [_vp, _vp, _i, _i, _i, _vp],
+    "tmat_circle_mask_host": [_vp, _i, _i, _i, _i, _i, _i, _vp],
     "tmat_dmt_graph_host": [_vp, _i, _i, C.c_float, C.c_float, _vp, _i64, C.POINTER(_i64), _vp, _i64, C.POINTER(_i64)],
     "tmat_resize_dev": [_vp, _vp, _i, _i, _i, _vp, _i, _i, _i, _vp],
     "tmat_resize_host": [_vp, _vp, _i, _i, _i, _vp, _i, _i, _i],

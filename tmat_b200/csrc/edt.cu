@@ -156,3 +156,107 @@ extern "C" int tmat_centerline_weight_host(tmat_ctx* ctx, const double* pred_hos
   if (rc == TMAT_ERR_CUDA) tmat_set_error("tmat_centerline_weight_host: %s", cudaGetErrorString(cudaGetLastError()));
   return rc;
 }
+
+// ---- cv2.distanceTransform(mask, cv2.DIST_L2, 5) and cv2.circle(..., thickness=-1) -----------------------------------
+// preprocessing.py:96-163 (gen_circ_mask, dt_blur, sdt_blur; notebook / training helpers).
+// OpenCV's 5x5 chamfer transform walks the image in two raster scans adding 1.0f / 1.4f / 2.1969f per step in
+// float32.  In free space the cheapest chamfer path between two pixels has a closed form (dx >= dy: dy knight moves +
+// (dx - 2 dy) straight ones if 2 dy <= dx, else (dx - dy) knight moves + (2 dy - dx) diagonal ones), and the cost is
+// monotone in |dy|, so the same two passes as the exact EDT apply with that metric.  The closed form adds the same
+// steps in a different ORDER than the raster scan: parity with OpenCV is ~1e-6 relative (a tolerance, stated in
+// tests/test_gpu_preproc.py), exact after the reference's .round().astype(uint8) except at ties.
+namespace {
+
+__device__ __forceinline__ float chamfer5(int dx, int dy) {
+  const int mx = max(dx, dy), mn = min(dx, dy);
+  if (2 * mn <= mx) return __fadd_rn(__fmul_rn(2.1969f, (float)mn), (float)(mx - 2 * mn));
+  return __fadd_rn(__fmul_rn(2.1969f, (float)(mx - mn)), __fmul_rn(1.4f, (float)(2 * mn - mx)));
+}
+__global__ void __launch_bounds__(256) chamfer_rows(const unsigned int* __restrict__ g, int H, int W, float* __restrict__ out) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  if (x >= W) return;
+  const unsigned int* grow = g + (int64_t)y * W;
+  const unsigned int g0 = grow[x];
+  float best = g0 == EDT_INF ? 3.0e38f : (float)g0;
+  for (int d = 1; d < W; ++d) {
+    if ((float)d >= best) break;                         // a path that moves d columns costs at least d
+    const int xl = x - d, xr = x + d;
+    if (xl < 0 && xr >= W) break;
+    if (xl >= 0) { const unsigned int gv = grow[xl]; if (gv != EDT_INF) best = fminf(best, chamfer5(d, (int)gv)); }
+    if (xr < W) { const unsigned int gv = grow[xr]; if (gv != EDT_INF) best = fminf(best, chamfer5(d, (int)gv)); }
+  }
+  out[(int64_t)y * W + x] = best;
+}
+__global__ void __launch_bounds__(256) circle_fill(int H, int W, int cx, int cy, int r, const int* __restrict__ half_width,
+                                                   uint8_t val, uint8_t* __restrict__ out) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  if (x >= W) return;
+  const int dy = abs(y - cy);
+  out[(int64_t)y * W + x] = (dy <= r && abs(x - cx) <= half_width[dy]) ? val : (uint8_t)0;
+}
+
+}  // namespace
+
+extern "C" int tmat_distance_transform_cv5_dev(tmat_ctx* ctx, const uint8_t* mask_dev, int H, int W, int invert,
+                                               float* out_dev, void* stream) {
+  TMAT_REQUIRE(ctx && mask_dev && out_dev && H >= 1 && W >= 1, "tmat_distance_transform_cv5: bad argument");
+  TMAT_TRY(arena_reset(ctx));
+  cudaStream_t st = as_stream(stream);
+  unsigned int* g;
+  TMAT_TRY(arena_get(ctx, (size_t)H * W, &g));
+  edt_columns<<<cdiv(W, 128), 128, 0, st>>>(mask_dev, H, W, invert, g);
+  KERNEL_CHECK(ctx);
+  chamfer_rows<<<dim3(cdiv(W, 256), H), 256, 0, st>>>(g, H, W, out_dev);
+  KERNEL_CHECK(ctx);
+  return TMAT_OK;
+}
+
+extern "C" int tmat_distance_transform_cv5_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W, int invert,
+                                                float* out_host) {
+  TMAT_REQUIRE(ctx && mask_host && out_host && H >= 1 && W >= 1, "tmat_distance_transform_cv5_host: bad argument");
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  const size_t n = (size_t)H * W;
+  char* blk = nullptr;
+  CUDA_TRY(cudaMalloc((void**)&blk, n * 5));
+  float* d_out = (float*)blk;
+  uint8_t* d_in = (uint8_t*)(blk + n * 4);
+  int rc = cudaMemcpyAsync(d_in, mask_host, n, cudaMemcpyHostToDevice, 0) == cudaSuccess ? TMAT_OK : TMAT_ERR_CUDA;
+  if (rc == TMAT_OK) rc = tmat_distance_transform_cv5_dev(ctx, d_in, H, W, invert, d_out, nullptr);
+  if (rc == TMAT_OK && cudaMemcpyAsync(out_host, d_out, n * 4, cudaMemcpyDeviceToHost, 0) != cudaSuccess) rc = TMAT_ERR_CUDA;
+  if (cudaStreamSynchronize(0) != cudaSuccess && rc == TMAT_OK) rc = TMAT_ERR_CUDA;
+  cudaFree(blk);
+  if (rc == TMAT_ERR_CUDA) tmat_set_error("tmat_distance_transform_cv5_host: %s", cudaGetErrorString(cudaGetLastError()));
+  return rc;
+}
+
+// cv2.circle(img, (cx, cy), r, val, -1) on a zero image: OpenCV's integer midpoint circle (drawing.cpp Circle()),
+// reproduced exactly -- the per-row half widths come from the same error recurrence.
+extern "C" int tmat_circle_mask_host(tmat_ctx* ctx, int H, int W, int cx, int cy, int r, int val, uint8_t* out_host) {
+  TMAT_REQUIRE(ctx && out_host && H >= 1 && W >= 1 && r >= 0, "tmat_circle_mask: bad argument");
+  TMAT_REQUIRE(val >= 0 && val <= 255, "tmat_circle_mask: mask_val %d outside [0, 255]", val);
+  CUDA_TRY(cudaSetDevice(ctx->device));
+  std::vector<int> hw((size_t)r + 1, -1);
+  int err = 0, dx = r, dy = 0, plus = 1, minus = (r << 1) - 1;
+  while (dx >= dy) {
+    hw[dy] = std::max(hw[dy], dx);
+    hw[dx] = std::max(hw[dx], dy);
+    dy++;
+    err += plus;
+    plus += 2;
+    const int mask = (err <= 0) - 1;
+    err -= minus & mask;
+    dx += mask;
+    minus -= mask & 2;
+  }
+  TMAT_TRY(arena_reset(ctx));
+  int* d_hw;
+  uint8_t* d_out;
+  TMAT_TRY(arena_get(ctx, hw.size(), &d_hw));
+  TMAT_TRY(arena_get(ctx, (size_t)H * W, &d_out));
+  CUDA_TRY(cudaMemcpyAsync(d_hw, hw.data(), hw.size() * sizeof(int), cudaMemcpyHostToDevice, 0));
+  circle_fill<<<dim3(cdiv(W, 256), H), 256>>>(H, W, cx, cy, r, d_hw, (uint8_t)val, d_out);
+  KERNEL_CHECK(ctx);
+  CUDA_TRY(cudaMemcpyAsync(out_host, d_out, (size_t)H * W, cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaStreamSynchronize(0));
+  return TMAT_OK;
+}

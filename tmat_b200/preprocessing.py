@@ -49,6 +49,44 @@ def blur(img, blur_itr, k_size=3, gs=True):
     return out
 
 
+DIST_L2 = 2          # cv2.DIST_L2
+
+
+def gen_circ_mask(center, radius, shape, mask_val=1):
+    """preprocessing.py:96-116: ``cv2.circle(zeros(shape, uint8), center, radius, mask_val, -1)``; ``center`` is
+    (column, row).  OpenCV's integer midpoint circle, bit-exact."""
+    h, w = int(shape[0]), int(shape[1])
+    out = np.empty((h, w), np.uint8)
+    _ffi.check(_ffi.lib().tmat_circle_mask_host(_ffi.default_context().handle, h, w, int(center[0]), int(center[1]),
+                                                int(radius), int(mask_val), _ffi.ptr(out)))
+    return out
+
+
+def _chamfer5(mask_u8, invert=False):
+    m = np.ascontiguousarray(mask_u8, dtype=np.uint8)
+    out = np.empty(m.shape, np.float32)
+    _ffi.check(_ffi.lib().tmat_distance_transform_cv5_host(_ffi.default_context().handle, _ffi.ptr(m), m.shape[0],
+                                                           m.shape[1], int(invert), _ffi.ptr(out)))
+    return out
+
+
+def dt_blur(img, blur_itr, dist_metric=DIST_L2, k_size=3):
+    """preprocessing.py:118-135: ``cv2.distanceTransform(bin_thresh(img, 255).round().astype(uint8), DIST_L2, 5)`` then
+    ``blur`` (uint8 out).  The chamfer transform matches OpenCV to ~1e-6 relative (see csrc/edt.cu)."""
+    if dist_metric != DIST_L2:
+        raise NotImplementedError("dt_blur: cv2.DIST_L2 (the reference's default) is built")
+    mask = (np.asarray(img) > 0).astype(np.uint8)
+    return blur(_chamfer5(mask), blur_itr, k_size)
+
+
+def sdt_blur(img, blur_itr, dist_metric=DIST_L2, k_size=3):
+    """preprocessing.py:138-163: signed distance (inside minus outside) then ``blur(..., gs=False)`` (float32 out)."""
+    if dist_metric != DIST_L2:
+        raise NotImplementedError("sdt_blur: cv2.DIST_L2 (the reference's default) is built")
+    mask = (np.asarray(img) > 0).astype(np.uint8)
+    return blur(_chamfer5(mask) - _chamfer5(mask, invert=True), blur_itr, k_size, gs=False)
+
+
 def gmm_foreground_threshold(pixels, sd_coef, rand_state, return_params=False):
     """The scalar of preprocessing.py:75-87: 2-component GMM on ``pixels`` (1-D), threshold =
     ``min(255, mean_fg + sd_coef * sd_fg)``.  The three uniform draws scikit-learn's k-means++ seeding would

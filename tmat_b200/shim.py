@@ -26,7 +26,8 @@ PATCHES = {
     "smooth_tiled_predictions": ("tmat_b200.smooth_tiled_predictions", ("predict_img_with_smooth_windowing",)),
     "transforms": ("tmat_b200.transforms", ("filter_branch_seg_mask", "remove_small_islands", "regionprops_image")),
     "well_mask_generation": ("tmat_b200.well_mask_generation", ("auto_threshold_well",)),
-    "preprocessing": ("tmat_b200.preprocessing", ("apply_mask", "bin_thresh", "exec_threshold", "blur")),
+    "preprocessing": ("tmat_b200.preprocessing", ("apply_mask", "bin_thresh", "exec_threshold", "blur", "dt_blur", "sdt_blur",
+                                                   "gen_circ_mask")),
     "dmtgraph": ("tmat_b200.dmtgraph", ("compute_dmt_graph",)),
     "models": ("tmat_b200.models", ("UNetXceptionPatchSegmentor", "get_unet_patch_segmentor_from_cfg",
                                     "predict_img_with_smooth_windowing")),
