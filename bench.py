@@ -22,7 +22,8 @@ Keys beyond the base contract:
   e2e           the public Python call with host buffers, H2D/D2H inside the timed region.
   stages        after the timed region: C2 (five Z projections of a 32x2048x2048 uint16 stack: ms, algorithmic GB/s,
                 fraction of the measured HBM copy peak) and C3 (auto_threshold_well + filter_branch_seg_mask over a
-                batch of 2048^2 images per rank: images/s kernels-only and end-to-end).
+                batch of 2048^2 images per rank: images/s kernels-only and end-to-end) and C4 (the whole mask path, stack
+                in -> cleaned mask out, one image per rank: ms, MP/s).
   c5            one 8192x8192 image, 256-px windows, owner-computes row strips over the N ranks (+ one all_gather):
                 ms, MP/s, redundant patches -- so the driver's 1/2/4/8 run records the row-strip split too.
 
@@ -299,6 +300,29 @@ def stages_leg(ctx, world, rank, pk):
                  "e2e": "numpy in -> H2D -> kernels -> D2H -> numpy out through the Python mirrors, one image at a time",
                  "floor_bytes_per_image": floor_bytes,
                  "frac_of_hbm_floor": round(floor_bytes * B / (ms * 1e-3) / 1e9 / pk["hbm"], 4)}
+    del wells, segs
+
+    # C4: the WHOLE branching-mask path for one image per rank per step (compute_branches.py:228, 316-337):
+    # (32, 2048, 2048) uint16 stack -> max projection -> [0, 1] rescale -> tiled UNet x8 D4 + blend -> > 0.5 -> cleanup
+    from tmat_b200 import models
+    net = models.CudaUNet(models.random_init_weights(FILTERS, seed=0), WS, FILTERS, impl="tc", ctx=ctx)
+    g = torch.Generator(device="cuda").manual_seed(4000 + rank)
+    st4 = torch.randint(200, 30000, (Z, S, S), generator=g, device="cuda", dtype=torch.int32).to(torch.int16)
+    d_pred = torch.empty((S, S), dtype=torch.float64, device="cuda")
+    d_mask = torch.empty((S, S), dtype=torch.uint8, device="cuda")
+
+    def full_path():
+        _ffi.check(L.tmat_branch_mask_dev(ctx.handle, net._tmat_handle, _ffi.ptr(st4), Z, S, S, SUBDIV, _ffi.ptr(d_pred),
+                                          _ffi.ptr(d_mask), sptr))
+    ms = timed(full_path, iters=3, warm=2)
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    out["C4"] = {"workload": f"whole mask path per image: ({Z},{S},{S}) uint16 stack -> max projection -> rescale -> tiled UNet "
+                             "(ws 320, 8x D4) + blend -> > 0.5 -> filter_branch_seg_mask; one image per rank per step",
+                 "n_gpus": world, "ms_per_image": round(ms, 3), "MP/s": round(world * S * S / 1e6 / (ms / 1e3), 2)}
+    net.close()
     return out
 
 
