@@ -266,6 +266,16 @@ int tmat_distance_transform_edt_dev(tmat_ctx* ctx, const uint8_t* mask_dev, int 
                                     double* out_dev, void* stream);
 int tmat_distance_transform_edt_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W, int invert,
                                      double* out_host);
+/* Allocation-free variant of tmat_distance_transform_edt_dev.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same result, bit for bit.  Takes no context: it runs on the calling thread's CURRENT
+ * device, on `stream`, and calls no cudaMalloc / cudaFree / allocating routine -- its one scratch plane is a
+ * file-scope __device__ array of TMAT_EDT_STATIC_MAX_PIXELS uint32 (16 MiB per GPU that loads the library, held until
+ * exit).  H * W beyond that limit is rejected with TMAT_ERR_INVALID (tmat_last_error names the limit).  Every call
+ * shares the array: calls that overlap on the GPU (two streams, two threads on one device) race -- serialise them. */
+#define TMAT_EDT_STATIC_MAX_PIXELS (1 << 22)
+int tmat_distance_transform_edt_static_dev(const uint8_t* mask_dev, int H, int W, int invert,
+                                           double* out_dev, void* stream);
 /* scripts/compute_branches.py:341-344: out = pred * dist / (dist + centerline_dt), dist = edt(seg_mask),
  * centerline_dt = edt(~skel).  The skeleton is an input: medial_axis breaks ties with an unseeded RNG in the
  * reference and is not reproducible even against itself. */

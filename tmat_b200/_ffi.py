@@ -98,6 +98,7 @@ SIGNATURES = {
     "tmat_skeletonize_host": [_vp, _vp, _i, _i, _vp, _pi],
     "tmat_distance_transform_edt_dev": [_vp, _vp, _i, _i, _i, _vp, _vp],
     "tmat_distance_transform_edt_host": [_vp, _vp, _i, _i, _i, _vp],
+    "tmat_distance_transform_edt_static_dev": [_vp, _i, _i, _i, _vp, _vp],
     "tmat_centerline_weight_dev": [_vp, _vp, _vp, _vp, _i, _i, _vp, _vp],
     "tmat_centerline_weight_host": [_vp, _vp, _vp, _vp, _i, _i, _vp],
     "tmat_distance_transform_cv5_dev": [_vp, _vp, _i, _i, _i, _vp, _vp],

@@ -260,3 +260,51 @@ extern "C" int tmat_circle_mask_host(tmat_ctx* ctx, int H, int W, int cx, int cy
   CUDA_TRY(cudaStreamSynchronize(0));
   return TMAT_OK;
 }
+
+// ---- allocation-free variant of the exact EDT -------------------------------------------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (CUDA graph capture, tight serving loops, harnesses that forbid it).  The column-distance plane `g` that
+// tmat_distance_transform_edt_dev takes from the context arena lives here in a file-scope device array of
+// TMAT_EDT_STATIC_MAX_PIXELS uint32 (16 MiB, held by every GPU that loads the library until the process exits).
+// In host code the array's NAME is only a stand-in for the symbol, not a device address: the address is looked up once
+// per device, with that device current, by cudaGetSymbolAddress and that pointer is what the kernels receive.
+// Nothing here needs to start at zero: edt_columns overwrites every element of the H*W prefix that edt_rows reads, so
+// the previous call's contents never show through.  All calls share the one array: calls whose kernels overlap on the
+// GPU (different streams, different host threads on the same device) race -- serialise them.
+#include <mutex>
+
+static __device__ __align__(256) unsigned int g_edt_static_scratch[TMAT_EDT_STATIC_MAX_PIXELS];
+
+namespace {
+constexpr int EDT_STATIC_MAX_DEVICES = 64;
+std::mutex g_edt_static_mu;
+unsigned int* g_edt_static_ptr[EDT_STATIC_MAX_DEVICES];          // per device; nullptr until first use there
+}  // namespace
+
+extern "C" int tmat_distance_transform_edt_static_dev(const uint8_t* mask_dev, int H, int W, int invert,
+                                                      double* out_dev, void* stream) {
+  TMAT_REQUIRE(mask_dev && out_dev && H >= 1 && W >= 1, "tmat_distance_transform_edt_static: bad argument");
+  TMAT_REQUIRE(H <= 65535 && W <= 65535 && (int64_t)H * W <= (int64_t)TMAT_EDT_STATIC_MAX_PIXELS,
+               "tmat_distance_transform_edt_static: %d x %d = %lld pixels exceed the static scratch of %d pixels "
+               "(TMAT_EDT_STATIC_MAX_PIXELS); use tmat_distance_transform_edt_dev for larger images",
+               H, W, (long long)H * W, (int)TMAT_EDT_STATIC_MAX_PIXELS);
+  int dev = -1;
+  CUDA_TRY(cudaGetDevice(&dev));
+  TMAT_REQUIRE(dev >= 0 && dev < EDT_STATIC_MAX_DEVICES, "tmat_distance_transform_edt_static: device %d out of range", dev);
+  unsigned int* g = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_edt_static_mu);
+    if (!g_edt_static_ptr[dev]) {                                // set-up, once per device, that device current
+      void* p = nullptr;
+      CUDA_TRY(cudaGetSymbolAddress(&p, g_edt_static_scratch));
+      g_edt_static_ptr[dev] = (unsigned int*)p;
+    }
+    g = g_edt_static_ptr[dev];
+  }
+  cudaStream_t st = as_stream(stream);
+  edt_columns<<<cdiv(W, 128), 128, 0, st>>>(mask_dev, H, W, invert, g);
+  CUDA_TRY(cudaGetLastError());
+  edt_rows<<<dim3(cdiv(W, 256), H), 256, 0, st>>>(g, H, W, out_dev);
+  CUDA_TRY(cudaGetLastError());
+  return TMAT_OK;
+}
