@@ -9,6 +9,8 @@
 #   launches [env]  ncu launch list (gpu__time_duration) of one 64-patch chunk -> gpurun_out/launches.csv
 #   dram            ncu launch list + DRAM bytes of one full 2048^2 step -> gpurun_out/dram_2048.csv
 #   ncu <regex> [skip] [count]   ncu --set full of matching kernels in a 64-patch chunk -> gpurun_out/ncu_<tag>.ncu-rep
+#   noalloc         tests/test_zz_no_alloc.py alone in a fresh process
+#   ncu4            ncu --set full of the stage 3/4 kernels (one C3 image)
 #   stages          scripts/bench_stages.py (C2/C3 stage table)
 mkdir -p gpurun_out
 mode=$1; shift
@@ -62,6 +64,13 @@ ncu)
   rx=$1; skip=${2:-0}; cnt=${3:-8}; tag=$(echo "$rx" | tr -c 'A-Za-z0-9_\n' '_')
   TMAT_CHUNK=64 timeout 900 ncu --set full --import-source on --clock-control none -k regex:"$rx" --launch-skip $skip --launch-count $cnt -o gpurun_out/ncu_$tag -f python bench.py --size 1024 --steps 1 --warmup 3 --no-cpu-baseline --no-e2e --no-extras > gpurun_out/ncu_full.log 2>&1
   echo "ncu full exit $?"
+  ;;
+noalloc)   # the allocation-free entry point: alone in a fresh process, then again after the whole suite (verify)
+  timeout 600 python -m pytest tests/test_zz_no_alloc.py -m gpu -x -q 2>&1 | tail -8 | cut -c1-300
+  ;;
+ncu4)      # ncu --set full of the stage 3/4 kernels over one C3 image -> gpurun_out/ncu_stage4.ncu-rep
+  timeout 900 ncu --set full --import-source on --clock-control none -k regex:"thin_|ccl_|erode_disk|root_|gauss_|otsu_|median_|footprint_|border_" --launch-count 60 -o gpurun_out/ncu_stage4 -f python scripts/bench_stages.py --config C3 --no-cpu --iters 1 > gpurun_out/ncu_stage4.log 2>&1
+  echo "ncu stage4 exit $?"; tail -3 gpurun_out/ncu_stage4.log
   ;;
 stages)
   timeout 900 python scripts/bench_stages.py "$@" 2>&1 | tail -40
