@@ -192,6 +192,25 @@ int tmat_auto_threshold_well_dev(tmat_ctx* ctx, const void* img_dev, int dtype, 
                                  uint8_t* mask_dev, int* info, void* stream);
 int tmat_auto_threshold_well_host(tmat_ctx* ctx, const void* img_host, int dtype, int H, int W,
                                   uint8_t* mask_host, int* info);
+/* The numpy-only pieces of generate_well_mask (well_mask_generation.py:16-140).
+ * get_superellipse_hull(x, y, n, num_iters) :16-91 -- params (num_iters x 6: theta, d, s_a, s_b, c_x, c_y) are the
+ * parameter sets as the reference draws them (np.random.rand mapped into the bounds, done by the caller with numpy so
+ * that the global seed decides the same draw), cos/sin = np.cos / np.sin of theta (may be NULL for n == 2, where the
+ * reference ignores theta), gamma1_sq = gamma(1 + 1/n)**2, gamma2 = gamma(1 + 2/n).  best_index = the first parameter
+ * set of smallest area among those with max_j f(x_j, y_j) < 1, or -1 when none encloses the points (the reference's
+ * np.argmin of an empty array raises ValueError there). */
+int tmat_superellipse_hull_host(tmat_ctx* ctx, const double* x_host, const double* y_host, int n_points, int n,
+                                const double* params_host, const double* cos_host, const double* sin_host,
+                                int num_iters, double gamma1_sq, double gamma2, int* best_index);
+/* gen_superellipse_mask :94-118: out[a][b] = |((xs[a]-c_x) cos - (ys[b]-c_y) sin) / d_sa|**n +
+ * |((xs[a]-c_x) sin + (ys[b]-c_y) cos) / d_sb|**n < 1, xs = linspace(-1, 1, n0), ys = linspace(-1, 1, n1),
+ * d_sa = d * s_a, d_sb = d * s_b; out uint8 0/1, n0 x n1 (the reference's swapaxes is folded in). */
+int tmat_superellipse_mask_host(tmat_ctx* ctx, const double* xs_host, int n0, const double* ys_host, int n1,
+                                double c_x, double c_y, double cos_t, double sin_t, double d_sa, double d_sb, int n,
+                                uint8_t* out_host);
+/* create_convex_hull_mask :121-140 (scipy Delaunay(hull).find_simplex(pixel) >= 0): pixels inside or on the convex
+ * polygon verts (n_verts x 2 int32 (row, col), in polygon order, either orientation); exact integer arithmetic. */
+int tmat_convex_hull_mask_host(tmat_ctx* ctx, int H, int W, const int32_t* verts_host, int n_verts, uint8_t* out_host);
 
 /* ---- stage 4: binary morphology / component cleanup --------------------------------- */
 /* skimage.filters.median(bool mask, disk(2)) (transforms.py:323) */
@@ -227,8 +246,10 @@ int tmat_remove_small_islands_host(tmat_ctx* ctx, const uint8_t* mask_host, int 
                                    int connectivity1, uint8_t* out_host);
 /* transforms.py:291-303 regionprops_image(mask, 'area'): float64 image of component areas */
 int tmat_area_image_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W, double* out_host);
-/* the same for the area-like properties the reference's callers use (scripts/compute_branches.py:276-277):
- * prop 0 = 'area', 1 = 'equivalent_diameter_area' (= sqrt(4*area/pi), as skimage.measure.regionprops). */
+/* the same for the properties the reference's callers use (scripts/compute_branches.py:276-277):
+ * prop 0 = 'area', 1 = 'equivalent_diameter_area' (= sqrt(4*area/pi), as skimage.measure.regionprops),
+ * 2 = 'eccentricity' (sqrt(1 - l2/l1) of the inertia-tensor eigenvalues, 0 when l1 == 0; moments accumulated exactly
+ * in integers -- skimage's float64 dot products differ by rounding, parity is a tolerance and unpinned). */
 int tmat_region_prop_image_host(tmat_ctx* ctx, const uint8_t* mask_host, int H, int W, int prop,
                                 double* out_host);
 /* Rank filter of a boolean image under an arbitrary footprint (fh x fw bytes, non-zero = member, both odd;

@@ -205,3 +205,27 @@ def regionprops_image_area(mask):
     lab, n = label(mask, 2)
     props = np.insert(region_areas(lab, n).astype(np.float64), 0, 0)
     return props[lab]
+
+
+def regionprops_image_eccentricity(mask):
+    """transforms.py:291-303 with prop='eccentricity' (compute_branches.py:276), restating scikit-image 0.22's
+    RegionProperties: moments_central of the bounding-box crop about its centroid (float64 dot products),
+    inertia tensor [[mu02, -mu11], [-mu11, mu20]] / mu00, eigvalsh clipped at 0 and sorted descending,
+    eccentricity = 0 if l1 == 0 else sqrt(1 - l2 / l1).  PARITY UNPINNED: scikit-image is not installable here."""
+    lab, n = label(np.asarray(mask) != 0, 2)
+    out = np.zeros(lab.shape, dtype=np.float64)
+    for k, sl in enumerate(ndi.find_objects(lab), start=1):
+        img = (lab[sl] == k).astype(np.float64)
+        r = np.arange(img.shape[0], dtype=np.float64)
+        c = np.arange(img.shape[1], dtype=np.float64)
+        m00 = img.sum()
+        cr, cc = (img.sum(axis=1) @ r) / m00, (img.sum(axis=0) @ c) / m00
+        dr, dc = r - cr, c - cc
+        mu20 = (dr ** 2) @ img @ np.ones_like(c)
+        mu02 = np.ones_like(r) @ img @ (dc ** 2)
+        mu11 = dr @ img @ dc
+        T = np.array([[mu02, -mu11], [-mu11, mu20]]) / m00
+        ev = np.clip(np.linalg.eigvalsh(T), 0, None)
+        l1, l2 = max(ev), min(ev)
+        out[lab == k] = 0.0 if l1 == 0 else np.sqrt(1 - l2 / l1)
+    return out

@@ -85,3 +85,44 @@ def auto_threshold_well(image, return_stages=False):
     if return_stages:
         return mask, {"blur": blur, "u8": u8, "invert": inv, "otsu": thr}
     return mask
+
+
+# ---- superellipse fit / hull mask: well_mask_generation.py:16-140 (numpy-only in the reference) ------------------
+# PINNED: tests/golden/wellmask.npz holds outputs of the reference's own functions (imported by
+# tests/golden/make_golden.py with np.random.seed set); these restatements are checked against them on the CPU.
+_SE_BOUNDS = np.array([(-np.pi / 20, np.pi / 20), (0.67, 1.33), (0.9, 1.1), (0.9, 1.1), (-0.3, 0.3), (-0.3, 0.3)])
+
+
+def get_superellipse_hull(x, y, n, num_iters=25000):
+    """:16-91.  Draws from numpy's global RNG, like the reference."""
+    from scipy.special import gamma
+    w = np.random.rand(num_iters, 6)
+    pv = (_SE_BOUNDS[:, 1] - _SE_BOUNDS[:, 0]) * w + _SE_BOUNDS[:, 0]
+    t, d, s_a, s_b, c_x, c_y = pv.T[..., np.newaxis]
+    if n == 2:
+        val = ((x - c_x) / (d * s_a)) ** 2 + ((y - c_y) / (d * s_b)) ** 2
+    elif n % 2 == 0:
+        val = ((((x - c_x) * np.cos(t) - ((y - c_y) * np.sin(t))) / (d * s_a)) ** n
+               + (((x - c_x) * np.sin(t) + (y - c_y) * np.cos(t)) / (d * s_b)) ** n)
+    else:
+        val = (np.abs(((x - c_x) * np.cos(t) - ((y - c_y) * np.sin(t))) / (d * s_a)) ** n
+               + np.abs(((x - c_x) * np.sin(t) + (y - c_y) * np.cos(t)) / (d * s_b)) ** n)
+    cand = np.where(np.max(val, axis=1) < 1)[0]
+    area = 4 * d[cand] ** 2 * s_a[cand] * s_b[cand] * gamma(1 + 1 / n) ** 2 / gamma(1 + 2 / n)
+    k = cand[np.argmin(area)]            # ValueError on an empty candidate set, as in the reference
+    return tuple(pv[k])
+
+
+def gen_superellipse_mask(t, d, s_a, s_b, c_x, c_y, n, shape):
+    """:94-118."""
+    X, Y = np.meshgrid(np.linspace(-1, 1, shape[0]), np.linspace(-1, 1, shape[1]))
+    mask = ((np.abs(((X - c_x) * np.cos(t) - (Y - c_y) * np.sin(t)) / (d * s_a))) ** n
+            + (np.abs(((X - c_x) * np.sin(t) + (Y - c_y) * np.cos(t)) / (d * s_b))) ** n < 1)
+    return np.swapaxes(mask, 0, 1)
+
+
+def create_convex_hull_mask(array_shape, hull_vertices):
+    """:121-140 -- scipy's Delaunay, as the reference."""
+    from scipy.spatial import Delaunay
+    coords = np.indices(array_shape).reshape(2, -1).T
+    return (Delaunay(hull_vertices).find_simplex(coords) >= 0).reshape(array_shape)

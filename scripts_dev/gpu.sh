@@ -11,6 +11,8 @@
 #   ncu <regex> [skip] [count]   ncu --set full of matching kernels in a 64-patch chunk -> gpurun_out/ncu_<tag>.ncu-rep
 #   noalloc         tests/test_zz_no_alloc.py alone in a fresh process
 #   ncu4            ncu --set full of the stage 3/4 kernels (one C3 image)
+#   multi N         bench.py under torchrun on N GPUs, as the driver launches it
+#   tests <files>   selected GPU test files only
 #   stages          scripts/bench_stages.py (C2/C3 stage table)
 mkdir -p gpurun_out
 mode=$1; shift
@@ -69,8 +71,16 @@ noalloc)   # the allocation-free entry point: alone in a fresh process, then aga
   timeout 600 python -m pytest tests/test_zz_no_alloc.py -m gpu -x -q 2>&1 | tail -8 | cut -c1-300
   ;;
 ncu4)      # ncu --set full of the stage 3/4 kernels over one C3 image -> gpurun_out/ncu_stage4.ncu-rep
-  timeout 900 ncu --set full --import-source on --clock-control none -k regex:"thin_|ccl_|erode_disk|root_|gauss_|otsu_|median_|footprint_|border_" --launch-count 60 -o gpurun_out/ncu_stage4 -f python scripts/bench_stages.py --config C3 --no-cpu --iters 1 > gpurun_out/ncu_stage4.log 2>&1
+  timeout 900 ncu --set full --import-source on --clock-control none -k regex:"thin_|ccl_|erode_disk|root_|gauss_|otsu_|median_|footprint_|border_|rescale_u8|minmax64" --launch-count 36 -o gpurun_out/ncu_stage4 -f python scripts/bench_stages.py --config C3 --no-cpu --iters 1 > gpurun_out/ncu_stage4.log 2>&1
   echo "ncu stage4 exit $?"; tail -3 gpurun_out/ncu_stage4.log
+  ;;
+multi)     # bench.py on N GPUs exactly as the driver launches it (gpurun --gpus N): multi N
+  N=${1:-2}
+  timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N --steps 10 --warmup 3 > gpurun_out/bench_n$N.log 2>&1; echo "bench N=$N exit $?"
+  tail -1 gpurun_out/bench_n$N.log > gpurun_out/bench_n$N.json; cut -c1-2500 gpurun_out/bench_n$N.json
+  ;;
+tests)     # selected GPU test files only (no bench)
+  timeout 1500 python -m pytest "$@" -m gpu -x -q 2>&1 | tail -25 | cut -c1-400
   ;;
 stages)
   timeout 900 python scripts/bench_stages.py "$@" 2>&1 | tail -40

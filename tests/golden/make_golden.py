@@ -70,8 +70,21 @@ def _install_stubs():
     morph.remove_small_objects = lambda lab, min_size=64: om.remove_small_objects(lab, min_size)
     morph.disk = om.disk
     morph.skeletonize = om.skeletonize
+    # well_mask_generation.py imports these at module level; the functions pinned from it (get_superellipse_hull,
+    # gen_superellipse_mask, create_convex_hull_mask) are numpy / scipy only and never call them
+    filters.gaussian = filters.threshold_otsu = None
+    morph.binary_erosion = None
+    feature = types.ModuleType("skimage.feature")
+    feature.canny = None
+    exposure = types.ModuleType("skimage.exposure")
+    exposure.rescale_intensity = None
+    transform = types.ModuleType("skimage.transform")
+    transform.rescale = transform.resize = None
+    draw = types.ModuleType("skimage.draw")
+    draw.disk = None
     for name, mod in (("skimage", sk), ("skimage.filters", filters), ("skimage.measure", measure),
-                      ("skimage.morphology", morph)):
+                      ("skimage.morphology", morph), ("skimage.feature", feature), ("skimage.exposure", exposure),
+                      ("skimage.transform", transform), ("skimage.draw", draw)):
         sys.modules[name] = mod
 
 
@@ -171,8 +184,36 @@ def gen_dmt():
     np.savez_compressed(os.path.join(OUT, "dmt.npz"), **cases)
 
 
+def gen_wellmask():
+    """The reference's own numpy-only well-mask functions (well_mask_generation.py:16-140), np.random.seed set."""
+    from fl_tissue_model_tools import well_mask_generation as r
+    from scipy.spatial import ConvexHull
+    cases = {}
+    for name, (kind, n, seed, iters) in {"circ2": ("circle", 2, 11, 25000), "sq8": ("square", 8, 12, 25000),
+                                         "circ8": ("circle", 8, 13, 6000), "odd3": ("circle", 3, 14, 4000)}.items():
+        x, y = helpers.wellmask_points(kind, seed)
+        np.random.seed(seed)
+        out = r.get_superellipse_hull(x, y, n, iters)
+        cases[f"hull_{name}_cfg"] = np.array([n, seed, iters], np.int64)
+        cases[f"hull_{name}_x"], cases[f"hull_{name}_y"] = x, y
+        cases[f"hull_{name}_out"] = np.array(out, np.float64)
+        for shp in ((200, 200), (150, 200), (37, 53)):
+            t, d, s_a, s_b, c_x, c_y = out
+            m = r.gen_superellipse_mask(t, d * 0.9, s_a, s_b, c_x, c_y, n, shp)
+            cases[f"mask_{name}_{shp[0]}x{shp[1]}"] = np.packbits(m)
+    rng = np.random.default_rng(5)
+    for name, (H, W, npts) in {"a": (120, 160, 40), "b": (200, 200, 300), "c": (33, 47, 6), "tri": (50, 60, 3)}.items():
+        pts = np.stack([rng.integers(0, H, npts), rng.integers(0, W, npts)], axis=1)
+        hv = pts[ConvexHull(pts).vertices]
+        cases[f"chull_{name}_shape"] = np.array([H, W], np.int64)
+        cases[f"chull_{name}_verts"] = hv.astype(np.int64)
+        cases[f"chull_{name}_mask"] = np.packbits(r.create_convex_hull_mask((H, W), hv))
+    np.savez_compressed(os.path.join(OUT, "wellmask.npz"), **cases)
+
+
 if __name__ == "__main__":
     _install_stubs()
+    gen_wellmask()
     gen_dmt()
     gen_stp()
     gen_zproj()

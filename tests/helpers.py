@@ -94,3 +94,23 @@ def synth_well(h, w, seed, dtype=np.uint16, invert=False):
     if np.dtype(dtype).kind == "f":
         return img.astype(dtype)
     return (img * np.iinfo(dtype).max).astype(dtype)
+
+
+def wellmask_points(kind, seed, npts=28):
+    """Hull-vertex-like points in [-1, 1]^2 as generate_well_mask hands them over (:208-209): integer pixel
+    coordinates of a <= 200-px thumbnail, scaled."""
+    rng = np.random.default_rng(seed)
+    size = 200
+    ang = np.sort(rng.uniform(0, 2 * np.pi, npts))
+    if kind == "circle":
+        rad = 0.78 + rng.uniform(-0.02, 0.0, npts)
+        px, py = rad * np.cos(ang), rad * np.sin(ang)
+    else:                                         # rounded square: |x|^8 + |y|^8 = r^8
+        rad = 0.8
+        c, s_ = np.cos(ang), np.sin(ang)
+        k = rad / (np.abs(c) ** 8 + np.abs(s_) ** 8) ** 0.125
+        px, py = k * c, k * s_
+    px, py = px + 0.04, py - 0.03
+    rows = np.round((px + 1) / 2 * size).astype(np.int64)
+    cols = np.round((py + 1) / 2 * size).astype(np.int64)
+    return rows / size * 2 - 1, cols / size * 2 - 1

@@ -102,3 +102,39 @@ def test_unet_oracle_shapes_and_flops():
     y = unet.forward(w, np.random.default_rng(0).random((2, 64, 64), dtype=np.float32))
     assert y.shape == (2, 64, 64, 1) and y.dtype == np.float32
     assert sum(v.size for v in unet.make_weights().values()) == 8197313
+
+
+def test_wellmask_superellipse_and_hull_match_reference(golden):
+    """well_mask_generation.py:16-140 (numpy-only in the reference): the restatements in oracle/wellmask.py against
+    outputs of the reference's own functions, same np.random seed."""
+    from oracle import wellmask as ow
+    g = golden("wellmask")
+    for name in ("circ2", "sq8", "circ8", "odd3"):
+        n, seed, iters = (int(v) for v in g[f"hull_{name}_cfg"])
+        np.random.seed(seed)
+        out = ow.get_superellipse_hull(g[f"hull_{name}_x"], g[f"hull_{name}_y"], n, iters)
+        assert np.array_equal(np.array(out), g[f"hull_{name}_out"]), name
+        t, d, s_a, s_b, c_x, c_y = out
+        for shp in ((200, 200), (150, 200), (37, 53)):
+            m = ow.gen_superellipse_mask(t, d * 0.9, s_a, s_b, c_x, c_y, n, shp)
+            assert m.shape == shp
+            assert np.array_equal(np.packbits(m), g[f"mask_{name}_{shp[0]}x{shp[1]}"]), (name, shp)
+    for name in ("a", "b", "c", "tri"):
+        H, W = (int(v) for v in g[f"chull_{name}_shape"])
+        m = ow.create_convex_hull_mask((H, W), g[f"chull_{name}_verts"])
+        assert np.array_equal(np.packbits(m), g[f"chull_{name}_mask"]), name
+
+
+def test_eccentricity_oracle_known_shapes():
+    """The restated regionprops eccentricity on shapes with a closed form: a disk / square -> 0, a 1 x L line -> 1,
+    an a x b rectangle -> sqrt(1 - (b^2 - 1) / (a^2 - 1)) (variance of k equally spaced points = (k^2 - 1) / 12)."""
+    m = np.zeros((80, 120), bool)
+    m[5:25, 5:25] = True                      # 20 x 20 square
+    m[40, 10:60] = True                       # 1 x 50 line
+    m[50:58, 70:110] = True                   # 8 x 40 rectangle
+    m[70, 5] = True                           # single pixel
+    e = om.regionprops_image_eccentricity(m)
+    assert abs(e[10, 10]) < 1e-6
+    assert e[40, 30] == 1.0
+    assert abs(e[52, 80] - np.sqrt(1 - (8 ** 2 - 1) / (40 ** 2 - 1))) < 1e-12
+    assert e[70, 5] == 0.0 and e[0, 0] == 0.0

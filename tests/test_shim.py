@@ -110,6 +110,44 @@ def test_shim_uninstall_restores_the_reference(shimmed):
 
 
 @needs_ref
+def test_shim_patches_generate_well_mask_in_place():
+    """With scikit-image importable (here: import-only test doubles for the seven names well_mask_generation.py:6-13
+    binds) the reference's module loads, stays the reference's, and its generate_well_mask (:143-233) resolves
+    auto_threshold_well / get_superellipse_hull / gen_superellipse_mask / create_convex_hull_mask to the GPU mirrors."""
+    from tmat_b200 import shim, well_mask_generation as tw
+    before = {k for k in sys.modules if k.startswith("fl_tissue_model_tools")}
+    doubles = {"skimage": {}, "skimage.filters": {"gaussian": None, "threshold_otsu": None},
+               "skimage.morphology": {"disk": None, "binary_erosion": None}, "skimage.feature": {"canny": None},
+               "skimage.exposure": {"rescale_intensity": None}, "skimage.transform": {"rescale": None, "resize": None},
+               "skimage.draw": {"disk": None}}
+    saved = {name: sys.modules.get(name) for name in doubles}
+    for name, attrs in doubles.items():
+        m = types.ModuleType(name)
+        m.__dict__.update(attrs)
+        sys.modules[name] = m
+    try:
+        report = shim.install(reference_root=REF, modules=["well_mask_generation"])
+        assert report == {"well_mask_generation": "patched"}
+        ref = importlib.import_module("fl_tissue_model_tools.well_mask_generation")
+        assert ref.__file__.startswith(REF)
+        assert ref.generate_well_mask.__module__ == "fl_tissue_model_tools.well_mask_generation"
+        glob = ref.generate_well_mask.__globals__
+        for name in ("auto_threshold_well", "get_superellipse_hull", "gen_superellipse_mask", "create_convex_hull_mask"):
+            assert glob[name] is getattr(tw, name), name
+        shim.uninstall()
+        assert ref.auto_threshold_well.__module__ == "fl_tissue_model_tools.well_mask_generation"
+    finally:
+        shim.uninstall()
+        for name, old in saved.items():
+            if old is None:
+                sys.modules.pop(name, None)
+            else:
+                sys.modules[name] = old
+        for k in [k for k in sys.modules if k.startswith("fl_tissue_model_tools") and k not in before]:
+            sys.modules.pop(k, None)
+
+
+@needs_ref
 @pytest.mark.gpu
 @pytest.mark.parametrize("method", ["fs", "max", "med"])
 def test_compute_zproj_main_runs_unchanged_on_the_gpu(shimmed, tmp_path, method):

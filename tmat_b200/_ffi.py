@@ -96,6 +96,10 @@ SIGNATURES = {
     "tmat_erode_disk_host": [_vp, _vp, _i, _i, _i, _i, _vp],
     "tmat_label_host": [_vp, _vp, _i, _i, _i, _vp, _pi],
     "tmat_skeletonize_host": [_vp, _vp, _i, _i, _vp, _pi],
+    "tmat_superellipse_hull_host": [_vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _i, C.c_double, C.c_double, _pi],
+    "tmat_superellipse_mask_host": [_vp, _vp, _i, _vp, _i, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double,
+                                    C.c_double, _i, _vp],
+    "tmat_convex_hull_mask_host": [_vp, _i, _i, _vp, _i, _vp],
     "tmat_distance_transform_edt_dev": [_vp, _vp, _i, _i, _i, _vp, _vp],
     "tmat_distance_transform_edt_host": [_vp, _vp, _i, _i, _i, _vp],
     "tmat_distance_transform_edt_static_dev": [_vp, _i, _i, _i, _vp, _vp],

@@ -6,6 +6,7 @@
 // Floating-point steps that feed an integer decision are evaluated in the reference's precision
 // with the reference's operation order and no FMA contraction, so the uint8 image is bit-identical.
 #include "common.cuh"
+#include <stdlib.h>
 #include <math.h>
 #include <algorithm>
 #include <type_traits>
@@ -107,6 +108,79 @@ __global__ void __launch_bounds__(256) gauss_axis1(const T* __restrict__ in, int
   }
 }
 
+// ---- the same two passes for a compile-time radius (sigma = 1 -> R = 4, what auto_threshold_well uses) -----------
+// ncu (round 2, 2048^2 uint16): the per-pixel kernels above spend their time on 2R+1 integer->float64 conversions per
+// output (axis 0) and on 16 384 one-row CTAs of load -> barrier -> compute with two same-address atomics each (axis 1:
+// 27 us, 40 us with the min/max).  Here a thread slides down GROWS rows (each input converted once: (GROWS + 2R) / GROWS
+// conversions per output) resp. along 4 columns x 4 rows with every load issued before the first use, and a CTA
+// issues one pair of atomics.  Per-output arithmetic and its order are unchanged (bit-identical results).
+constexpr int GROWS = 8;
+template <typename TIn, typename TOut, int R>
+__global__ void __launch_bounds__(256) gauss_axis0_fixed(const TIn* __restrict__ in, int H, int W, GaussW g, double int_scale,
+                                                         TOut* __restrict__ out) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  const int y0 = blockIdx.y * GROWS;
+  if (x >= W) return;
+  double v[GROWS + 2 * R];
+#pragma unroll
+  for (int i = 0; i < GROWS + 2 * R; ++i) {
+    const int yy = min(max(y0 - R + i, 0), H - 1);
+    v[i] = load_as_f64<TIn>(in, (int64_t)yy * W + x, int_scale);
+  }
+#pragma unroll
+  for (int k = 0; k < GROWS; ++k) {
+    if (y0 + k >= H) break;
+    double tmp = __dmul_rn(v[k + R], g.w[0]);
+#pragma unroll
+    for (int j = R; j >= 1; --j) tmp = __dadd_rn(tmp, __dmul_rn(__dadd_rn(v[k + R - j], v[k + R + j]), g.w[j]));
+    out[(int64_t)(y0 + k) * W + x] = (TOut)tmp;
+  }
+}
+constexpr int GX = 4, GY = 4;                  // outputs per thread of the horizontal pass: 4 columns x 4 rows
+template <typename T, int R>
+__global__ void __launch_bounds__(128) gauss_axis1_fixed(const T* __restrict__ in, int H, int W, GaussW g, T* __restrict__ out,
+                                                         unsigned long long* __restrict__ mm) {
+  const int x0 = (blockIdx.x * 128 + threadIdx.x) * GX;
+  const int y0 = blockIdx.y * GY;
+  unsigned long long lo = ~0ull, hi = 0ull;
+  if (x0 < W) {
+    double v[GY][GX + 2 * R];
+#pragma unroll
+    for (int r = 0; r < GY; ++r) {
+      const T* row = in + (int64_t)min(y0 + r, H - 1) * W;
+#pragma unroll
+      for (int i = 0; i < GX + 2 * R; ++i) v[r][i] = (double)row[min(max(x0 - R + i, 0), W - 1)];
+    }
+#pragma unroll
+    for (int r = 0; r < GY; ++r) {
+      if (y0 + r >= H) break;
+#pragma unroll
+      for (int k = 0; k < GX; ++k) {
+        if (x0 + k >= W) break;
+        double tmp = __dmul_rn(v[r][k + R], g.w[0]);
+#pragma unroll
+        for (int j = R; j >= 1; --j) tmp = __dadd_rn(tmp, __dmul_rn(__dadd_rn(v[r][k + R - j], v[r][k + R + j]), g.w[j]));
+        const T o = (T)tmp;
+        out[(int64_t)(y0 + r) * W + x0 + k] = o;
+        const unsigned long long key = f64_key((double)o);
+        lo = min(lo, key); hi = max(hi, key);
+      }
+    }
+  }
+  if (mm == nullptr) return;
+  __shared__ unsigned long long s_lo[4], s_hi[4];
+  for (int o = 16; o > 0; o >>= 1) {
+    lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+    hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+  }
+  if ((threadIdx.x & 31) == 0) { s_lo[threadIdx.x >> 5] = lo; s_hi[threadIdx.x >> 5] = hi; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < 4; ++w) { lo = min(lo, s_lo[w]); hi = max(hi, s_hi[w]); }
+    if (lo != ~0ull) { atomicMin(mm, lo); atomicMax(mm + 1, hi); }
+  }
+}
+
 __global__ void minmax64_init(unsigned long long* k) { k[0] = ~0ull; k[1] = 0ull; }
 // rescale_intensity(x, out_range=(0,255)).astype(uint8)  +  the 4 corner histograms + global histogram
 //   y = (x - lo) / (hi - lo);  y = y * 255 + 0;  uint8(trunc(y))      in T's precision (float64 / float32)
@@ -147,18 +221,36 @@ __global__ void __launch_bounds__(256) rescale_u8_hist(const T* __restrict__ x, 
     if (sh[i]) atomicAdd(&hist[i], sh[i]);
 }
 
-// np.median of a uint8 block from its histogram
-__device__ double dev_hist_median(const unsigned int* h) {
-  unsigned long long n = 0;
-  for (int i = 0; i < 256; ++i) n += h[i];
-  if (n == 0) return __longlong_as_double(0x7ff8000000000000ll);
-  unsigned long long k0 = (n - 1) / 2, k1 = n / 2, acc = 0;
-  int v0 = -1, v1 = -1;
-  for (int i = 0; i < 256; ++i) {
-    acc += h[i];
-    if (v0 < 0 && acc > k0) v0 = i;
-    if (v1 < 0 && acc > k1) { v1 = i; break; }
+// np.median of a uint8 block from its 256-bin histogram (shared memory), computed by one warp: every lane owns 8
+// consecutive bins, a shuffle scan gives the counts below each lane, and the lane in which the cumulative count
+// first exceeds k walks its 8 bins.  Returns (v0 + v1) / 2 for the two middle order statistics (all lanes).
+__device__ __forceinline__ int warp_hist_select(const unsigned int* h, unsigned long long below, unsigned long long mine,
+                                                unsigned long long k, int lane) {
+  // lane owning the k-th element (0-based): below <= k < below + mine
+  const bool own = mine > 0 && below <= k && k < below + mine;
+  int v = -1;
+  if (own) {
+    unsigned long long acc = below;
+    for (int i = 0; i < 8; ++i) {
+      acc += h[lane * 8 + i];
+      if (acc > k) { v = lane * 8 + i; break; }
+    }
   }
+  const unsigned int who = __ballot_sync(0xffffffffu, own);
+  return __shfl_sync(0xffffffffu, v, who ? __ffs(who) - 1 : 0);
+}
+__device__ double warp_hist_median(const unsigned int* h, int lane) {
+  unsigned long long mine = 0;
+  for (int i = 0; i < 8; ++i) mine += h[lane * 8 + i];
+  unsigned long long incl = mine;
+  for (int o = 1; o < 32; o <<= 1) {
+    const unsigned long long up = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += up;
+  }
+  const unsigned long long n = __shfl_sync(0xffffffffu, incl, 31), below = incl - mine;
+  if (n == 0) return __longlong_as_double(0x7ff8000000000000ll);
+  const int v0 = warp_hist_select(h, below, mine, (n - 1) / 2, lane);
+  const int v1 = warp_hist_select(h, below, mine, n / 2, lane);
   return __ddiv_rn(__dadd_rn((double)v0, (double)v1), 2.0);
 }
 // Corner medians, invert decision and skimage.filters.threshold_otsu (well_mask_generation.py:248-272) on the device:
@@ -174,15 +266,17 @@ __global__ void __launch_bounds__(256) otsu_decide_kernel(const unsigned int* __
   __shared__ int s_i[256];
   __shared__ double s_med[4];
   __shared__ int s_misc[4];
+  __shared__ unsigned int s_h[5 * 256];
   const int t = threadIdx.x;
-  if (t < 4) s_med[t] = dev_hist_median(hist + t * 256);
-  const unsigned int* g = hist + 4 * 256;
-  if (t == 4) {
-    int vmin = 0, vmax = 255;
-    while (vmin < 255 && g[vmin] == 0) ++vmin;
-    while (vmax > 0 && g[vmax] == 0) --vmax;
-    s_misc[0] = vmin; s_misc[1] = vmax;
+  for (int i = t; i < 5 * 256; i += 256) s_h[i] = hist[i];
+  if (t == 0) { s_misc[0] = 255; s_misc[1] = 0; }
+  __syncthreads();
+  const unsigned int* g = s_h + 4 * 256;
+  if (t < 128) {                                   // warps 0..3: one corner block each
+    const double m = warp_hist_median(s_h + (t >> 5) * 256, t & 31);
+    if ((t & 31) == 0) s_med[t >> 5] = m;
   }
+  if (g[t] != 0) { atomicMin(&s_misc[0], t); atomicMax(&s_misc[1], t); }      // occupied range of the image (n >= 400 pixels)
   __syncthreads();
   const int vmin = s_misc[0], vmax = s_misc[1];
   const double mmin = fmin(fmin(s_med[0], s_med[1]), fmin(s_med[2], s_med[3]));
@@ -260,6 +354,16 @@ static int gaussian_impl(tmat_ctx* ctx, const void* img, int dtype, int H, int W
     double* tmp;
     TMAT_TRY(arena_get(ctx, n, &tmp));
     // skimage img_as_float: np.multiply(image, 1. / imax, dtype=float64)
+    static const bool generic = [] { const char* v = getenv("TMAT_GAUSS_GENERIC"); return v && atoi(v) == 1; }();
+    if (g.R == 4 && !generic) {
+      const dim3 gf0(cdiv(W, 256), cdiv(H, GROWS)), gf1(cdiv(W, 128 * GX), cdiv(H, GY));
+      if (dtype == TMAT_U8) gauss_axis0_fixed<uint8_t, double, 4><<<gf0, 256, 0, st>>>((const uint8_t*)img, H, W, g, 1.0 / 255.0, tmp);
+      else gauss_axis0_fixed<uint16_t, double, 4><<<gf0, 256, 0, st>>>((const uint16_t*)img, H, W, g, 1.0 / 65535.0, tmp);
+      KERNEL_CHECK(ctx);
+      gauss_axis1_fixed<double, 4><<<gf1, 128, 0, st>>>(tmp, H, W, g, (double*)out, mm);
+      KERNEL_CHECK(ctx);
+      return TMAT_OK;
+    }
     if (dtype == TMAT_U8) gauss_axis0<uint8_t, double><<<grid0, 256, 0, st>>>((const uint8_t*)img, H, W, g, 1.0 / 255.0, tmp);
     else gauss_axis0<uint16_t, double><<<grid0, 256, 0, st>>>((const uint16_t*)img, H, W, g, 1.0 / 65535.0, tmp);
     KERNEL_CHECK(ctx);

@@ -25,7 +25,8 @@ PATCHES = {
     "zstacks": ("tmat_b200.zstacks", ("proj_focus_stacking", "proj_avg", "proj_med", "proj_max", "proj_min")),
     "smooth_tiled_predictions": ("tmat_b200.smooth_tiled_predictions", ("predict_img_with_smooth_windowing",)),
     "transforms": ("tmat_b200.transforms", ("filter_branch_seg_mask", "remove_small_islands", "regionprops_image")),
-    "well_mask_generation": ("tmat_b200.well_mask_generation", ("auto_threshold_well",)),
+    "well_mask_generation": ("tmat_b200.well_mask_generation", ("auto_threshold_well", "get_superellipse_hull",
+                                                                "gen_superellipse_mask", "create_convex_hull_mask")),
     "preprocessing": ("tmat_b200.preprocessing", ("apply_mask", "bin_thresh", "exec_threshold", "blur", "dt_blur", "sdt_blur",
                                                    "gen_circ_mask")),
     "dmtgraph": ("tmat_b200.dmtgraph", ("compute_dmt_graph",)),

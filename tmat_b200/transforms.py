@@ -97,13 +97,13 @@ def remove_small_islands(mask, min_area0=100, min_area1=100, connectivity0=1, co
     return out.astype(m.dtype)
 
 
-_REGION_PROPS = {"area": 0, "equivalent_diameter_area": 1, "equivalent_diameter": 1}
+_REGION_PROPS = {"area": 0, "equivalent_diameter_area": 1, "equivalent_diameter": 1, "eccentricity": 2}
 
 
 def regionprops_image(mask, prop):
-    """transforms.py:291-303.  The area-like properties (``area``, ``equivalent_diameter_area`` -- the one
-    compute_branches.py:277 asks for) are computed on the GPU; moment-based ones (``eccentricity``, :276) are
-    SURVEY 8(f) "next" and raise."""
+    """transforms.py:291-303 for the properties the reference's callers ask for (compute_branches.py:276-277):
+    ``area``, ``equivalent_diameter_area`` and ``eccentricity`` (exact integer moments; a tolerance against
+    scikit-image's float64 dot products).  Anything else raises NotImplementedError."""
     if prop not in _REGION_PROPS:
         raise NotImplementedError(f"regionprops_image(prop={prop!r}): built properties are {sorted(_REGION_PROPS)}")
     m = _mask_u8(mask)
