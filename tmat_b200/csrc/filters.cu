@@ -181,7 +181,11 @@ __global__ void __launch_bounds__(128) gauss_axis1_fixed(const T* __restrict__ i
   }
 }
 
-__global__ void minmax64_init(unsigned long long* k) { k[0] = ~0ull; k[1] = 0ull; }
+// min / max keys and the 5 x 256 histogram counters of auto_threshold_well, initialised in one launch
+__global__ void __launch_bounds__(256) minmax64_hist_init(unsigned long long* k, unsigned int* hist) {
+  if (threadIdx.x == 0) { k[0] = ~0ull; k[1] = 0ull; }
+  for (int i = threadIdx.x; i < 5 * 256; i += 256) hist[i] = 0;
+}
 // rescale_intensity(x, out_range=(0,255)).astype(uint8)  +  the 4 corner histograms + global histogram
 //   y = (x - lo) / (hi - lo);  y = y * 255 + 0;  uint8(trunc(y))      in T's precision (float64 / float32)
 template <typename T>
@@ -194,27 +198,49 @@ __global__ void __launch_bounds__(256) rescale_u8_hist(const T* __restrict__ x, 
   __syncthreads();
   const T lo = (T)f64_unkey(keys[0]), hi = (T)f64_unkey(keys[1]);
   const bool flat = (lo == hi);
-  int64_t n = (int64_t)H * W;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    T v = x[i];
-    T y;
-    if (sizeof(T) == 8) {
-      double d = (double)v;
-      if (!flat) d = __ddiv_rn(__dsub_rn(d, (double)lo), __dsub_rn((double)hi, (double)lo));
-      y = (T)__dadd_rn(__dmul_rn(d, 255.0), 0.0);
-    } else {
-      float f = (float)v;
-      if (!flat) f = __fdiv_rn(__fsub_rn(f, (float)lo), __fsub_rn((float)hi, (float)lo));
-      y = (T)__fadd_rn(__fmul_rn(f, 255.0f), 0.0f);
+  const int lane = threadIdx.x & 31;
+  // a block walks whole rows (no 64-bit index division per pixel); the global histogram takes one shared-memory atomic
+  // per distinct value per warp (neighbouring pixels of a blurred image mostly share a handful of values)
+  for (int r = blockIdx.x; r < H; r += gridDim.x) {
+    const T* xr = x + (int64_t)r * W;
+    uint8_t* ur = u8 + (int64_t)r * W;
+    const bool top = r < xs, bot = r >= xe;
+    for (int cb = 0; cb < W; cb += 4 * 256) {
+      T raw[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {             // four independent loads in flight before the first division
+        const int c = cb + u * 256 + threadIdx.x;
+        raw[u] = c < W ? xr[c] : (T)0;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int c0 = cb + u * 256;
+        if (c0 >= W) break;                     // block-uniform
+        const int c = c0 + threadIdx.x;
+        int q = -1;
+        if (c < W) {
+          T y;
+          if (sizeof(T) == 8) {
+            double d = (double)raw[u];
+            if (!flat) d = __ddiv_rn(__dsub_rn(d, (double)lo), __dsub_rn((double)hi, (double)lo));
+            y = (T)__dadd_rn(__dmul_rn(d, 255.0), 0.0);
+          } else {
+            float f = (float)raw[u];
+            if (!flat) f = __fdiv_rn(__fsub_rn(f, (float)lo), __fsub_rn((float)hi, (float)lo));
+            y = (T)__fadd_rn(__fmul_rn(f, 255.0f), 0.0f);
+          }
+          const uint8_t qq = (uint8_t)(long long)y;
+          ur[c] = qq;
+          q = qq;
+          if (top && c < ys) atomicAdd(&sh[0 * 256 + q], 1u);
+          if (top && c >= ye) atomicAdd(&sh[1 * 256 + q], 1u);
+          if (bot && c < ys) atomicAdd(&sh[2 * 256 + q], 1u);
+          if (bot && c >= ye) atomicAdd(&sh[3 * 256 + q], 1u);
+        }
+        const unsigned int peers = __match_any_sync(0xffffffffu, q);
+        if (q >= 0 && lane == __ffs(peers) - 1) atomicAdd(&sh[4 * 256 + q], (unsigned int)__popc(peers));
+      }
     }
-    uint8_t q = (uint8_t)(long long)y;
-    u8[i] = q;
-    int r = (int)(i / W), c = (int)(i - (int64_t)r * W);
-    atomicAdd(&sh[4 * 256 + q], 1u);
-    if (r < xs && c < ys) atomicAdd(&sh[0 * 256 + q], 1u);
-    if (r < xs && c >= ye) atomicAdd(&sh[1 * 256 + q], 1u);
-    if (r >= xe && c < ys) atomicAdd(&sh[2 * 256 + q], 1u);
-    if (r >= xe && c >= ye) atomicAdd(&sh[3 * 256 + q], 1u);
   }
   __syncthreads();
   for (int i = threadIdx.x; i < 5 * 256; i += blockDim.x)
@@ -451,11 +477,11 @@ static int auto_threshold_impl(tmat_ctx* ctx, const void* img, int dtype, int H,
   TMAT_TRY(arena_get(ctx, 2, &keys));
   TMAT_TRY(arena_get(ctx, 5 * 256, &hist));
   TMAT_TRY(arena_get(ctx, n, &u8));
-  minmax64_init<<<1, 1, 0, st>>>(keys);
+  minmax64_hist_init<<<1, 256, 0, st>>>(keys, hist);
   KERNEL_CHECK(ctx);
   TMAT_TRY(gaussian_impl(ctx, img, dtype, H, W, 1.0, blur, st, keys));     // min / max of the result reduced in its last pass
-  int blocks = (int)std::min<int64_t>(cdiv64((int64_t)n, 256), (int64_t)ctx->sm_count * 8);
-  CUDA_TRY(cudaMemsetAsync(hist, 0, 5 * 256 * sizeof(unsigned int), st));
+  const int rows_per_block = cdiv(H, ctx->sm_count * 8);        // rescale_u8_hist walks whole rows: the same number per block
+  int blocks = cdiv(H, rows_per_block);
   int xs = (int)(H * 0.05), xe = (int)(H * 0.95), ys = (int)(W * 0.05), ye = (int)(W * 0.95);
   if (f32) rescale_u8_hist<float><<<blocks, 256, 0, st>>>((const float*)blur, H, W, keys, xs, xe, ys, ye, u8, hist);
   else rescale_u8_hist<double><<<blocks, 256, 0, st>>>((const double*)blur, H, W, keys, xs, xe, ys, ye, u8, hist);

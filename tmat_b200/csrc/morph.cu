@@ -33,6 +33,65 @@ __global__ void __launch_bounds__(256) median_disk2_kernel(const uint8_t* __rest
   out[(int64_t)y * W + x] = cnt >= 7;
 }
 
+// Bit-sliced version (the default): a warp owns 32 columns and a segment of rows.  A row (32 + 4 pixels, indices clamped
+// = mode 'nearest') becomes a 64-bit mask by two ballots; its horizontal counts over half-widths 0 / 1 / 2 are held as
+// bit planes (S1: the pixel, S3 = 2 planes, S5 = 3 planes; full adders are one XOR3 and one MAJ3 logic operation on 32
+// pixels at once), and output row y adds S5[y] + S3[y-1] + S3[y+1] + S1[y-2] + S1[y+2] with six more full adders:
+// count >= 7 <=> bit3 | (bit2 & bit1 & bit0).  ~30 logic operations per 32 pixels instead of 13 clamped loads and
+// compares per pixel (26 us -> per 2048^2, ALU pipe 71 %, round-2 ncu).
+constexpr int MED_SEG = 32;
+__device__ __forceinline__ unsigned int xor3(unsigned int a, unsigned int b, unsigned int c) { return a ^ b ^ c; }
+__device__ __forceinline__ unsigned int maj3(unsigned int a, unsigned int b, unsigned int c) { return (a & b) | (c & (a | b)); }
+__global__ void __launch_bounds__(128) median_disk2_bits(const uint8_t* __restrict__ in, int H, int W, uint8_t* __restrict__ out) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int x0 = blockIdx.x * 32;
+  const int y0 = (blockIdx.y * 4 + warp) * MED_SEG;
+  if (y0 >= H) return;
+  const int y1 = min(y0 + MED_SEG, H);
+  const int xa = min(max(x0 - 2 + lane, 0), W - 1), xb = min(x0 + 30 + lane, W - 1);     // clamped column indices
+  // planes of the last five input rows, slot = (row - (y0 - 2)) mod 5, kept static by unrolling five rows
+  unsigned int s1[5], a0[5], a1[5], t0[5], u1[5], u2[5];
+  for (int base = y0 - 2; base < y1 + 2; base += 5) {
+    uint8_t va[5], vb[5];
+#pragma unroll
+    for (int s = 0; s < 5; ++s) {
+      const int yi = min(max(base + s, 0), H - 1);
+      va[s] = in[(int64_t)yi * W + xa];
+      vb[s] = in[(int64_t)yi * W + xb];
+    }
+#pragma unroll
+    for (int s = 0; s < 5; ++s) {
+      const int yi = base + s;                               // rows past the segment only fill slots that are never read
+      const unsigned int lo = __ballot_sync(0xffffffffu, va[s] != 0);
+      const unsigned int hi = __ballot_sync(0xffffffffu, vb[s] != 0);     // only bits 0..3 are used
+      // w[d]: bit i = pixel x0 + i + d
+      const unsigned int wm2 = lo, wm1 = __funnelshift_r(lo, hi, 1), w0 = __funnelshift_r(lo, hi, 2),
+                         wp1 = __funnelshift_r(lo, hi, 3), wp2 = __funnelshift_r(lo, hi, 4);
+      s1[s] = w0;
+      a0[s] = xor3(wm1, w0, wp1);                            // S3 = a1 a0
+      a1[s] = maj3(wm1, w0, wp1);
+      t0[s] = xor3(a0[s], wm2, wp2);                         // S5 = u2 u1 t0
+      const unsigned int c1 = maj3(a0[s], wm2, wp2);
+      u1[s] = a1[s] ^ c1;
+      u2[s] = a1[s] & c1;
+      // output row yo = yi - 2 has now seen rows yo - 2 .. yo + 2: slots (s - 4 .. s) mod 5
+      const int yo = yi - 2;
+      if (yo >= y0 && yo < y1) {
+        constexpr int M = 5;
+        const int sm2 = (s + 1) % M, sm1 = (s + 2) % M, sc = (s + 3) % M, sp1 = (s + 4) % M, sp2 = s;   // rows yo-2 .. yo+2
+        const unsigned int x0b = xor3(t0[sc], a0[sm1], a0[sp1]), cx = maj3(t0[sc], a0[sm1], a0[sp1]);
+        const unsigned int r0 = xor3(x0b, s1[sm2], s1[sp2]), cy = maj3(x0b, s1[sm2], s1[sp2]);
+        const unsigned int x1b = xor3(u1[sc], a1[sm1], a1[sp1]), dx = maj3(u1[sc], a1[sm1], a1[sp1]);
+        const unsigned int r1 = xor3(x1b, cx, cy), dy = maj3(x1b, cx, cy);
+        const unsigned int r2 = xor3(u2[sc], dx, dy), r3 = maj3(u2[sc], dx, dy);
+        const unsigned int res = r3 | (r2 & r1 & r0);
+        const int x = x0 + lane;
+        if (x < W) out[(int64_t)yo * W + x] = (res >> lane) & 1u;
+      }
+    }
+  }
+}
+
 // ---- erosion with disk(r): all footprint pixels set; outside the image counts as border_value --------
 // Bit-parallel: a warp owns a strip of 32 columns and a segment of rows.  Each input row (32 + 2r pixels) becomes one
 // 64-bit mask by two ballots; E_h = AND of the row shifted by -h..h (two operations per h) is the row eroded by a
@@ -56,53 +115,50 @@ __global__ void __launch_bounds__(128) erode_disk_bits(const uint8_t* __restrict
   const int y0 = (blockIdx.y * 4 + warp) * ER_SEGT;
   if (y0 >= H) return;
   const int y1 = min(y0 + ER_SEGT, H);
-  const int invert = thr_params ? thr_params[0] : 0, thr = thr_params ? thr_params[1] : 1;
-  const unsigned long long edge = border_value ? ~0ull : 0ull;
+  // one predicate for both uses: a plain mask is 'v >= 1', the fused Otsu threshold '(invert ? 255 - v : v) >= thr'
+  const int thr = thr_params ? thr_params[1] : 1;
+  const int vxor = (thr_params && thr_params[0]) ? 255 : 0;            // 255 - v == v ^ 255 for a byte
+  const bool bord = border_value != 0;
   unsigned int acc[2 * R + 1];
 #pragma unroll
   for (int k = 0; k <= 2 * R; ++k) acc[k] = 0xffffffffu;
-  // input rows y0 - R .. y1 - 1 + R; slot of output row yo: (yo - y0 + R... ) kept static by unrolling 2R+1 rows
+  // input rows y0 - R .. y1 - 1 + R; slot of output row yo: (yo - y0 + R... ) kept static by unrolling 2R+1 rows.
+  // Straight-line row body: loads go to clamped addresses and are overridden by selects, rows past the segment's end
+  // are processed like any other (they only reach accumulator slots that are never stored) -- the first version spent
+  // ~155 instructions per row, most of them compares, branches and reconvergence barriers around the two ballots.
   const int xa = x0 - R + lane, xb = xa + 32;
   const bool xa_in = xa >= 0 && xa < W, xb_in = lane < 2 * R && xb < W;     // xb >= 0 always (x0 >= 0, lane >= 0)
+  const int xa_c = min(max(xa, 0), W - 1), xb_c = min(xb, W - 1);
+  const bool hi_lane = lane < 2 * R;
+  const int xo = x0 + lane;
   for (int base = y0 - R; base < y1 + R; base += 2 * R + 1) {
-    // all loads of the batch first: 2 (2R + 1) independent loads in flight per lane instead of one dependent
-    // global-memory latency per row (ncu, round 2: 62 us per 2048^2 image at 0.84 us per row)
+    // all loads of the batch first: 2 (2R + 1) independent loads in flight per lane
     int va[2 * R + 1], vb[2 * R + 1];
 #pragma unroll
     for (int s = 0; s <= 2 * R; ++s) {
-      const int yi = base + s;
-      const bool row_in = yi >= 0 && yi < H && yi < y1 + R;
-      const uint8_t* p = in + (int64_t)(row_in ? yi : 0) * W;
-      va[s] = (row_in && xa_in) ? (int)p[xa] : -1;
-      vb[s] = (row_in && xb_in) ? (int)p[xb] : -1;
+      const int yc = min(max(base + s, 0), H - 1);
+      const uint8_t* p = in + (int64_t)yc * W;
+      va[s] = p[xa_c];
+      vb[s] = p[xb_c];
     }
 #pragma unroll
     for (int s = 0; s <= 2 * R; ++s) {
       const int yi = base + s;
-      if (yi < y1 + R) {
-        unsigned long long row;
-        if (yi < 0 || yi >= H) {
-          row = edge;
-        } else {
-          auto bit = [&](int v) -> bool {
-            if (v < 0) return border_value != 0;             // outside the image
-            if (thr_params) { if (invert) v = 255 - v; return v >= thr; }
-            return v != 0;
-          };
-          const unsigned int lo = __ballot_sync(0xffffffffu, bit(va[s]));
-          const unsigned int hi = __ballot_sync(0xffffffffu, lane < 2 * R ? bit(vb[s]) : false);
-          row = (unsigned long long)lo | ((unsigned long long)hi << 32);
-        }
-        // E[h]: bit j set iff pixels j-h .. j+h of the row are all set (bits shifted in from outside the 32+2R window
-        // are never looked at: only bits R .. R+31 are used and h <= R)
-        unsigned long long e = row;
+      {
+        const bool row_in = yi >= 0 && yi < H;
+        const bool ba = (row_in && xa_in) ? ((va[s] ^ vxor) >= thr) : bord;
+        const bool bb = hi_lane && ((row_in && xb_in) ? ((vb[s] ^ vxor) >= thr) : bord);
+        const unsigned int rlo = __ballot_sync(0xffffffffu, ba);
+        const unsigned int rhi = __ballot_sync(0xffffffffu, bb);
+        // E[h]: bit j set iff pixels j-h .. j+h of the row are all set.  Only the 32 bits R .. R+31 are ever used, so the
+        // shifted copies are taken as 32-bit windows of the 64-bit row (one funnel shift each) and E[h] = E[h-1] & w[-h] &
+        // w[+h] is one three-input logic operation: 2R + 1 shifts + R LOP3 per row instead of 64-bit shift/AND chains
+        // (ncu, round 2: the ALU pipe was 78 % busy with those, 37 us per 2048^2 image).
         unsigned int eh[R + 1];
-        eh[0] = (unsigned int)(e >> R);
+        eh[0] = __funnelshift_r(rlo, rhi, R);
 #pragma unroll
-        for (int h = 1; h <= R; ++h) {
-          e &= (row << h) & (row >> h);
-          eh[h] = (unsigned int)(e >> R);
-        }
+        for (int h = 1; h <= R; ++h)
+          eh[h] = eh[h - 1] & __funnelshift_r(rlo, rhi, R - h) & __funnelshift_r(rlo, rhi, R + h);
         // this input row is row (yi - yo) of the footprint for output row yo = yi - dy
 #pragma unroll
         for (int k = 0; k <= 2 * R; ++k) {
@@ -113,10 +169,7 @@ __global__ void __launch_bounds__(128) erode_disk_bits(const uint8_t* __restrict
         const int yo = yi - R;
         constexpr int M = 2 * R + 1;
         const int slot = (s - R + M) % M;
-        if (yo >= y0 && yo < y1) {
-          const int x = x0 + lane;
-          if (x < W) out[(int64_t)yo * W + x] = (acc[slot] >> lane) & 1u;
-        }
+        if (yo >= y0 && yo < y1 && xo < W) out[(int64_t)yo * W + xo] = (acc[slot] >> lane) & 1u;
         acc[slot] = 0xffffffffu;
       }
     }
@@ -169,52 +222,113 @@ __device__ __forceinline__ void uf_union(int* parent, int a, int b) {
 
 // Step 1: every foreground pixel points at the start of its horizontal run inside its 32-pixel warp segment (one
 // ballot per warp instead of one atomic per pixel pair; a tree is at most one link deep afterwards).
+constexpr int CCL_RPB = 4;    // rows per CTA of ccl_init
 __global__ void __launch_bounds__(256) ccl_init(const uint8_t* __restrict__ m, int H, int W, int fg_is_zero,
                                                 int* __restrict__ parent) {
-  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, yb = blockIdx.y * CCL_RPB;
   const bool in = x < W;
-  const bool fg = in && (fg_is_zero ? (m[(int64_t)y * W + x] == 0) : (m[(int64_t)y * W + x] != 0));
-  const unsigned int bits = __ballot_sync(0xffffffffu, fg);
-  if (!in) return;
   const int lane = threadIdx.x & 31;
-  // highest zero bit below this lane -> the run starts one past it
-  const unsigned int below = ~bits & ((1u << lane) - 1u);
-  const int start = below ? 32 - __clz(below) : 0;
-  parent[y * W + x] = fg ? y * W + (x - lane + start) : -1;
+  uint8_t v[CCL_RPB];
+#pragma unroll
+  for (int k = 0; k < CCL_RPB; ++k) v[k] = (in && yb + k < H) ? m[(int64_t)(yb + k) * W + x] : (uint8_t)(fg_is_zero ? 1 : 0);
+#pragma unroll
+  for (int k = 0; k < CCL_RPB; ++k) {
+    const int y = yb + k;
+    if (y >= H) break;                                   // CTA-uniform
+    const bool fg = in && (fg_is_zero ? (v[k] == 0) : (v[k] != 0));
+    const unsigned int bits = __ballot_sync(0xffffffffu, fg);
+    if (!in) continue;
+    // highest zero bit below this lane -> the run starts one past it
+    const unsigned int below = ~bits & ((1u << lane) - 1u);
+    const int start = below ? 32 - __clz(below) : 0;
+    parent[y * W + x] = fg ? y * W + (x - lane + start) : -1;
+  }
 }
 // Step 2: link the runs.  A pixel only issues the unions its left neighbour has not already made:
 //   * a run that continues across a 32-pixel segment boundary is joined to the previous segment;
 //   * upwards (8-connectivity): W set -> only NE, and only if N is clear (W already met N and NW);
 //     W clear -> N if set (N's own run reaches NW and NE), else NW and NE separately.
 //   * 4-connectivity: N only, and only for the first pixel of a run or where the left neighbour had no N.
-__global__ void __launch_bounds__(256) ccl_merge(int* __restrict__ parent, int H, int W, int conn8) {
-  int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+// Foreground tests read the byte mask (not the 4-byte parent array) and a CTA walks MRG_RPB rows, each row's three
+// neighbour bytes serving as the "row above" of the next.
+constexpr int MRG_RPB = 4;
+__global__ void __launch_bounds__(256) ccl_merge(const uint8_t* __restrict__ m, int fg_is_zero, int* __restrict__ parent, int H, int W,
+                                                 int conn8) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, yb = blockIdx.y * MRG_RPB;
   if (x >= W) return;
-  int i = y * W + x;
-  if (parent[i] < 0) return;
-  const bool w = x > 0 && parent[i - 1] >= 0;
-  if (w && (x & 31) == 0) uf_union(parent, i, i - 1);
-  if (y == 0) return;
-  const bool n = parent[i - W] >= 0;
-  if (conn8) {
-    const bool ne = x + 1 < W && parent[i - W + 1] >= 0;
-    if (w) {
-      if (ne && !n) uf_union(parent, i, i - W + 1);
-    } else if (n) {
-      uf_union(parent, i, i - W);
-    } else {
-      if (x > 0 && parent[i - W - 1] >= 0) uf_union(parent, i, i - W - 1);
-      if (ne) uf_union(parent, i, i - W + 1);
+  const uint8_t bg = fg_is_zero ? 1 : 0;                 // a byte that reads as background
+  uint8_t L[MRG_RPB + 1], C[MRG_RPB + 1], Rt[MRG_RPB + 1];
+#pragma unroll
+  for (int k = 0; k <= MRG_RPB; ++k) {
+    const int y = yb - 1 + k;
+    const bool row_in = y >= 0 && y < H;
+    const uint8_t* p = m + (int64_t)(row_in ? y : 0) * W;
+    C[k] = row_in ? p[x] : bg;
+    L[k] = (row_in && x > 0) ? p[x - 1] : bg;
+    Rt[k] = (row_in && x + 1 < W) ? p[x + 1] : bg;
+  }
+  auto fg = [&](uint8_t v) -> bool { return fg_is_zero ? (v == 0) : (v != 0); };
+#pragma unroll
+  for (int k = 1; k <= MRG_RPB; ++k) {
+    const int y = yb + k - 1;
+    if (y >= H) break;
+    if (!fg(C[k])) continue;
+    const int i = y * W + x;
+    const bool w = fg(L[k]);
+    if (w && (x & 31) == 0) uf_union(parent, i, i - 1);
+    if (y == 0) continue;
+    const bool n = fg(C[k - 1]), ne = fg(Rt[k - 1]), nw = fg(L[k - 1]);
+    if (conn8) {
+      if (w) {
+        if (ne && !n) uf_union(parent, i, i - W + 1);
+      } else if (n) {
+        uf_union(parent, i, i - W);
+      } else {
+        if (nw) uf_union(parent, i, i - W - 1);
+        if (ne) uf_union(parent, i, i - W + 1);
+      }
+    } else if (n && !(w && nw)) {
+      uf_union(parent, i, i - W);        // W and NW both set: the left neighbour already joined this run to the run above
     }
-  } else if (n && !(w && parent[i - W - 1] >= 0)) {
-    uf_union(parent, i, i - W);          // W and NW both set: the left neighbour already joined this run to the run above
   }
 }
 
+// The streaming kernels of this file take EPT elements per thread, 256 apart (coalesced, no alignment requirement, all
+// loads issued before the first use): one element per thread meant 16 384 one-shot CTAs per 2048^2 image and 13-16 us
+// per pass whatever the pass did (ncu, round 2).
+constexpr int EPT = 4;
 __global__ void __launch_bounds__(256) ccl_flatten(int* __restrict__ parent, int64_t n) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n || parent[i] < 0) return;
-  parent[i] = uf_find(parent, (int)i);
+  const int64_t base = (int64_t)blockIdx.x * (256 * EPT) + threadIdx.x;
+  int p[EPT];
+#pragma unroll
+  for (int k = 0; k < EPT; ++k) { const int64_t i = base + k * 256; p[k] = i < n ? parent[i] : -1; }
+#pragma unroll
+  for (int k = 0; k < EPT; ++k) {
+    const int64_t i = base + k * 256;
+    if (p[k] >= 0) parent[i] = uf_find(parent, (int)i);
+  }
+}
+// ccl_flatten that also zeroes the per-root statistics of the cleanup driver (area, the 10 perimeter counters, the kill
+// flag) at every root it meets: one pass less over the parent array than a separate initialisation kernel
+__global__ void __launch_bounds__(256) ccl_flatten_init(int* __restrict__ parent, int64_t n, unsigned int* __restrict__ area,
+                                                        unsigned int* __restrict__ hist10, uint8_t* __restrict__ kill) {
+  const int64_t base = (int64_t)blockIdx.x * (256 * EPT) + threadIdx.x;
+  int p[EPT];
+#pragma unroll
+  for (int k = 0; k < EPT; ++k) { const int64_t i = base + k * 256; p[k] = i < n ? parent[i] : -1; }
+#pragma unroll
+  for (int k = 0; k < EPT; ++k) {
+    const int64_t i = base + k * 256;
+    if (p[k] < 0) continue;
+    const int r = uf_find(parent, (int)i);
+    parent[i] = r;
+    if (r == (int)i) {
+      area[i] = 0;
+#pragma unroll
+      for (int c = 0; c < 10; ++c) hist10[i * 10 + c] = 0;
+      kill[i] = 0;
+    }
+  }
 }
 
 // raster-order renumbering: rank of each root among the roots (3-kernel scan over 1024-pixel blocks)
@@ -352,27 +466,37 @@ __device__ __forceinline__ int perim_slot(int code) {
 
 // ---- the cleanup driver's statistics, indexed by ROOT PIXEL instead of by label rank ------------------------------
 // filter_branch_seg_mask never needs the raster-order label numbers, only "which component": the root pixel index does.
-// Per-root arrays have one entry per pixel but only root entries are ever touched (zeroed by root_init_kernel), so the
+// Per-root arrays have one entry per pixel but only root entries are ever touched (zeroed by ccl_flatten_init), so the
 // four renumbering kernels and every memset of a label-sized array disappear from the path.
-__global__ void __launch_bounds__(256) root_init_kernel(const int* __restrict__ parent, int64_t n, unsigned int* __restrict__ area,
-                                                        unsigned int* __restrict__ hist10, uint8_t* __restrict__ round_flag,
-                                                        uint8_t* __restrict__ kill) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n || parent[i] != (int)i) return;
-  area[i] = 0;
-#pragma unroll
-  for (int c = 0; c < 10; ++c) hist10[i * 10 + c] = 0;
-  round_flag[i] = 0;
-  kill[i] = 0;
-}
-__global__ void __launch_bounds__(256) border_from_roots(const int* __restrict__ parent, int H, int W, uint8_t* __restrict__ border) {
-  int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+// border pixels of the mask (skimage perimeter: foreground with a background or outside 4-neighbour), from the 0/1 mask
+// itself (a byte per pixel instead of the 4-byte parent array), RPB rows per CTA
+constexpr int RPB = 4;
+static inline dim3 grid2d_rpb(int H, int W) { return dim3(cdiv(W, 256), cdiv(H, RPB)); }
+__global__ void __launch_bounds__(256) border_from_mask(const uint8_t* __restrict__ m, int H, int W, uint8_t* __restrict__ border) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, yb = blockIdx.y * RPB;
   if (x >= W) return;
-  int64_t i = (int64_t)y * W + x;
-  bool fg = parent[i] >= 0;
-  bool interior = fg && y > 0 && y + 1 < H && x > 0 && x + 1 < W && parent[i - W] >= 0 && parent[i + W] >= 0 &&
-                  parent[i - 1] >= 0 && parent[i + 1] >= 0;
-  border[i] = fg && !interior;
+  // rows yb - 1 .. yb + RPB of column x and of its two neighbours, loaded once
+  uint8_t c[RPB + 2], l[RPB], r[RPB];
+#pragma unroll
+  for (int k = 0; k < RPB + 2; ++k) {
+    const int y = yb - 1 + k;
+    c[k] = (y >= 0 && y < H) ? m[(int64_t)y * W + x] : (uint8_t)0;
+  }
+#pragma unroll
+  for (int k = 0; k < RPB; ++k) {
+    const int y = yb + k;
+    const bool in = y < H;
+    l[k] = (in && x > 0) ? m[(int64_t)y * W + x - 1] : (uint8_t)0;
+    r[k] = (in && x + 1 < W) ? m[(int64_t)y * W + x + 1] : (uint8_t)0;
+  }
+#pragma unroll
+  for (int k = 0; k < RPB; ++k) {
+    const int y = yb + k;
+    if (y >= H) break;
+    const bool fg = c[k + 1] != 0;
+    const bool interior = fg && c[k] && c[k + 2] && l[k] && r[k];       // outside the image counts as background
+    border[(int64_t)y * W + x] = fg && !interior;
+  }
 }
 // one atomic per distinct key per warp: the pixels of a warp mostly belong to one or two components
 __device__ __forceinline__ void warp_count(unsigned int* __restrict__ counters, long long key) {
@@ -404,34 +528,47 @@ __global__ void __launch_bounds__(256) root_stats_kernel(const int* __restrict__
   }
   warp_count(hist10, hkey);
 }
-__global__ void __launch_bounds__(256) root_circ_kernel(const int* __restrict__ parent, int64_t n, const unsigned int* __restrict__ area,
-                                                        const unsigned int* __restrict__ hist10, uint8_t* __restrict__ round_flag) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n || parent[i] != (int)i) return;
+// skimage: circularity = 4 pi area / (perimeter^2 + 1e-7), perimeter = sum of the 10 code counters x their weights
+__device__ __forceinline__ bool root_is_round(const unsigned int* __restrict__ area, const unsigned int* __restrict__ hist10, int r) {
   const double w2 = 1.4142135623730951, w3 = (1.0 + 1.4142135623730951) / 2.0;
   const double wt[10] = {1.0, 1.0, w3, 1.0, 1.0, w2, w3, 1.0, 1.0, w2};
   double perim = 0.0;
 #pragma unroll
-  for (int c = 0; c < 10; ++c) perim = __dadd_rn(perim, __dmul_rn((double)hist10[i * 10 + c], wt[c]));
-  double circ = __ddiv_rn(__dmul_rn(__dmul_rn(4.0, 3.141592653589793), (double)area[i]),
-                          __dadd_rn(__dmul_rn(perim, perim), 1e-7));
-  round_flag[i] = circ > 0.8;
+  for (int c = 0; c < 10; ++c) perim = __dadd_rn(perim, __dmul_rn((double)hist10[(int64_t)r * 10 + c], wt[c]));
+  const double circ = __ddiv_rn(__dmul_rn(__dmul_rn(4.0, 3.141592653589793), (double)area[r]),
+                                __dadd_rn(__dmul_rn(perim, perim), 1e-7));
+  return circ > 0.8;
 }
-// one thread per skeleton component (its root pixel): decide whether the mask component under it dies
+// one thread per skeleton component (its root pixel): decide whether the mask component under it dies.  Every mask
+// component carries a skeleton component (thinning never removes a component's last pixel), so the circularity test
+// (transforms.py:346-351) is evaluated here, once per skeleton root, instead of in a pass of its own over all pixels.
 __global__ void __launch_bounds__(256) root_kill_kernel(const int* __restrict__ sk_root, const uint8_t* __restrict__ has_fork,
-                                                        const int* __restrict__ parent, const uint8_t* __restrict__ round_flag,
-                                                        int64_t n, int remove_isolated, uint8_t* __restrict__ kill) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n || sk_root[i] != (int)i) return;
-  const int r = parent[i];                      // the skeleton is a subset of the mask: r >= 0
-  if ((remove_isolated && !has_fork[i]) || round_flag[r]) kill[r] = 1;
+                                                        const int* __restrict__ parent, const unsigned int* __restrict__ area,
+                                                        const unsigned int* __restrict__ hist10, int64_t n, int remove_isolated,
+                                                        uint8_t* __restrict__ kill) {
+  const int64_t base = (int64_t)blockIdx.x * (256 * EPT) + threadIdx.x;
+  int sr[EPT];
+#pragma unroll
+  for (int k = 0; k < EPT; ++k) { const int64_t i = base + k * 256; sr[k] = i < n ? sk_root[i] : -1; }
+#pragma unroll
+  for (int k = 0; k < EPT; ++k) {
+    const int64_t i = base + k * 256;
+    if (i >= n || sr[k] != (int)i) continue;
+    const int r = parent[i];                    // the skeleton is a subset of the mask: r >= 0
+    if ((remove_isolated && !has_fork[i]) || root_is_round(area, hist10, r)) kill[r] = 1;
+  }
 }
 __global__ void __launch_bounds__(256) root_apply_kill(const int* __restrict__ parent, const uint8_t* __restrict__ kill, int64_t n,
                                                        uint8_t* __restrict__ out) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const int r = parent[i];
-  out[i] = r >= 0 && !kill[r];
+  const int64_t base = (int64_t)blockIdx.x * (256 * EPT) + threadIdx.x;
+  int r[EPT];
+  uint8_t dead[EPT];
+#pragma unroll
+  for (int k = 0; k < EPT; ++k) { const int64_t i = base + k * 256; r[k] = i < n ? parent[i] : -1; }
+#pragma unroll
+  for (int k = 0; k < EPT; ++k) dead[k] = r[k] >= 0 ? kill[r[k]] : (uint8_t)1;
+#pragma unroll
+  for (int k = 0; k < EPT; ++k) { const int64_t i = base + k * 256; if (i < n) out[i] = !dead[k]; }
 }
 
 // ---- Zhang-Suen thinning (skimage.morphology.skeletonize, 2-D) -----------------------------------------
@@ -638,8 +775,12 @@ __global__ void __launch_bounds__(256) fork_kernel(const uint8_t* __restrict__ s
   if (__popc(nb_code(sk, H, W, y, x)) > 2) has_fork[sk_root[i]] = 1;
 }
 __global__ void __launch_bounds__(256) binarize(const uint8_t* __restrict__ m, int64_t n, uint8_t* __restrict__ out) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) out[i] = m[i] != 0;
+  const int64_t base = (int64_t)blockIdx.x * (256 * EPT) + threadIdx.x;
+  uint8_t v[EPT];
+#pragma unroll
+  for (int k = 0; k < EPT; ++k) { const int64_t i = base + k * 256; v[k] = i < n ? m[i] : (uint8_t)0; }
+#pragma unroll
+  for (int k = 0; k < EPT; ++k) { const int64_t i = base + k * 256; if (i < n) out[i] = v[k] != 0; }
 }
 
 // ---- per-root areas (no renumbering needed) ------------------------------------------------------------
@@ -752,6 +893,7 @@ extern "C" int tmat_skeleton_lut_get(uint8_t* lut256) {
 
 static inline dim3 grid2d(int H, int W) { return dim3(cdiv(W, 256), H); }
 static inline unsigned grid1d(int64_t n) { return (unsigned)cdiv64(n, 256); }
+static inline unsigned grid1d_ept(int64_t n) { return (unsigned)cdiv64(n, 256 * EPT); }
 
 int erode_disk_thr(tmat_ctx* ctx, const uint8_t* in, int H, int W, int r, int border_value, const int* thr_params_dev,
                    uint8_t* out, cudaStream_t st) {
@@ -780,7 +922,9 @@ int erode_disk(tmat_ctx* ctx, const uint8_t* in, int H, int W, int r, int border
 }
 
 int median_disk2(tmat_ctx* ctx, const uint8_t* in, int H, int W, uint8_t* out, cudaStream_t st) {
-  median_disk2_kernel<<<grid2d(H, W), 256, 0, st>>>(in, H, W, out);
+  static const bool per_pixel = [] { const char* v = getenv("TMAT_MEDIAN_PER_PIXEL"); return v && atoi(v) == 1; }();
+  if (per_pixel) median_disk2_kernel<<<grid2d(H, W), 256, 0, st>>>(in, H, W, out);
+  else median_disk2_bits<<<dim3(cdiv(W, 32), cdiv(cdiv(H, MED_SEG), 4)), 128, 0, st>>>(in, H, W, out);
   KERNEL_CHECK(ctx);
   return TMAT_OK;
 }
@@ -813,15 +957,17 @@ int footprint_filter(tmat_ctx* ctx, const uint8_t* in, int H, int W, const uint8
 
 // parent[i] = index of the first pixel (raster order) of i's component, -1 for background
 static int ccl_roots(tmat_ctx* ctx, const uint8_t* mask, int H, int W, int connectivity, int fg_is_zero, int* parent,
-                     cudaStream_t st) {
+                     cudaStream_t st, unsigned int* init_area = nullptr, unsigned int* init_hist10 = nullptr,
+                     uint8_t* init_kill = nullptr) {
   TMAT_REQUIRE(connectivity == 1 || connectivity == 2, "label: connectivity must be 1 or 2, got %d", connectivity);
   TMAT_REQUIRE((int64_t)H * W < (1ll << 31), "label: image too large");
   int64_t n = (int64_t)H * W;
-  ccl_init<<<grid2d(H, W), 256, 0, st>>>(mask, H, W, fg_is_zero, parent);
+  ccl_init<<<dim3(cdiv(W, 256), cdiv(H, CCL_RPB)), 256, 0, st>>>(mask, H, W, fg_is_zero, parent);
   KERNEL_CHECK(ctx);
-  ccl_merge<<<grid2d(H, W), 256, 0, st>>>(parent, H, W, connectivity == 2);
+  ccl_merge<<<dim3(cdiv(W, 256), cdiv(H, MRG_RPB)), 256, 0, st>>>(mask, fg_is_zero, parent, H, W, connectivity == 2);
   KERNEL_CHECK(ctx);
-  ccl_flatten<<<grid1d(n), 256, 0, st>>>(parent, n);
+  if (init_area) ccl_flatten_init<<<grid1d_ept(n), 256, 0, st>>>(parent, n, init_area, init_hist10, init_kill);
+  else ccl_flatten<<<grid1d_ept(n), 256, 0, st>>>(parent, n);
   KERNEL_CHECK(ctx);
   return TMAT_OK;
 }
@@ -859,7 +1005,7 @@ static int skeletonize_impl(tmat_ctx* ctx, const uint8_t* mask, int H, int W, ui
   int64_t n = (int64_t)H * W;
   uint8_t* tmp;
   TMAT_TRY(arena_get(ctx, (size_t)n, &tmp));
-  binarize<<<grid1d(n), 256, 0, st>>>(mask, n, out);
+  binarize<<<grid1d_ept(n), 256, 0, st>>>(mask, n, out);
   KERNEL_CHECK(ctx);
   static const bool no_coop = [] { const char* e = getenv("TMAT_THIN_MULTILAUNCH"); return e && atoi(e) != 0; }();
   static const int variant = [] { const char* e = getenv("TMAT_THIN_VARIANT"); return e ? atoi(e) : 1; }();   // 1: 8-pixel words (default where W % 8 == 0), 2: tiles
@@ -961,7 +1107,7 @@ int filter_branch_impl(tmat_ctx* ctx, const uint8_t* mask, int H, int W, int use
                        uint8_t* out, cudaStream_t st) {
   TMAT_REQUIRE((int64_t)H * W < (1ll << 31), "filter_branch_seg_mask: image too large");
   int64_t n = (int64_t)H * W;
-  uint8_t *m, *sk, *border, *round_flag, *kill, *has_fork;
+  uint8_t *m, *sk, *border, *kill, *has_fork;
   int *parent, *sk_root;
   unsigned int *area, *hist;
   TMAT_TRY(arena_get(ctx, (size_t)n, &m));
@@ -971,29 +1117,24 @@ int filter_branch_impl(tmat_ctx* ctx, const uint8_t* mask, int H, int W, int use
   TMAT_TRY(arena_get(ctx, (size_t)n, &sk_root));
   TMAT_TRY(arena_get(ctx, (size_t)n, &area));
   TMAT_TRY(arena_get(ctx, (size_t)n * 10, &hist));
-  TMAT_TRY(arena_get(ctx, (size_t)n, &round_flag));
   TMAT_TRY(arena_get(ctx, (size_t)n, &kill));
   TMAT_TRY(arena_get(ctx, (size_t)n, &has_fork));
   if (use_median) TMAT_TRY(median_disk2(ctx, mask, H, W, m, st));
-  else { binarize<<<grid1d(n), 256, 0, st>>>(mask, n, m); KERNEL_CHECK(ctx); }
+  else { binarize<<<grid1d_ept(n), 256, 0, st>>>(mask, n, m); KERNEL_CHECK(ctx); }
   // components by root pixel; no renumbering, no host round trip anywhere below
-  TMAT_TRY(ccl_roots(ctx, m, H, W, 2, 0, parent, st));
-  root_init_kernel<<<grid1d(n), 256, 0, st>>>(parent, n, area, hist, round_flag, kill);
-  KERNEL_CHECK(ctx);
-  border_from_roots<<<grid2d(H, W), 256, 0, st>>>(parent, H, W, border);
+  TMAT_TRY(ccl_roots(ctx, m, H, W, 2, 0, parent, st, area, hist, kill));
+  border_from_mask<<<grid2d_rpb(H, W), 256, 0, st>>>(m, H, W, border);
   KERNEL_CHECK(ctx);
   root_stats_kernel<<<grid2d(H, W), 256, 0, st>>>(parent, border, H, W, area, hist);
-  KERNEL_CHECK(ctx);
-  root_circ_kernel<<<grid1d(n), 256, 0, st>>>(parent, n, area, hist, round_flag);
   KERNEL_CHECK(ctx);
   TMAT_TRY(skeletonize_impl(ctx, m, H, W, sk, nullptr, st));
   TMAT_TRY(ccl_roots(ctx, sk, H, W, 2, 0, sk_root, st));
   CUDA_TRY(cudaMemsetAsync(has_fork, 0, (size_t)n, st));
   fork_kernel<<<grid2d(H, W), 256, 0, st>>>(sk, H, W, sk_root, has_fork);
   KERNEL_CHECK(ctx);
-  root_kill_kernel<<<grid1d(n), 256, 0, st>>>(sk_root, has_fork, parent, round_flag, n, remove_isolated, kill);
+  root_kill_kernel<<<grid1d_ept(n), 256, 0, st>>>(sk_root, has_fork, parent, area, hist, n, remove_isolated, kill);
   KERNEL_CHECK(ctx);
-  root_apply_kill<<<grid1d(n), 256, 0, st>>>(parent, kill, n, out);
+  root_apply_kill<<<grid1d_ept(n), 256, 0, st>>>(parent, kill, n, out);
   KERNEL_CHECK(ctx);
   return TMAT_OK;
 }
