@@ -602,7 +602,7 @@ __device__ __forceinline__ void grid_barrier(unsigned int* bar, unsigned int& go
     goal += gridDim.x;
     __threadfence();
     atomicAdd(bar, 1u);
-    while (*(volatile unsigned int*)bar < goal) {}
+    while (*(volatile unsigned int*)bar < goal) __nanosleep(40);       // back off: the pollers share one L2 line with the arrivals
     __threadfence();
   }
   __syncthreads();
@@ -642,22 +642,164 @@ __device__ __forceinline__ unsigned int thin_pass_words(const uint8_t* __restric
   }
   return removed;
 }
-// img: the 0/1 image, thinned in place; tmp: scratch of the same size; counters[r] = pixels removed in round r
-// (zeroed by the caller, at least max_rounds entries); bar: zeroed barrier word; iters_out: rounds executed.
-__global__ void __launch_bounds__(256) thin_persistent(uint8_t* __restrict__ img, uint8_t* __restrict__ tmp, int H, int W,
+// Thinning only removes pixels: a word that is zero stays zero.  The words with a set pixel are therefore listed ONCE
+// (warp-aggregated append; the same scan copies the image into the ping-pong buffer so that both agree everywhere) and
+// every sub-pass walks the list instead of the image -- a vessel mask has a set pixel in 10-30 % of its words, and the
+// full-image sub-passes (read 4 MB, write 4 MB, 14 times) were 130 of the 316 us of filter_branch_seg_mask.
+__device__ __forceinline__ void thin_build_list(const uint8_t* __restrict__ img, uint8_t* __restrict__ tmp, int nw,
+                                                int* __restrict__ list, unsigned int* __restrict__ n_active) {
+  const int lane = threadIdx.x & 31;
+  const int stride = gridDim.x * blockDim.x;
+  for (int i0 = blockIdx.x * blockDim.x; i0 < nw; i0 += stride) {          // block-uniform trip count
+    const int i = i0 + threadIdx.x;
+    unsigned long long c = 0ull;
+    if (i < nw) {
+      c = reinterpret_cast<const unsigned long long*>(img)[i];
+      reinterpret_cast<unsigned long long*>(tmp)[i] = c;
+    }
+    const unsigned int nz = __ballot_sync(0xffffffffu, c != 0ull);
+    if (nz) {
+      unsigned int base = 0;
+      if (lane == 0) base = atomicAdd(n_active, (unsigned int)__popc(nz));
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (c != 0ull) list[base + __popc(nz & ((1u << lane) - 1u))] = i;
+    }
+  }
+}
+// TLB listed words per thread and iteration, their loads issued together: a word's chain list -> word -> 3 neighbour rows
+// is three dependent L2 round trips, and with one word at a time that latency, not the barrier, was the sub-pass.
+constexpr int TLB = 4;
+__device__ __forceinline__ unsigned int thin_pass_list(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int H, int W,
+                                                       const uint8_t* __restrict__ s_lut, int bit, const int* __restrict__ list,
+                                                       int n_list, int k_begin) {
+  const int wpr = W >> 3;
+  const int stride = gridDim.x * blockDim.x;
+  unsigned int removed = 0;
+  for (int k0 = k_begin + blockIdx.x * blockDim.x + threadIdx.x; k0 < n_list; k0 += TLB * stride) {
+    int idx[TLB], yy[TLB], xx[TLB];
+    unsigned long long c[TLB];
+    uint32_t U[TLB], C[TLB], D[TLB];
+#pragma unroll
+    for (int b = 0; b < TLB; ++b) { const int k = k0 + b * stride; idx[b] = k < n_list ? list[k] : -1; }
+#pragma unroll
+    for (int b = 0; b < TLB; ++b) {
+      c[b] = 0ull;
+      if (idx[b] >= 0) {
+        yy[b] = idx[b] / wpr; xx[b] = idx[b] - yy[b] * wpr;
+        c[b] = reinterpret_cast<const unsigned long long*>(in)[idx[b]];
+      }
+    }
+#pragma unroll
+    for (int b = 0; b < TLB; ++b) {
+      if (c[b] != 0ull) {
+        U[b] = row_bits(in, W, yy[b] - 1, xx[b], H); C[b] = row_bits(in, W, yy[b], xx[b], H); D[b] = row_bits(in, W, yy[b] + 1, xx[b], H);
+      }
+    }
+#pragma unroll
+    for (int b = 0; b < TLB; ++b) {
+      if (idx[b] < 0) continue;
+      unsigned long long cw = c[b];
+      if (cw != 0ull) {
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          if ((C[b] >> (q + 1)) & 1u) {
+            const uint32_t code = ((U[b] >> q) & 7u) | (((C[b] >> (q + 2)) & 1u) << 3) | (((D[b] >> (q + 2)) & 1u) << 4) |
+                                  (((D[b] >> (q + 1)) & 1u) << 5) | (((D[b] >> q) & 1u) << 6) | (((C[b] >> q) & 1u) << 7);
+            if (s_lut[code] & bit) { cw &= ~(0xffull << (8 * q)); ++removed; }
+          }
+        }
+      }
+      reinterpret_cast<unsigned long long*>(out)[idx[b]] = cw;      // also when it became zero: out holds an older state
+    }
+  }
+  return removed;
+}
+// The first TLB listed words of a thread are ITS words in every sub-pass (static assignment), so their indices and their
+// current values stay in registers across the whole kernel: a sub-pass then starts with the neighbour-row loads instead
+// of the dependent chain list -> word -> neighbours (three L2 round trips -> one).
+struct ThinOwn { int idx[TLB]; unsigned long long cur[TLB]; };
+__device__ __forceinline__ unsigned int thin_pass_own(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int H, int W,
+                                                      const uint8_t* __restrict__ s_lut, int bit, ThinOwn& o) {
+  const int wpr = W >> 3;
+  unsigned int removed = 0;
+  uint32_t U[TLB], C[TLB], D[TLB];
+#pragma unroll
+  for (int b = 0; b < TLB; ++b) {
+    if (o.idx[b] >= 0 && o.cur[b] != 0ull) {
+      const int y = o.idx[b] / wpr, xw = o.idx[b] - y * wpr;
+      U[b] = row_bits(in, W, y - 1, xw, H);
+      D[b] = row_bits(in, W, y + 1, xw, H);
+      const uint8_t* row = in + (int64_t)y * W;
+      uint32_t c = (uint32_t)(((o.cur[b] & 0x0101010101010101ull) * 0x0102040810204080ull) >> 56) << 1;
+      if (xw > 0) c |= row[8 * xw - 1] & 1u;
+      if (8 * xw + 8 < W) c |= (uint32_t)(row[8 * xw + 8] & 1u) << 9;
+      C[b] = c;
+    }
+  }
+#pragma unroll
+  for (int b = 0; b < TLB; ++b) {
+    if (o.idx[b] < 0) continue;
+    unsigned long long cw = o.cur[b];
+    if (cw != 0ull) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        if ((C[b] >> (q + 1)) & 1u) {
+          const uint32_t code = ((U[b] >> q) & 7u) | (((C[b] >> (q + 2)) & 1u) << 3) | (((D[b] >> (q + 2)) & 1u) << 4) |
+                                (((D[b] >> (q + 1)) & 1u) << 5) | (((D[b] >> q) & 1u) << 6) | (((C[b] >> q) & 1u) << 7);
+          if (s_lut[code] & bit) { cw &= ~(0xffull << (8 * q)); ++removed; }
+        }
+      }
+      o.cur[b] = cw;
+    }
+    reinterpret_cast<unsigned long long*>(out)[o.idx[b]] = cw;
+  }
+  return removed;
+}
+// THIN_THREADS threads per CTA, one CTA per SM by default: with the list a sub-pass is a few microseconds of work and the
+// grid barrier (one atomic and one spinning thread per CTA) is what a round costs -- 148 participants instead of 592.
+constexpr int THIN_THREADS = 512;
+__global__ void __launch_bounds__(THIN_THREADS) thin_persistent(uint8_t* __restrict__ img, uint8_t* __restrict__ tmp, int H, int W,
                                                        const uint8_t* __restrict__ lut, unsigned int* __restrict__ counters,
-                                                       int max_rounds, unsigned int* __restrict__ bar, int* __restrict__ iters_out) {
+                                                       int max_rounds, unsigned int* __restrict__ bar, int* __restrict__ iters_out,
+                                                       int* __restrict__ list, unsigned int* __restrict__ n_active) {
   __shared__ uint8_t s_lut[256];
   __shared__ unsigned int s_removed;
-  s_lut[threadIdx.x] = lut[threadIdx.x];
+  if (threadIdx.x < 256) s_lut[threadIdx.x] = lut[threadIdx.x];
   unsigned int goal = 0;
   int round = 0;
+  const bool use_list = list != nullptr;
+  int n_list = 0;
+  ThinOwn own;
+  const int stride = gridDim.x * blockDim.x;
+  if (use_list) {
+    thin_build_list(img, tmp, H * (W >> 3), list, n_active);
+    grid_barrier(bar, goal);
+    n_list = (int)*(volatile unsigned int*)n_active;
+#pragma unroll
+    for (int b = 0; b < TLB; ++b) {
+      const int k = blockIdx.x * blockDim.x + threadIdx.x + b * stride;
+      own.idx[b] = k < n_list ? list[k] : -1;
+    }
+#pragma unroll
+    for (int b = 0; b < TLB; ++b) own.cur[b] = own.idx[b] >= 0 ? reinterpret_cast<const unsigned long long*>(img)[own.idx[b]] : 0ull;
+  }
   for (; round < max_rounds; ++round) {
     if (threadIdx.x == 0) s_removed = 0;
     __syncthreads();
-    unsigned int r = thin_pass_words(img, tmp, H, W, s_lut, 1);
+    unsigned int r;
+    if (use_list) {
+      r = thin_pass_own(img, tmp, H, W, s_lut, 1, own);
+      if (n_list > TLB * stride) r += thin_pass_list(img, tmp, H, W, s_lut, 1, list, n_list, TLB * stride);
+    } else {
+      r = thin_pass_words(img, tmp, H, W, s_lut, 1);
+    }
     grid_barrier(bar, goal);
-    r += thin_pass_words(tmp, img, H, W, s_lut, 2);
+    if (use_list) {
+      r += thin_pass_own(tmp, img, H, W, s_lut, 2, own);
+      if (n_list > TLB * stride) r += thin_pass_list(tmp, img, H, W, s_lut, 2, list, n_list, TLB * stride);
+    } else {
+      r += thin_pass_words(tmp, img, H, W, s_lut, 2);
+    }
     for (int o = 16; o > 0; o >>= 1) r += __shfl_xor_sync(0xffffffffu, r, o);
     if ((threadIdx.x & 31) == 0 && r) atomicAdd(&s_removed, r);
     __syncthreads();
@@ -781,6 +923,93 @@ __global__ void __launch_bounds__(256) binarize(const uint8_t* __restrict__ m, i
   for (int k = 0; k < EPT; ++k) { const int64_t i = base + k * 256; v[k] = i < n ? m[i] : (uint8_t)0; }
 #pragma unroll
   for (int k = 0; k < EPT; ++k) { const int64_t i = base + k * 256; if (i < n) out[i] = v[k] != 0; }
+}
+
+// ---- the skeleton's components, forks and the kill decision over the thinning's word list ------------------------
+// The skeleton has a set pixel in a few per cent of the image's words, all of them on the list the thinning kernel
+// built.  Labelling it with the dense kernels (three passes over every pixel), marking forks and deciding the kills
+// cost ~85 us per 2048^2 image; here one thread takes one listed word (8 pixels), sk_root is preset to -1 by a memset.
+// Same union rules as ccl_merge, with runs that start at word boundaries.
+__global__ void __launch_bounds__(256) sk_init_list(const uint8_t* __restrict__ sk, int H, int W, const int* __restrict__ list,
+                                                    const unsigned int* __restrict__ n_list, int* __restrict__ sk_root,
+                                                    uint8_t* __restrict__ has_fork) {
+  const int wpr = W >> 3, n = (int)*n_list;
+  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+    const int i = list[k];
+    const int y = i / wpr, xw = i - y * wpr;
+    const unsigned long long c = *reinterpret_cast<const unsigned long long*>(sk + (int64_t)y * W + 8 * xw);
+    if (c == 0ull) continue;
+    const uint32_t bits = (uint32_t)(((c & 0x0101010101010101ull) * 0x0102040810204080ull) >> 56);
+    const int base = y * W + 8 * xw;
+    int start = 0;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      if ((bits >> q) & 1u) { sk_root[base + q] = base + start; has_fork[base + q] = 0; }
+      else start = q + 1;
+    }
+  }
+}
+// One thread per PIXEL of a listed word from here on (8 consecutive threads share a word): a union or a find is a chain
+// of dependent global accesses, and a thread that walked its word's pixels one after the other made the merge pass 35 us
+// for ~1 % of the image's pixels.
+__global__ void __launch_bounds__(256) sk_merge_list(const uint8_t* __restrict__ sk, int H, int W, const int* __restrict__ list,
+                                                     const unsigned int* __restrict__ n_list, int* __restrict__ sk_root) {
+  const int wpr = W >> 3;
+  const int64_t n = (int64_t)*n_list * 8;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (int64_t)gridDim.x * blockDim.x) {
+    const int wi = list[t >> 3], q = (int)(t & 7) + 1;
+    const int y = wi / wpr, xw = wi - y * wpr;
+    const uint32_t C = row_bits(sk, W, y, xw, H);
+    if (!((C >> q) & 1u)) continue;
+    const uint32_t U = row_bits(sk, W, y - 1, xw, H);
+    const int i = y * W + 8 * xw + q - 1;
+    const bool w = (C >> (q - 1)) & 1u;
+    if (w && q == 1) uf_union(sk_root, i, i - 1);                 // the run continues from the previous word
+    const bool n_ = (U >> q) & 1u, ne = (U >> (q + 1)) & 1u, nw = (U >> (q - 1)) & 1u;
+    if (w) {
+      if (ne && !n_) uf_union(sk_root, i, i - W + 1);
+    } else if (n_) {
+      uf_union(sk_root, i, i - W);
+    } else {
+      if (nw) uf_union(sk_root, i, i - W - 1);
+      if (ne) uf_union(sk_root, i, i - W + 1);
+    }
+  }
+}
+// flatten + fork marking: degree > 2 in the 8-neighbour pixel graph (transforms.py:248, :334)
+__global__ void __launch_bounds__(256) sk_flatten_fork_list(const uint8_t* __restrict__ sk, int H, int W, const int* __restrict__ list,
+                                                            const unsigned int* __restrict__ n_list, int* __restrict__ sk_root,
+                                                            uint8_t* __restrict__ has_fork) {
+  const int wpr = W >> 3;
+  const int64_t n = (int64_t)*n_list * 8;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (int64_t)gridDim.x * blockDim.x) {
+    const int wi = list[t >> 3], q = (int)(t & 7) + 1;
+    const int y = wi / wpr, xw = wi - y * wpr;
+    const uint32_t C = row_bits(sk, W, y, xw, H);
+    if (!((C >> q) & 1u)) continue;
+    const uint32_t U = row_bits(sk, W, y - 1, xw, H), D = row_bits(sk, W, y + 1, xw, H);
+    const int i = y * W + 8 * xw + q - 1;
+    const int r = uf_find(sk_root, i);
+    sk_root[i] = r;
+    const int deg = __popc((U >> (q - 1)) & 7u) + __popc((D >> (q - 1)) & 7u) + (int)((C >> (q - 1)) & 1u) + (int)((C >> (q + 1)) & 1u);
+    if (deg > 2) has_fork[r] = 1;
+  }
+}
+__global__ void __launch_bounds__(256) sk_kill_list(const uint8_t* __restrict__ sk, int W, const int* __restrict__ list,
+                                                    const unsigned int* __restrict__ n_list, const int* __restrict__ sk_root,
+                                                    const uint8_t* __restrict__ has_fork, const int* __restrict__ parent,
+                                                    const unsigned int* __restrict__ area, const unsigned int* __restrict__ hist10,
+                                                    int remove_isolated, uint8_t* __restrict__ kill) {
+  const int wpr = W >> 3;
+  const int64_t n = (int64_t)*n_list * 8;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (int64_t)gridDim.x * blockDim.x) {
+    const int wi = list[t >> 3];
+    const int y = wi / wpr, xw = wi - y * wpr;
+    const int i = y * W + 8 * xw + (int)(t & 7);
+    if (!sk[i] || sk_root[i] != i) continue;
+    const int r = parent[i];
+    if ((remove_isolated && !has_fork[i]) || root_is_round(area, hist10, r)) kill[r] = 1;
+  }
 }
 
 // ---- per-root areas (no renumbering needed) ------------------------------------------------------------
@@ -1001,7 +1230,8 @@ static int label_impl(tmat_ctx* ctx, const uint8_t* mask, int H, int W, int conn
 
 // iterations (optional, host): rounds executed -- asking for it costs a stream synchronisation on the cooperative path.
 static int skeletonize_impl(tmat_ctx* ctx, const uint8_t* mask, int H, int W, uint8_t* out, int* iterations,
-                            cudaStream_t st) {
+                            cudaStream_t st, int** list_out = nullptr, unsigned int** n_list_out = nullptr) {
+  if (list_out) *list_out = nullptr;
   int64_t n = (int64_t)H * W;
   uint8_t* tmp;
   TMAT_TRY(arena_get(ctx, (size_t)n, &tmp));
@@ -1018,13 +1248,13 @@ static int skeletonize_impl(tmat_ctx* ctx, const uint8_t* mask, int H, int W, ui
     unsigned int* counters;
     int* d_iters;
     TMAT_TRY(arena_get(ctx, 256, &d_lut));
-    TMAT_TRY(arena_get(ctx, (size_t)max_rounds + 2, &counters));      // [max_rounds] counters, then the barrier word
+    TMAT_TRY(arena_get(ctx, (size_t)max_rounds + 3, &counters));      // [max_rounds] counters, the barrier word, the list length
     TMAT_TRY(arena_get(ctx, 1, &d_iters));
     // the table goes through the context's pinned page so that the copy is stream-ordered and the call stays asynchronous
     uint8_t* stage = (uint8_t*)ctx->pinned + 8192 + 256 * (ctx->lut_slot++ & 7);
     memcpy(stage, zs_lut_host(), 256);
     CUDA_TRY(cudaMemcpyAsync(d_lut, stage, 256, cudaMemcpyHostToDevice, st));
-    CUDA_TRY(cudaMemsetAsync(counters, 0, ((size_t)max_rounds + 2) * sizeof(unsigned int), st));
+    CUDA_TRY(cudaMemsetAsync(counters, 0, ((size_t)max_rounds + 3) * sizeof(unsigned int), st));
     if (tiled) {
       static int tiled_bps = 0;
       if (!tiled_bps) {
@@ -1052,21 +1282,26 @@ static int skeletonize_impl(tmat_ctx* ctx, const uint8_t* mask, int H, int W, ui
     }
     static int blocks_per_sm = 0;
     if (!blocks_per_sm) {
-      CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, thin_persistent, 256, 0));
+      CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, thin_persistent, THIN_THREADS, 0));
       const char* e = getenv("TMAT_THIN_BLOCKS");
-      const int cap_b = e && atoi(e) > 0 ? atoi(e) : 4;
+      const int cap_b = e && atoi(e) > 0 ? atoi(e) : 1;
       if (blocks_per_sm > cap_b) blocks_per_sm = cap_b;      // every block is a participant of the grid barrier
       if (blocks_per_sm < 1) blocks_per_sm = 1;
     }
     const int64_t words = n / 8;
-    int grid = (int)std::min<int64_t>((int64_t)ctx->sm_count * blocks_per_sm, cdiv64(words, 256));
+    int grid = (int)std::min<int64_t>((int64_t)ctx->sm_count * blocks_per_sm, cdiv64(words, THIN_THREADS));
     if (grid < 1) grid = 1;
     unsigned int* bar = counters + max_rounds + 1;
+    unsigned int* n_active = counters + max_rounds + 2;
+    static const bool full_scan = [] { const char* e = getenv("TMAT_THIN_FULLSCAN"); return e && atoi(e) == 1; }();
+    int* list = nullptr;
+    if (!full_scan) TMAT_TRY(arena_get(ctx, (size_t)words, &list));
+    if (list_out) { *list_out = list; *n_list_out = n_active; }
     int Hh = H, Ww = W, mr = max_rounds;
     const uint8_t* lut_c = d_lut;
     void* args[] = {(void*)&out, (void*)&tmp, (void*)&Hh, (void*)&Ww, (void*)&lut_c, (void*)&counters, (void*)&mr, (void*)&bar,
-                    (void*)&d_iters};
-    CUDA_TRY(cudaLaunchCooperativeKernel((const void*)thin_persistent, dim3(grid), dim3(256), args, 0, st));
+                    (void*)&d_iters, (void*)&list, (void*)&n_active};
+    CUDA_TRY(cudaLaunchCooperativeKernel((const void*)thin_persistent, dim3(grid), dim3(THIN_THREADS), args, 0, st));
     ctx->launches++;
     if (iterations) {
       int* h = (int*)ctx->pinned;
@@ -1127,13 +1362,30 @@ int filter_branch_impl(tmat_ctx* ctx, const uint8_t* mask, int H, int W, int use
   KERNEL_CHECK(ctx);
   root_stats_kernel<<<grid2d(H, W), 256, 0, st>>>(parent, border, H, W, area, hist);
   KERNEL_CHECK(ctx);
-  TMAT_TRY(skeletonize_impl(ctx, m, H, W, sk, nullptr, st));
-  TMAT_TRY(ccl_roots(ctx, sk, H, W, 2, 0, sk_root, st));
-  CUDA_TRY(cudaMemsetAsync(has_fork, 0, (size_t)n, st));
-  fork_kernel<<<grid2d(H, W), 256, 0, st>>>(sk, H, W, sk_root, has_fork);
-  KERNEL_CHECK(ctx);
-  root_kill_kernel<<<grid1d_ept(n), 256, 0, st>>>(sk_root, has_fork, parent, area, hist, n, remove_isolated, kill);
-  KERNEL_CHECK(ctx);
+  int* sk_list = nullptr;
+  unsigned int* sk_n = nullptr;
+  TMAT_TRY(skeletonize_impl(ctx, m, H, W, sk, nullptr, st, &sk_list, &sk_n));
+  static const bool dense_sk = [] { const char* e = getenv("TMAT_SK_DENSE"); return e && atoi(e) == 1; }();
+  if (sk_list && !dense_sk) {
+    // the skeleton lives in the words the thinning kernel listed
+    const int g = ctx->sm_count * 8;
+    CUDA_TRY(cudaMemsetAsync(sk_root, 0xff, (size_t)n * sizeof(int), st));
+    sk_init_list<<<g, 256, 0, st>>>(sk, H, W, sk_list, sk_n, sk_root, has_fork);
+    KERNEL_CHECK(ctx);
+    sk_merge_list<<<g, 256, 0, st>>>(sk, H, W, sk_list, sk_n, sk_root);
+    KERNEL_CHECK(ctx);
+    sk_flatten_fork_list<<<g, 256, 0, st>>>(sk, H, W, sk_list, sk_n, sk_root, has_fork);
+    KERNEL_CHECK(ctx);
+    sk_kill_list<<<g, 256, 0, st>>>(sk, W, sk_list, sk_n, sk_root, has_fork, parent, area, hist, remove_isolated, kill);
+    KERNEL_CHECK(ctx);
+  } else {
+    TMAT_TRY(ccl_roots(ctx, sk, H, W, 2, 0, sk_root, st));
+    CUDA_TRY(cudaMemsetAsync(has_fork, 0, (size_t)n, st));
+    fork_kernel<<<grid2d(H, W), 256, 0, st>>>(sk, H, W, sk_root, has_fork);
+    KERNEL_CHECK(ctx);
+    root_kill_kernel<<<grid1d_ept(n), 256, 0, st>>>(sk_root, has_fork, parent, area, hist, n, remove_isolated, kill);
+    KERNEL_CHECK(ctx);
+  }
   root_apply_kill<<<grid1d_ept(n), 256, 0, st>>>(parent, kill, n, out);
   KERNEL_CHECK(ctx);
   return TMAT_OK;
