@@ -602,7 +602,8 @@ __device__ __forceinline__ void grid_barrier(unsigned int* bar, unsigned int& go
     goal += gridDim.x;
     __threadfence();
     atomicAdd(bar, 1u);
-    while (*(volatile unsigned int*)bar < goal) __nanosleep(40);       // back off: the pollers share one L2 line with the arrivals
+    // release/acquire instead of the fences and polling without back-off all measured the same (0.112-0.114 ms per 2048^2 skeleton)
+    while (*(volatile unsigned int*)bar < goal) __nanosleep(40);
     __threadfence();
   }
   __syncthreads();
