@@ -647,7 +647,9 @@ __device__ __forceinline__ unsigned int thin_pass_words(const uint8_t* __restric
 // (warp-aggregated append; the same scan copies the image into the ping-pong buffer so that both agree everywhere) and
 // every sub-pass walks the list instead of the image -- a vessel mask has a set pixel in 10-30 % of its words, and the
 // full-image sub-passes (read 4 MB, write 4 MB, 14 times) were 130 of the 316 us of filter_branch_seg_mask.
-__device__ __forceinline__ void thin_build_list(const uint8_t* __restrict__ img, uint8_t* __restrict__ tmp, int nw,
+// src != nullptr: the caller's mask (any non-zero byte = set) is binarised on the way in and written to BOTH buffers, which
+// saves the separate binarize pass; src and img may be the same array (every thread reads and writes its own word).
+__device__ __forceinline__ void thin_build_list(const uint8_t* src, uint8_t* img, uint8_t* __restrict__ tmp, int nw,
                                                 int* __restrict__ list, unsigned int* __restrict__ n_active) {
   const int lane = threadIdx.x & 31;
   const int stride = gridDim.x * blockDim.x;
@@ -655,7 +657,14 @@ __device__ __forceinline__ void thin_build_list(const uint8_t* __restrict__ img,
     const int i = i0 + threadIdx.x;
     unsigned long long c = 0ull;
     if (i < nw) {
-      c = reinterpret_cast<const unsigned long long*>(img)[i];
+      if (src) {
+        c = reinterpret_cast<const unsigned long long*>(src)[i];
+        // byte != 0 -> 1: the low seven bits carry into bit 7, OR the byte's own bit 7, keep that bit
+        c = ((((c & 0x7f7f7f7f7f7f7f7full) + 0x7f7f7f7f7f7f7f7full) | c) >> 7) & 0x0101010101010101ull;
+        reinterpret_cast<unsigned long long*>(img)[i] = c;
+      } else {
+        c = reinterpret_cast<const unsigned long long*>(img)[i];
+      }
       reinterpret_cast<unsigned long long*>(tmp)[i] = c;
     }
     const unsigned int nz = __ballot_sync(0xffffffffu, c != 0ull);
@@ -759,10 +768,11 @@ __device__ __forceinline__ unsigned int thin_pass_own(const uint8_t* __restrict_
 // THIN_THREADS threads per CTA, one CTA per SM by default: with the list a sub-pass is a few microseconds of work and the
 // grid barrier (one atomic and one spinning thread per CTA) is what a round costs -- 148 participants instead of 592.
 constexpr int THIN_THREADS = 512;
-__global__ void __launch_bounds__(THIN_THREADS) thin_persistent(uint8_t* __restrict__ img, uint8_t* __restrict__ tmp, int H, int W,
+__global__ void __launch_bounds__(THIN_THREADS) thin_persistent(uint8_t* img, uint8_t* __restrict__ tmp, int H, int W,
                                                        const uint8_t* __restrict__ lut, unsigned int* __restrict__ counters,
                                                        int max_rounds, unsigned int* __restrict__ bar, int* __restrict__ iters_out,
-                                                       int* __restrict__ list, unsigned int* __restrict__ n_active) {
+                                                       int* __restrict__ list, unsigned int* __restrict__ n_active,
+                                                       const uint8_t* src) {
   __shared__ uint8_t s_lut[256];
   __shared__ unsigned int s_removed;
   if (threadIdx.x < 256) s_lut[threadIdx.x] = lut[threadIdx.x];
@@ -773,7 +783,7 @@ __global__ void __launch_bounds__(THIN_THREADS) thin_persistent(uint8_t* __restr
   ThinOwn own;
   const int stride = gridDim.x * blockDim.x;
   if (use_list) {
-    thin_build_list(img, tmp, H * (W >> 3), list, n_active);
+    thin_build_list(src, img, tmp, H * (W >> 3), list, n_active);
     grid_barrier(bar, goal);
     n_list = (int)*(volatile unsigned int*)n_active;
 #pragma unroll
@@ -1236,11 +1246,16 @@ static int skeletonize_impl(tmat_ctx* ctx, const uint8_t* mask, int H, int W, ui
   int64_t n = (int64_t)H * W;
   uint8_t* tmp;
   TMAT_TRY(arena_get(ctx, (size_t)n, &tmp));
-  binarize<<<grid1d_ept(n), 256, 0, st>>>(mask, n, out);
-  KERNEL_CHECK(ctx);
   static const bool no_coop = [] { const char* e = getenv("TMAT_THIN_MULTILAUNCH"); return e && atoi(e) != 0; }();
   static const int variant = [] { const char* e = getenv("TMAT_THIN_VARIANT"); return e ? atoi(e) : 1; }();   // 1: 8-pixel words (default where W % 8 == 0), 2: tiles
+  static const bool full_scan = [] { const char* e = getenv("TMAT_THIN_FULLSCAN"); return e && atoi(e) == 1; }();
   const bool words_ok = (W % 8) == 0 && (reinterpret_cast<uintptr_t>(out) % 8) == 0 && (reinterpret_cast<uintptr_t>(tmp) % 8) == 0;
+  // the list-building scan of the word kernel binarises the mask itself when it can read it in 8-byte words
+  const bool fuse_bin = !no_coop && variant != 2 && words_ok && !full_scan && (reinterpret_cast<uintptr_t>(mask) % 8) == 0;
+  if (!fuse_bin) {
+    binarize<<<grid1d_ept(n), 256, 0, st>>>(mask, n, out);
+    KERNEL_CHECK(ctx);
+  }
   if (!no_coop && (variant == 2 || words_ok)) {
     const bool tiled = variant == 2 || !words_ok;
     int max_rounds = std::min(H, W) / 2 + 2;               // a round that removes something peels one layer
@@ -1294,14 +1309,14 @@ static int skeletonize_impl(tmat_ctx* ctx, const uint8_t* mask, int H, int W, ui
     if (grid < 1) grid = 1;
     unsigned int* bar = counters + max_rounds + 1;
     unsigned int* n_active = counters + max_rounds + 2;
-    static const bool full_scan = [] { const char* e = getenv("TMAT_THIN_FULLSCAN"); return e && atoi(e) == 1; }();
     int* list = nullptr;
     if (!full_scan) TMAT_TRY(arena_get(ctx, (size_t)words, &list));
     if (list_out) { *list_out = list; *n_list_out = n_active; }
     int Hh = H, Ww = W, mr = max_rounds;
     const uint8_t* lut_c = d_lut;
+    const uint8_t* src = fuse_bin ? mask : nullptr;
     void* args[] = {(void*)&out, (void*)&tmp, (void*)&Hh, (void*)&Ww, (void*)&lut_c, (void*)&counters, (void*)&mr, (void*)&bar,
-                    (void*)&d_iters, (void*)&list, (void*)&n_active};
+                    (void*)&d_iters, (void*)&list, (void*)&n_active, (void*)&src};
     CUDA_TRY(cudaLaunchCooperativeKernel((const void*)thin_persistent, dim3(grid), dim3(THIN_THREADS), args, 0, st));
     ctx->launches++;
     if (iterations) {
