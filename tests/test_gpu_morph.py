@@ -83,6 +83,33 @@ def test_edge_cases_empty_full_and_errors():
         T.remove_small_islands(np.ones((8, 8), np.uint8))     # the reference rejects an all-ones mask too
 
 
+@pytest.mark.parametrize("h,w", [(50, 8), (70, 264), (37, 256), (130, 520), (1, 16), (9, 1032), (64, 72)])
+def test_word_lane_erosion_and_median_vs_oracle(h, w):
+    """Widths on the 8-pixel grid take the 8-pixels-per-lane kernels (a warp spans 256 columns): one word, one span plus
+    one word, exact spans, several spans, a single row -- random masks dense enough for the erosion to keep something."""
+    from tmat_b200 import transforms as T
+    rng = np.random.default_rng(h * 1009 + w)
+    for dens in (0.5, 0.9, 0.985):
+        m = rng.random((h, w)) < dens
+        assert np.array_equal(T.median_filter(m, T.disk(2)), om.median_bool(m, om.disk(2))), dens
+        assert np.array_equal(T.binary_erosion(m, T.disk(5)), om.binary_erosion(m, om.disk(5))), dens
+    m = np.ones((h, w), bool)
+    assert T.binary_erosion(m, T.disk(5)).all() and T.median_filter(m, T.disk(2)).all()
+
+
+@pytest.mark.parametrize("shape", [(256, 512), (120, 264), (64, 1032)])
+def test_auto_threshold_well_word_path_shapes(shape):
+    """auto_threshold_well on widths that are multiples of 8: the fused Gaussian passes feed the word-lane erosion with
+    the Otsu threshold folded into its load."""
+    from tmat_b200 import well_mask_generation as W
+    for dtype, invert in ((np.uint16, False), (np.uint8, True)):
+        img = helpers.synth_well(*shape, 23, dtype, invert)
+        mask, info = W.auto_threshold_well(img, return_info=True)
+        ref, st = ow.auto_threshold_well(img, return_stages=True)
+        assert info["invert"] == st["invert"] and info["otsu"] == st["otsu"]
+        assert np.array_equal(mask, ref)
+
+
 @pytest.mark.parametrize("dtype,invert", [(np.uint16, False), (np.uint16, True), (np.uint8, False), (np.float32, True),
                                           (np.float32, False)])
 def test_auto_threshold_well_vs_oracle(dtype, invert):

@@ -181,6 +181,109 @@ __global__ void __launch_bounds__(128) gauss_axis1_fixed(const T* __restrict__ i
   }
 }
 
+// Both passes in ONE kernel for sigma = 1 on integer images: a CTA of 256 threads takes a 56 x 32-pixel tile, 64 columns
+// (tile + 4 halo columns each side, indices clamped = mode 'nearest') x 4 groups of 8 rows run the vertical pass from
+// registers into a 32 x 64 float64 tile in shared memory, then every thread runs the horizontal pass for 7 consecutive
+// outputs of one row.  The float64 intermediate (33.6 MB at 2048^2, written and re-read by the two-pass version) never
+// leaves the SM.  Same operations in the same order per output as the two passes: bit-identical.
+// MODE 0: write the blurred image (+ min / max keys when mm != nullptr); MODE 1: min / max only (nothing written);
+// MODE 2: rescale_intensity -> uint8 + the five histograms straight from the recomputed blur (needs the keys).
+constexpr int G2_TW = 56, G2_TH = 32, G2_PITCH = 66;
+struct G2Corners { int xs, xe, ys, ye; };
+template <typename TIn, int MODE>
+__global__ void __launch_bounds__(256) gauss2d_sigma1(const TIn* __restrict__ in, int H, int W, GaussW g, double int_scale,
+                                                      double* __restrict__ out, unsigned long long* __restrict__ mm,
+                                                      G2Corners cn, uint8_t* __restrict__ u8, unsigned int* __restrict__ hist) {
+  constexpr int R = 4;
+  __shared__ double V[G2_TH * G2_PITCH];
+  __shared__ unsigned int sh[MODE == 2 ? 5 * 256 : 1];
+  __shared__ unsigned long long s_lo[8], s_hi[8];
+  const int x0 = blockIdx.x * G2_TW, y0 = blockIdx.y * G2_TH;
+  if (MODE == 2) {
+    for (int i = threadIdx.x; i < 5 * 256; i += 256) sh[i] = 0;
+  }
+  {
+    // vertical pass: column c of the 64, rows 8 grp .. 8 grp + 7 of the tile
+    const int c = threadIdx.x & 63, grp = threadIdx.x >> 6;
+    const int xc = min(max(x0 - R + c, 0), W - 1);
+    double v[8 + 2 * R];
+#pragma unroll
+    for (int i = 0; i < 8 + 2 * R; ++i) {
+      const int yy = min(max(y0 + 8 * grp - R + i, 0), H - 1);
+      v[i] = load_as_f64<TIn>(in, (int64_t)yy * W + xc, int_scale);
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      double tmp = __dmul_rn(v[k + R], g.w[0]);
+#pragma unroll
+      for (int j = R; j >= 1; --j) tmp = __dadd_rn(tmp, __dmul_rn(__dadd_rn(v[k + R - j], v[k + R + j]), g.w[j]));
+      V[(8 * grp + k) * G2_PITCH + c] = tmp;
+    }
+  }
+  __syncthreads();
+  unsigned long long lo = ~0ull, hi = 0ull;
+  double klo = 0.0, khi = 0.0;
+  bool flat = false;
+  if (MODE == 2) { klo = f64_unkey(mm[0]); khi = f64_unkey(mm[1]); flat = (klo == khi); }
+  {
+    // horizontal pass: row r of the tile, 7 consecutive outputs
+    const int r = threadIdx.x >> 3, q = threadIdx.x & 7;
+    const int y = y0 + r;
+    const double* vr = V + r * G2_PITCH + 7 * q;          // vr[i] = column x0 + 7 q - R + i
+    double v[7 + 2 * R];
+#pragma unroll
+    for (int i = 0; i < 7 + 2 * R; ++i) v[i] = vr[i];
+    const bool top = y < cn.xs, bot = y >= cn.xe;
+#pragma unroll
+    for (int k = 0; k < 7; ++k) {
+      const int x = x0 + 7 * q + k;
+      int qv = -1;
+      if (y < H && x < W) {
+        double tmp = __dmul_rn(v[k + R], g.w[0]);
+#pragma unroll
+        for (int j = R; j >= 1; --j) tmp = __dadd_rn(tmp, __dmul_rn(__dadd_rn(v[k + R - j], v[k + R + j]), g.w[j]));
+        if (MODE == 0) out[(int64_t)y * W + x] = tmp;
+        if (MODE != 2) {
+          const unsigned long long key = f64_key(tmp);
+          lo = min(lo, key); hi = max(hi, key);
+        } else {
+          double d = tmp;
+          if (!flat) d = __ddiv_rn(__dsub_rn(d, klo), __dsub_rn(khi, klo));
+          const double yv = __dadd_rn(__dmul_rn(d, 255.0), 0.0);
+          const uint8_t qq = (uint8_t)(long long)yv;
+          u8[(int64_t)y * W + x] = qq;
+          qv = qq;
+          if (top && x < cn.ys) atomicAdd(&sh[0 * 256 + qv], 1u);
+          if (top && x >= cn.ye) atomicAdd(&sh[1 * 256 + qv], 1u);
+          if (bot && x < cn.ys) atomicAdd(&sh[2 * 256 + qv], 1u);
+          if (bot && x >= cn.ye) atomicAdd(&sh[3 * 256 + qv], 1u);
+        }
+      }
+      if (MODE == 2) {
+        const unsigned int peers = __match_any_sync(0xffffffffu, qv);
+        if (qv >= 0 && (threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(&sh[4 * 256 + qv], (unsigned int)__popc(peers));
+      }
+    }
+  }
+  if (MODE == 2) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < 5 * 256; i += 256)
+      if (sh[i]) atomicAdd(&hist[i], sh[i]);
+    return;
+  }
+  if (mm == nullptr) return;
+  for (int o = 16; o > 0; o >>= 1) {
+    lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+    hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+  }
+  if ((threadIdx.x & 31) == 0) { s_lo[threadIdx.x >> 5] = lo; s_hi[threadIdx.x >> 5] = hi; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < 8; ++w) { lo = min(lo, s_lo[w]); hi = max(hi, s_hi[w]); }
+    if (lo != ~0ull) { atomicMin(mm, lo); atomicMax(mm + 1, hi); }
+  }
+}
+
 // min / max keys and the 5 x 256 histogram counters of auto_threshold_well, initialised in one launch
 __global__ void __launch_bounds__(256) minmax64_hist_init(unsigned long long* k, unsigned int* hist) {
   if (threadIdx.x == 0) { k[0] = ~0ull; k[1] = 0ull; }
@@ -369,6 +472,15 @@ static int make_gauss(double sigma, GaussW* g) {
   return TMAT_OK;
 }
 
+// which sigma = 1 implementation runs (measurement switches): 0 fused 2-D kernel, 1 the two fixed-radius passes, 2 generic
+static int gauss_sigma1_mode() {
+  static const int mode = [] {
+    const char* a = getenv("TMAT_GAUSS_GENERIC");
+    const char* b = getenv("TMAT_GAUSS_TWO_PASS");
+    return (a && atoi(a) == 1) ? 2 : ((b && atoi(b) == 1) ? 1 : 0);
+  }();
+  return mode;
+}
 // blur: float64 (H,W) for integer input, float32 for float32 input
 static int gaussian_impl(tmat_ctx* ctx, const void* img, int dtype, int H, int W, double sigma, void* out,
                          cudaStream_t st, unsigned long long* mm = nullptr) {
@@ -380,7 +492,15 @@ static int gaussian_impl(tmat_ctx* ctx, const void* img, int dtype, int H, int W
     double* tmp;
     TMAT_TRY(arena_get(ctx, n, &tmp));
     // skimage img_as_float: np.multiply(image, 1. / imax, dtype=float64)
-    static const bool generic = [] { const char* v = getenv("TMAT_GAUSS_GENERIC"); return v && atoi(v) == 1; }();
+    const bool generic = gauss_sigma1_mode() == 2, two_pass = gauss_sigma1_mode() == 1;
+    if (g.R == 4 && !generic && !two_pass) {
+      const dim3 g2(cdiv(W, G2_TW), cdiv(H, G2_TH));
+      const G2Corners none{0, 0, 0, 0};
+      if (dtype == TMAT_U8) gauss2d_sigma1<uint8_t, 0><<<g2, 256, 0, st>>>((const uint8_t*)img, H, W, g, 1.0 / 255.0, (double*)out, mm, none, nullptr, nullptr);
+      else gauss2d_sigma1<uint16_t, 0><<<g2, 256, 0, st>>>((const uint16_t*)img, H, W, g, 1.0 / 65535.0, (double*)out, mm, none, nullptr, nullptr);
+      KERNEL_CHECK(ctx);
+      return TMAT_OK;
+    }
     if (g.R == 4 && !generic) {
       const dim3 gf0(cdiv(W, 256), cdiv(H, GROWS)), gf1(cdiv(W, 128 * GX), cdiv(H, GY));
       if (dtype == TMAT_U8) gauss_axis0_fixed<uint8_t, double, 4><<<gf0, 256, 0, st>>>((const uint8_t*)img, H, W, g, 1.0 / 255.0, tmp);
@@ -469,8 +589,6 @@ static int auto_threshold_impl(tmat_ctx* ctx, const void* img, int dtype, int H,
                "class weights of threshold_otsu stop being exact integers)");
   size_t n = (size_t)H * W;
   const bool f32 = (dtype == TMAT_F32);
-  void* blur;
-  TMAT_TRY(arena_alloc(ctx, n * (f32 ? 4 : 8), &blur));
   unsigned long long* keys;
   unsigned int* hist;
   uint8_t* u8;
@@ -479,13 +597,35 @@ static int auto_threshold_impl(tmat_ctx* ctx, const void* img, int dtype, int H,
   TMAT_TRY(arena_get(ctx, n, &u8));
   minmax64_hist_init<<<1, 256, 0, st>>>(keys, hist);
   KERNEL_CHECK(ctx);
-  TMAT_TRY(gaussian_impl(ctx, img, dtype, H, W, 1.0, blur, st, keys));     // min / max of the result reduced in its last pass
-  const int rows_per_block = cdiv(H, ctx->sm_count * 8);        // rescale_u8_hist walks whole rows: the same number per block
-  int blocks = cdiv(H, rows_per_block);
   int xs = (int)(H * 0.05), xe = (int)(H * 0.95), ys = (int)(W * 0.05), ye = (int)(W * 0.95);
-  if (f32) rescale_u8_hist<float><<<blocks, 256, 0, st>>>((const float*)blur, H, W, keys, xs, xe, ys, ye, u8, hist);
-  else rescale_u8_hist<double><<<blocks, 256, 0, st>>>((const double*)blur, H, W, keys, xs, xe, ys, ye, u8, hist);
-  KERNEL_CHECK(ctx);
+  if ((dtype == TMAT_U8 || dtype == TMAT_U16) && gauss_sigma1_mode() == 0) {
+    // integer images: the blurred float64 image is never materialised -- one fused-Gaussian pass reduces its exact
+    // min / max, a second one recomputes it and quantises straight to uint8 + histograms (2 x 8.4 MB read and 4.2 MB
+    // written per 2048^2 uint16 image instead of 8.4 + 3 x 33.6 MB read and 2 x 33.6 + 4.2 MB written)
+    GaussW g;
+    TMAT_TRY(make_gauss(1.0, &g));
+    const dim3 g2(cdiv(W, G2_TW), cdiv(H, G2_TH));
+    const G2Corners none{0, 0, 0, 0}, cn{xs, xe, ys, ye};
+    if (dtype == TMAT_U8) {
+      gauss2d_sigma1<uint8_t, 1><<<g2, 256, 0, st>>>((const uint8_t*)img, H, W, g, 1.0 / 255.0, nullptr, keys, none, nullptr, nullptr);
+      KERNEL_CHECK(ctx);
+      gauss2d_sigma1<uint8_t, 2><<<g2, 256, 0, st>>>((const uint8_t*)img, H, W, g, 1.0 / 255.0, nullptr, keys, cn, u8, hist);
+    } else {
+      gauss2d_sigma1<uint16_t, 1><<<g2, 256, 0, st>>>((const uint16_t*)img, H, W, g, 1.0 / 65535.0, nullptr, keys, none, nullptr, nullptr);
+      KERNEL_CHECK(ctx);
+      gauss2d_sigma1<uint16_t, 2><<<g2, 256, 0, st>>>((const uint16_t*)img, H, W, g, 1.0 / 65535.0, nullptr, keys, cn, u8, hist);
+    }
+    KERNEL_CHECK(ctx);
+  } else {
+    void* blur;
+    TMAT_TRY(arena_alloc(ctx, n * (f32 ? 4 : 8), &blur));
+    TMAT_TRY(gaussian_impl(ctx, img, dtype, H, W, 1.0, blur, st, keys));     // min / max of the result reduced in its last pass
+    const int rows_per_block = cdiv(H, ctx->sm_count * 8);        // rescale_u8_hist walks whole rows: the same number per block
+    int blocks = cdiv(H, rows_per_block);
+    if (f32) rescale_u8_hist<float><<<blocks, 256, 0, st>>>((const float*)blur, H, W, keys, xs, xe, ys, ye, u8, hist);
+    else rescale_u8_hist<double><<<blocks, 256, 0, st>>>((const double*)blur, H, W, keys, xs, xe, ys, ye, u8, hist);
+    KERNEL_CHECK(ctx);
+  }
   int* params;
   TMAT_TRY(arena_get(ctx, 4, &params));
   otsu_decide_kernel<<<1, 256, 0, st>>>(hist, params);

@@ -176,6 +176,134 @@ __global__ void __launch_bounds__(128) erode_disk_bits(const uint8_t* __restrict
   }
 }
 
+// ---- eight pixels per lane: erosion and median for widths on the 8-pixel grid ---------------------------------------
+// The ballot kernels above pack 32 pixels per WARP instruction; here a lane loads one 8-byte word, packs its pixels into
+// 8 bits (SIMD byte compare + multiply), gets its neighbours' bits by two shuffles and runs the same shift / AND / adder
+// logic on its own 24-bit window -- 256 pixels per warp instruction.  A lane outside the row supplies the border
+// (erosion: border_value; median: the row's last pixel replicated = mode 'nearest'), lane 0 / lane 31 load the word
+// beyond the warp's 256-column span themselves.  Output bits are spread back to 0/1 bytes and stored as one word.
+__device__ __forceinline__ uint32_t pack4_ge(uint32_t w, uint32_t vx4, uint32_t thr4) {
+  const uint32_t m = __vcmpgeu4(w ^ vx4, thr4) & 0x01010101u;              // byte k -> bit 8k
+  return ((m * 0x01020408u) >> 24) & 0xfu;                                  // -> bits 0..3
+}
+__device__ __forceinline__ uint32_t pack8_ge(unsigned long long w, uint32_t vx4, uint32_t thr4) {
+  return pack4_ge((uint32_t)w, vx4, thr4) | (pack4_ge((uint32_t)(w >> 32), vx4, thr4) << 4);
+}
+__device__ __forceinline__ unsigned long long unpack8(uint32_t bits) {
+  unsigned long long x = ((unsigned long long)(bits & 0xffu) * 0x0101010101010101ull) & 0x8040201008040201ull;   // bit k of byte k
+  return ((x + 0x7f7f7f7f7f7f7f7full) >> 7) & 0x0101010101010101ull;
+}
+constexpr int EW_SEG = 16;
+template <int R>
+__global__ void __launch_bounds__(128) erode_disk_words(const uint8_t* __restrict__ in, int H, int W, int border_value,
+                                                        const int* __restrict__ thr_params, uint8_t* __restrict__ out) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int wpr = W >> 3;
+  const int xw = blockIdx.x * 32 + lane;                      // this lane's word in the row
+  const int y0 = (blockIdx.y * 4 + warp) * EW_SEG;
+  if (y0 >= H) return;
+  const int y1 = min(y0 + EW_SEG, H);
+  const uint32_t thr4 = (uint32_t)(thr_params ? thr_params[1] : 1) * 0x01010101u;
+  const uint32_t vx4 = (thr_params && thr_params[0]) ? 0xffffffffu : 0u;
+  const uint32_t bord8 = border_value ? 0xffu : 0u;
+  const bool in_row = xw < wpr;
+  // the word beyond the warp's span that this lane fetches (lane 0: left, lane 31: right), -1: none / outside
+  const int xe = lane == 0 ? xw - 1 : (lane == 31 ? xw + 1 : -1);
+  const bool e_in = xe >= 0 && xe < wpr;
+  const int xw_c = min(xw, wpr - 1), xe_c = min(max(xe, 0), wpr - 1);
+  unsigned int acc[2 * R + 1];
+#pragma unroll
+  for (int k = 0; k <= 2 * R; ++k) acc[k] = 0xffu;
+  for (int base = y0 - R; base < y1 + R; base += 2 * R + 1) {
+    unsigned long long wa[2 * R + 1], we[2 * R + 1];
+#pragma unroll
+    for (int s = 0; s <= 2 * R; ++s) {
+      const int yc = min(max(base + s, 0), H - 1);
+      const unsigned long long* row = reinterpret_cast<const unsigned long long*>(in + (int64_t)yc * W);
+      wa[s] = row[xw_c];
+      we[s] = row[xe_c];
+    }
+#pragma unroll
+    for (int s = 0; s <= 2 * R; ++s) {
+      const int yi = base + s;
+      const bool row_in = yi >= 0 && yi < H;
+      const uint32_t own = (row_in && in_row) ? pack8_ge(wa[s], vx4, thr4) : bord8;
+      const uint32_t ext = (row_in && e_in) ? pack8_ge(we[s], vx4, thr4) : bord8;
+      uint32_t l = __shfl_up_sync(0xffffffffu, own, 1), r = __shfl_down_sync(0xffffffffu, own, 1);
+      if (lane == 0) l = ext;
+      if (lane == 31) r = ext;
+      const uint32_t w = l | (own << 8) | (r << 16);          // bit j = pixel 8 xw - 8 + j
+      unsigned int eh[R + 1];
+      eh[0] = w >> 8;
+#pragma unroll
+      for (int h = 1; h <= R; ++h) eh[h] = eh[h - 1] & (w >> (8 - h)) & (w >> (8 + h));
+#pragma unroll
+      for (int k = 0; k <= 2 * R; ++k) acc[(s - (k - R) + 2 * R + 1) % (2 * R + 1)] &= eh[disk_half_width(R, k - R)];
+      const int yo = yi - R;
+      constexpr int M = 2 * R + 1;
+      const int slot = (s - R + M) % M;
+      if (yo >= y0 && yo < y1 && in_row)
+        reinterpret_cast<unsigned long long*>(out + (int64_t)yo * W)[xw] = unpack8(acc[slot]);
+      acc[slot] = 0xffu;
+    }
+  }
+}
+constexpr int MW_SEG = 16;
+__global__ void __launch_bounds__(128) median_disk2_words(const uint8_t* __restrict__ in, int H, int W, uint8_t* __restrict__ out) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int wpr = W >> 3;
+  const int xw = blockIdx.x * 32 + lane;
+  const int y0 = (blockIdx.y * 4 + warp) * MW_SEG;
+  if (y0 >= H) return;
+  const int y1 = min(y0 + MW_SEG, H);
+  const bool in_row = xw < wpr;
+  const int xe = lane == 0 ? xw - 1 : (lane == 31 ? xw + 1 : -1);
+  const int xw_c = min(xw, wpr - 1), xe_c = min(max(xe, 0), wpr - 1);
+  unsigned int s1[5], a0[5], a1[5], t0[5], u1[5], u2[5];
+  for (int base = y0 - 2; base < y1 + 2; base += 5) {
+    unsigned long long wa[5], we[5];
+#pragma unroll
+    for (int s = 0; s < 5; ++s) {
+      const int yc = min(max(base + s, 0), H - 1);
+      const unsigned long long* row = reinterpret_cast<const unsigned long long*>(in + (int64_t)yc * W);
+      wa[s] = row[xw_c];
+      we[s] = row[xe_c];
+    }
+#pragma unroll
+    for (int s = 0; s < 5; ++s) {
+      const int yi = base + s;
+      uint32_t own = pack8_ge(wa[s], 0u, 0x01010101u);
+      if (!in_row) own = (own & 0x80u) ? 0xffu : 0u;           // beyond the row: its last pixel, replicated
+      uint32_t ext = pack8_ge(we[s], 0u, 0x01010101u);
+      if (xe < 0) ext = (ext & 1u) ? 0xffu : 0u;               // left of column 0: the first pixel, replicated
+      if (xe >= wpr) ext = (ext & 0x80u) ? 0xffu : 0u;
+      uint32_t l = __shfl_up_sync(0xffffffffu, own, 1), r = __shfl_down_sync(0xffffffffu, own, 1);
+      if (lane == 0) l = ext;
+      if (lane == 31) r = ext;
+      const uint32_t w = l | (own << 8) | (r << 16);          // bit j = pixel 8 xw - 8 + j (clamped)
+      const uint32_t wm2 = w >> 6, wm1 = w >> 7, w0 = w >> 8, wp1 = w >> 9, wp2 = w >> 10;   // bit i = pixel 8 xw + i + d
+      s1[s] = w0;
+      a0[s] = xor3(wm1, w0, wp1);
+      a1[s] = maj3(wm1, w0, wp1);
+      t0[s] = xor3(a0[s], wm2, wp2);
+      const unsigned int c1 = maj3(a0[s], wm2, wp2);
+      u1[s] = a1[s] ^ c1;
+      u2[s] = a1[s] & c1;
+      const int yo = yi - 2;
+      if (yo >= y0 && yo < y1 && in_row) {
+        constexpr int M = 5;
+        const int sm2 = (s + 1) % M, sm1 = (s + 2) % M, sc = (s + 3) % M, sp1 = (s + 4) % M, sp2 = s;
+        const unsigned int x0b = xor3(t0[sc], a0[sm1], a0[sp1]), cx = maj3(t0[sc], a0[sm1], a0[sp1]);
+        const unsigned int r0 = xor3(x0b, s1[sm2], s1[sp2]), cy = maj3(x0b, s1[sm2], s1[sp2]);
+        const unsigned int x1b = xor3(u1[sc], a1[sm1], a1[sp1]), dx = maj3(u1[sc], a1[sm1], a1[sp1]);
+        const unsigned int r1 = xor3(x1b, cx, cy), dy = maj3(x1b, cx, cy);
+        const unsigned int r2 = xor3(u2[sc], dx, dy), r3 = maj3(u2[sc], dx, dy);
+        reinterpret_cast<unsigned long long*>(out + (int64_t)yo * W)[xw] = unpack8(r3 | (r2 & r1 & r0));
+      }
+    }
+  }
+}
+
 // ---- rank filter of a boolean image under an arbitrary footprint ------------------------------------------
 // offs: (dy, dx) of the nfp footprint members relative to the centre.  clamp != 0: indices clamped to the image
 // (ndimage mode 'nearest', the median); else pixels outside count as border_value (binary_erosion).
@@ -1141,6 +1269,13 @@ int erode_disk_thr(tmat_ctx* ctx, const uint8_t* in, int H, int W, int r, int bo
   // rows per warp: more, shorter segments hide the per-row dependency chain (ballot -> shifts -> accumulators) better
   // than the halo rows cost (measured at r = 5 on 2048^2, TMAT_ERODE_SEG)
   static const int seg = [] { const char* v = getenv("TMAT_ERODE_SEG"); int s = v ? atoi(v) : 32; return s == 16 || s == 32 ? s : 64; }();
+  static const bool ballot_only = [] { const char* v = getenv("TMAT_MORPH_BALLOT"); return v && atoi(v) == 1; }();
+  const bool words_ok = !ballot_only && (W % 8) == 0 && (reinterpret_cast<uintptr_t>(in) % 8) == 0 && (reinterpret_cast<uintptr_t>(out) % 8) == 0;
+  if (r == 5 && words_ok) {
+    erode_disk_words<5><<<dim3(cdiv(W / 8, 32), cdiv(cdiv(H, EW_SEG), 4)), 128, 0, st>>>(in, H, W, border_value, thr_params_dev, out);
+    KERNEL_CHECK(ctx);
+    return TMAT_OK;
+  }
   if (r == 5 && seg != ER_SEG) {
     dim3 g2(cdiv(W, 32), cdiv(cdiv(H, seg), 4));
     if (seg == 32) erode_disk_bits<5, 32><<<g2, 128, 0, st>>>(in, H, W, border_value, thr_params_dev, out);
@@ -1163,7 +1298,10 @@ int erode_disk(tmat_ctx* ctx, const uint8_t* in, int H, int W, int r, int border
 
 int median_disk2(tmat_ctx* ctx, const uint8_t* in, int H, int W, uint8_t* out, cudaStream_t st) {
   static const bool per_pixel = [] { const char* v = getenv("TMAT_MEDIAN_PER_PIXEL"); return v && atoi(v) == 1; }();
+  static const bool ballot_only = [] { const char* v = getenv("TMAT_MORPH_BALLOT"); return v && atoi(v) == 1; }();
+  const bool words_ok = !ballot_only && (W % 8) == 0 && (reinterpret_cast<uintptr_t>(in) % 8) == 0 && (reinterpret_cast<uintptr_t>(out) % 8) == 0;
   if (per_pixel) median_disk2_kernel<<<grid2d(H, W), 256, 0, st>>>(in, H, W, out);
+  else if (words_ok) median_disk2_words<<<dim3(cdiv(W / 8, 32), cdiv(cdiv(H, MW_SEG), 4)), 128, 0, st>>>(in, H, W, out);
   else median_disk2_bits<<<dim3(cdiv(W, 32), cdiv(cdiv(H, MED_SEG), 4)), 128, 0, st>>>(in, H, W, out);
   KERNEL_CHECK(ctx);
   return TMAT_OK;
