@@ -70,9 +70,13 @@ ncu)
 noalloc)   # the allocation-free entry point: alone in a fresh process, then again after the whole suite (verify)
   timeout 600 python -m pytest tests/test_zz_no_alloc.py -m gpu -x -q 2>&1 | tail -8 | cut -c1-300
   ;;
-ncu4)      # ncu --set full of the stage 3/4 kernels over one C3 image -> gpurun_out/ncu_stage4.ncu-rep; ncu4 [launch-skip]
-  timeout 900 ncu --launch-skip ${1:-0} --set full --import-source on --clock-control none -k regex:"thin_|ccl_|erode_disk|root_|gauss_|otsu_|median_|footprint_|border_|rescale_u8|minmax64" --launch-count 36 -o gpurun_out/ncu_stage4 -f python scripts/bench_stages.py --config C3 --no-cpu --iters 1 > gpurun_out/ncu_stage4.log 2>&1
-  echo "ncu stage4 exit $?"; tail -3 gpurun_out/ncu_stage4.log
+ncu4)      # ncu --set full of the stage 3/4 kernels of one C3 image (warm caches): the auto_threshold_well sequence and
+           # the last filter_branch_seg_mask sequence -> gpurun_out/ncu_stage3.ncu-rep, ncu_stage4.ncu-rep
+  RX='regex:thin_|ccl_|erode_disk|root_|gauss|otsu_|median_|footprint_|border_|rescale_u8|minmax64|sk_'
+  timeout 600 ncu --cache-control none --set full --import-source on --clock-control none -k "$RX" --launch-skip ${1:-25} --launch-count 5 -o gpurun_out/ncu_stage3 -f python scripts/bench_stages.py --config C3 --no-cpu --iters 2 > gpurun_out/ncu_stage3.log 2>&1
+  echo "ncu stage3 exit $?"
+  timeout 600 ncu --cache-control none --set full --import-source on --clock-control none -k "$RX" --launch-skip ${2:-103} --launch-count 12 -o gpurun_out/ncu_stage4 -f python scripts/bench_stages.py --config C3 --no-cpu --iters 2 > gpurun_out/ncu_stage4.log 2>&1
+  echo "ncu stage4 exit $?"
   ;;
 multi)     # bench.py on N GPUs exactly as the driver launches it (gpurun --gpus N): multi N
   N=${1:-2}
