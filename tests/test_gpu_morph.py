@@ -29,7 +29,8 @@ def test_filter_branch_seg_mask_golden(golden):
         assert np.array_equal(T.regionprops_image(m, "area").astype(np.float32), g[f"{name}_area_image_composition"])
 
 
-@pytest.mark.parametrize("h,w,seed", [(64, 64, 1), (97, 131, 2), (300, 340, 3), (33, 500, 4), (1, 40, 5), (40, 1, 6)])
+@pytest.mark.parametrize("h,w,seed", [(64, 64, 1), (97, 131, 2), (300, 340, 3), (33, 500, 4), (1, 40, 5), (40, 1, 6),
+                                      (128, 264, 7), (200, 1032, 8)])
 def test_morphology_primitives_vs_oracle(h, w, seed):
     from tmat_b200 import transforms as T
     m = helpers.synth_mask(h, w, seed, density=0.15)
@@ -95,6 +96,19 @@ def test_word_lane_erosion_and_median_vs_oracle(h, w):
         assert np.array_equal(T.binary_erosion(m, T.disk(5)), om.binary_erosion(m, om.disk(5))), dens
     m = np.ones((h, w), bool)
     assert T.binary_erosion(m, T.disk(5)).all() and T.median_filter(m, T.disk(2)).all()
+
+
+@pytest.mark.parametrize("w", [264, 100])
+def test_erosion_border_value_zero(w):
+    """tmat_erode_disk with border_value = 0 (outside the image counts as background) on both kernel families."""
+    from scipy import ndimage as ndi
+    from tmat_b200 import _ffi
+    rng = np.random.default_rng(w)
+    m = (rng.random((90, w)) < 0.97).astype(np.uint8)
+    out = np.empty_like(m)
+    for r in (5, 2):
+        _ffi.check(_ffi.lib().tmat_erode_disk_host(_ffi.default_context().handle, _ffi.ptr(m), 90, w, r, 0, _ffi.ptr(out)))
+        assert np.array_equal(out != 0, ndi.binary_erosion(m != 0, structure=om.disk(r), border_value=0)), r
 
 
 @pytest.mark.parametrize("shape", [(256, 512), (120, 264), (64, 1032)])
