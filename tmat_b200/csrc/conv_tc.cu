@@ -317,6 +317,7 @@ static int launch_tc(tmat_ctx* ctx, const CUtensorMap& a0, const CUtensorMap& a1
 }
 
 int conv_run_tc(tmat_ctx* ctx, const ConvOp& op, cudaStream_t st) {
+  if (conv_head_taps_supported(op)) return conv_run_head_taps(ctx, op, st);
   if (conv_halo_supported(op)) return conv_run_halo(ctx, op, conv_halo_mode(), st);
   TMAT_REQUIRE(conv_tc_supported(op), "conv_tc(%s): shape not supported by the tcgen05 path", op.name);
   TcParams p;

@@ -38,6 +38,7 @@ struct tmat_unet {
   // up[i>0]: ct1 parity-packed [4 f][gtaps cin], ct2 = [f][9 f], z = [f][cin] (residual at low resolution)
   struct Up { int cin, f; bf16 *ct1, *ct2, *z; float *sh1, *sh2, *shz; int ngroups, gtaps; } up[4];
   bf16* head_w = nullptr; float* head_shift = nullptr;
+  bf16* head_w2 = nullptr;        // [16 = (parity, 2x2 low-res tap)][C] for the taps-in-N head (conv_head.cu)
   std::map<std::string, Tap> taps;
   bool keep_taps = false;
 };
@@ -284,6 +285,18 @@ int pack_weights(tmat_unet* net, const WeightSet& ws) {
       }
     TMAT_TRY(upload_bf16(net, w, &net->head_w));
     TMAT_TRY(upload(net, sh, &net->head_shift));
+    // the same sums arranged as 16 (parity, tap) rows of cin weights: tap (a, b) of parity (py, px) is the low-res pixel at
+    // offset (a + py - 1, b + px - 1) and collects the fine taps that fall on it
+    std::vector<float> w2((size_t)16 * cin, 0.f);
+    for (int py = 0; py < 2; ++py)
+      for (int px = 0; px < 2; ++px)
+        for (int ky = 0; ky < 3; ++ky)
+          for (int kx = 0; kx < 3; ++kx) {
+            const int a = lowtap(py, ky) - (py - 1), bb = lowtap(px, kx) - (px - 1);       // 0 or 1
+            const int n = (py * 2 + px) * 4 + a * 2 + bb;
+            for (int c = 0; c < cin; ++c) w2[(size_t)n * cin + c] += k[(size_t)(ky * 3 + kx) * cin + c];
+          }
+    TMAT_TRY(upload_bf16(net, w2, &net->head_w2));
   }
   return TMAT_OK;
 }
@@ -450,7 +463,7 @@ int unet_forward(tmat_ctx* ctx, tmat_unet* net, const StemSrc& src, int B, float
   }
   ConvOp oh;
   oh.name = "head"; oh.a0 = P; oh.a0_C = fc[0]; oh.B = B; oh.H = S; oh.W = S; set_taps3x3(oh);
-  oh.wmat = net->head_w; oh.K = 9 * fc[0]; oh.shift = net->head_shift; oh.Cout = 4; oh.Npad = 16; oh.epi = EPI_HEAD;
+  oh.wmat = net->head_w; oh.wmat2 = net->head_w2; oh.K = 9 * fc[0]; oh.shift = net->head_shift; oh.Cout = 4; oh.Npad = 16; oh.epi = EPI_HEAD;
   oh.out_f32 = probs; oh.logits = logits;
   TMAT_TRY(run_op(ctx, net, oh, st));
   record(net, "probs", probs, B, ws, ws, 1, 1);

@@ -55,6 +55,7 @@ struct ConvOp {
   int ntaps = 1;                    // taps per group
   int8_t dy[CONV_MAX_GROUPS][9] = {{0}}, dx[CONV_MAX_GROUPS][9] = {{0}};
   const bf16* wmat = nullptr;       // [ngroups*Npad][K] K-major, BN scale folded in; K = ntaps*a0_C + a1_C
+  const bf16* wmat2 = nullptr;      // EPI_HEAD only: [16 = (parity, 2x2 low-res tap)][a0_C] for the taps-in-N head (conv_head.cu)
   int K = 0;
   const float* shift = nullptr;     // [Cout] bias / BN shift (EPI_HEAD: [Npad])
   int Cout = 0;                     // channels of the output tensor
@@ -135,3 +136,6 @@ int dwpw_run(tmat_ctx* ctx, const bf16* in, int B, int S, int C, const float* dw
 bool conv_halo_supported(const ConvOp& op);
 int conv_halo_mode();
 int conv_run_halo(tmat_ctx* ctx, const ConvOp& op, int mode, cudaStream_t st);
+// Head with the (parity, tap) pairs as the 16 GEMM columns of a 1x1 GEMM over the haloed tile (conv_head.cu)
+bool conv_head_taps_supported(const ConvOp& op);
+int conv_run_head_taps(tmat_ctx* ctx, const ConvOp& op, cudaStream_t st);
