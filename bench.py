@@ -532,7 +532,7 @@ def main():
                          "basis": "EXECUTED tensor-pipe FLOPs (parity evaluation of the up path: 4 taps instead of 9) over "
                                   "the summed CUDA-event time of the GEMM launches",
                          "kernel": "the tcgen05 GEMM kernels of the UNet: conv_tc_kernel (implicit-GEMM convolution), "
-                                   "conv_dwpw_kernel (fused SeparableConv2D), conv_halo_kernel (3x3, haloed tile)",
+                                   "conv_dwpw_kernel (fused SeparableConv2D), conv_halo_kernel (3x3, haloed tile), head_taps_kernel (head, taps in N)",
                          "executed_flops_per_step": exec_flops_step, "algorithmic_flops_per_step": algo_flops_step,
                          "effective_tflops": effective,
                          "effective_note": "algorithmic FLOPs (31.026 GFLOP per 320^2 patch as written in models.py) over "
