@@ -23,7 +23,7 @@ per = collections.OrderedDict()
 for d in step:
     e = per.setdefault(short(d['name']), {'launches': 0, 'dram_bytes': 0.0, 'time_us': 0.0})
     e['launches'] += 1; e['dram_bytes'] += d['bytes']; e['time_us'] += d['ns'] / 1e3
-gemm = [k for k in per if k.startswith(('conv_tc_kernel', 'conv_dwpw_kernel', 'conv_halo_kernel'))]
+gemm = [k for k in per if k.startswith(('conv_tc_kernel', 'conv_dwpw_kernel', 'conv_halo_kernel', 'head_taps_kernel'))]
 out = {'source': 'ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none '
                  '--cache-control none over bench.py --steps 1 --warmup 3 (scripts_dev/gpu.sh dram); last step of the list',
        'launches_in_step': len(step), 'gemm_launches': sum(per[k]['launches'] for k in gemm),
