@@ -44,3 +44,25 @@ def test_dmt_graph_live_against_installed_reference():
         assert np.array_equal(v, rv) and np.array_equal(e, re_), (d1, d2)
     with pytest.raises(ValueError):
         dmtgraph.compute_dmt_graph(np.zeros((3, 4, 5), np.float32), 1.0)
+
+
+def test_hull_order_matches_scipy_convex_hull():
+    """tmat_b200.well_mask_generation._hull_order (the exact integer monotone chain that orders the hull vertices for
+    tmat_convex_hull_mask_host) returns scipy's ConvexHull vertex set, as a simple polygon, for any point list."""
+    from scipy.spatial import ConvexHull
+    from tmat_b200.well_mask_generation import _hull_order
+    rng = np.random.default_rng(3)
+    for n, (H, W) in ((3, (50, 60)), (7, (40, 40)), (60, (200, 173)), (400, (64, 64))):
+        pts = np.stack([rng.integers(0, H, n), rng.integers(0, W, n)], axis=1)
+        poly = _hull_order(pts)
+        ref = ConvexHull(pts)
+        assert sorted(poly) == sorted(map(tuple, pts[ref.vertices].tolist()))
+        # same orientation all the way round (strictly convex polygon) and the same area
+        a = np.array(poly, dtype=np.int64)
+        b = np.roll(a, -1, axis=0)
+        c = np.roll(a, -2, axis=0)
+        cross = (b[:, 0] - a[:, 0]) * (c[:, 1] - b[:, 1]) - (b[:, 1] - a[:, 1]) * (c[:, 0] - b[:, 0])
+        assert (cross > 0).all() or (cross < 0).all()
+        area2 = abs(int(np.sum(a[:, 0] * b[:, 1] - b[:, 0] * a[:, 1])))
+        assert abs(area2 / 2 - ref.volume) < 1e-9
+    assert len(_hull_order(np.array([[1, 1], [2, 2], [3, 3], [5, 5]]))) < 3      # collinear: no polygon
