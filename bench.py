@@ -509,9 +509,10 @@ def main():
                 with open(os.path.join(ROOT, "profiles", name)) as f:
                     tr = json.load(f)
                 traffic = tr["gemm_dram_bytes_per_step"]
-                traffic_note = ("dram__bytes_read.sum + dram__bytes_write.sum summed over the %d GEMM launches of one step "
-                                "(ncu, cache-control none; profiles/%s); all %d launches of the step: %.1f GB" %
-                                (tr["gemm_launches"], name, tr["launches_in_step"], tr["all_dram_bytes_per_step"] / 1e9))
+                traffic_note = ("dram__bytes_read.sum + dram__bytes_write.sum summed over the GEMM launches of one step "
+                                "(ncu, cache-control none; profiles/%s, captured with %d GEMM launches = 4 chunks of 338 "
+                                "patches per step; the same work runs as 2 chunks of 676 now); all launches of the step: "
+                                "%.1f GB" % (name, tr["gemm_launches"], tr["all_dram_bytes_per_step"] / 1e9))
         except (OSError, KeyError, ValueError):
             pass
 
@@ -524,8 +525,8 @@ def main():
             "config": {"workload": f"C4 per-image unit: one {size}x{size} float32 projection per rank per step -> "
                                    f"{patches} patches of 320x320 (ws 320, subdiv 2, 8x D4) through the random-init "
                                    "binary_segmentation UNet (64/128/256/512) + spline blend",
-                       "l2": "working set per step (554 MB of patch probabilities + ~13 GB of activations per "
-                             "338-patch chunk) exceeds the 126 MB L2; no explicit flush",
+                       "l2": "working set per step (554 MB of patch probabilities + ~27 GB of activations per "
+                             "676-patch chunk) exceeds the 126 MB L2; no explicit flush",
                        "parallelism": f"image-sharded x{world}"},
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": pk["bf16_sustained"], "unit": "TFLOP/s",
                          "frac": achieved / pk["bf16_sustained"], "traffic": traffic, "traffic_note": traffic_note,

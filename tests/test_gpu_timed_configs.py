@@ -1,6 +1,6 @@
 """GPU: parity on the configurations bench.py actually times.
 
-* C1 exactly: one 1024x1024 projection, ws 320, subdivisions 2 -> 392 patches in two chunks, the
+* C1 exactly: one 1024x1024 projection, ws 320, subdivisions 2 -> 392 patches (one chunk), the
   fused CUDA path vs the oracle driver (smooth_tiled_predictions.py:220-267 restated) with the
   oracle UNet (models.py:110-171 restated) -- Keras-default init and a randomised-affine,
   head-gain-4 variant.
@@ -60,7 +60,8 @@ def chunk_env():
 
 @pytest.mark.parametrize("variant", ["keras_default", "affine_gain4"])
 def test_c1_exact_config_vs_oracle(variant):
-    """BASELINE.json configs[0]: 1024^2, ws 320, subdiv 2 -> pad 1344^2, 7x7x8 = 392 patches = 2 chunks of 196."""
+    """BASELINE.json configs[0]: 1024^2, ws 320, subdiv 2 -> pad 1344^2, 7x7x8 = 392 patches (one chunk by default;
+    forced chunking is covered below)."""
     from tmat_b200 import models
     from tmat_b200.smooth_tiled_predictions import predict_img_with_smooth_windowing
     w = (ou.make_weights(FC, seed=0) if variant == "keras_default"

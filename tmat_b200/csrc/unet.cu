@@ -550,15 +550,18 @@ extern "C" int tmat_unet_free(tmat_unet* net) {
   return TMAT_OK;
 }
 
-// Patches per chunk for n patches: at most ~352 patches of 320x320 (~40 MB of bf16 activations each, 14 GB per chunk),
-// split evenly so that the last chunk is not a short one (1352 patches -> 4 x 338).  Large chunks keep the persistent
-// GEMM kernels at >= 20 tiles per SM even at the 20x20 bottleneck (measured per 2048^2 image: 64 -> 65.8, 128 -> 61.9,
-// 256 -> 60.4 ms on the first path; 256 -> 43.0, 352 -> 42.3, 512 -> 42.5 ms on the final one).
+// Patches per chunk for n patches: at most ~704 patches of 320x320 (~40 MB of bf16 activations each, 27 GB per chunk),
+// split evenly so that the last chunk is not a short one (1352 patches -> 2 x 676).  Large chunks keep the persistent
+// GEMM kernels at >= 20 tiles per SM even at the 20x20 bottleneck and halve the launches and their tails (measured per
+// 2048^2 image: 64 -> 65.8, 128 -> 61.9, 256 -> 60.4 ms on the first path; 256 -> 43.0, 352 -> 42.3, 512 -> 42.5 ms at
+// the end of round 1; with the taps-in-N head, A/B pairs on one box: 4 x 338 -> 41.9 / 42.3, 3 x 451 -> 42.1,
+// 2 x 676 -> 41.6 / 41.3, 1 x 1352 -> 42.0 / 42.2 ms, identical outputs).  All tensor indexing is 64-bit: a chunk's
+// largest tensor (676 x 160 x 160 x 128) has 2.2e9 elements.
 static int chunk_size(const tmat_unet* net, int n) {
   const char* e = getenv("TMAT_CHUNK");
   if (e && atoi(e) > 0) return std::min(n, atoi(e));
   int64_t px = (int64_t)net->desc.patch * net->desc.patch;
-  int cap = (int)(352 * 102400 / px);
+  int cap = (int)(704 * 102400 / px);
   cap = cap < 8 ? 8 : (cap > 2048 ? 2048 : cap);
   const int n_chunks = (n + cap - 1) / cap;
   return (n + n_chunks - 1) / n_chunks;
